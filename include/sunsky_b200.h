@@ -1,0 +1,178 @@
+/* sunsky_b200.h — C ABI of the B200-native sunsky emitter hot path.
+ *
+ * Drop-in boundary for the `sunsky` emitter plugin of matttsss/mitsuba3-sunsky
+ * (reference: src/emitters/sunsky.cpp, class SunskyEmitter, lines 153-1034). The reference exposes
+ * the path only as a C++ class behind Mitsuba's plugin loader (plugin_name()/plugin_descr(),
+ * include/mitsuba/core/class.h:220-225); a Mitsuba adapter plugin or any other host binds the
+ * entry points below instead. Each entry point names the reference member it replaces.
+ *
+ * Conventions
+ *   - all arithmetic is fp32 and follows the reference's llvm_ad_rgb / llvm_ad_spectral op order
+ *   - arrays are planar (SoA): one pointer per component, `n` floats each, caller-owned
+ *   - `*_device` pointers are CUDA device pointers on the context's device; kernels are enqueued
+ *     on the caller's stream (a cudaStream_t passed as void*; NULL = legacy default stream) and
+ *     the call returns without synchronising
+ *   - `*_host` entry points take host pointers, stage through pinned memory, run the same kernels
+ *     and return after the results are in the caller's buffers
+ *   - every function returns SSK_OK (0) or a negative error code; ssk_last_error() describes the
+ *     last failure on the calling thread. There is no CPU fallback: without a CUDA device the
+ *     compute entry points fail with SSK_ERR_CUDA.
+ *   - a context is immutable between ssk_update() calls, so launches may be issued concurrently
+ */
+#ifndef SUNSKY_B200_H
+#define SUNSKY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSK_OK                 0
+#define SSK_ERR_INVALID       -1   /* bad argument / property out of range (reference: Log(Error,..) throws) */
+#define SSK_ERR_IO            -2   /* dataset file missing or malformed */
+#define SSK_ERR_CUDA          -3   /* CUDA runtime failure, or no device */
+#define SSK_ERR_UNSUPPORTED   -4
+
+#define SSK_MODE_RGB           0   /* llvm_ad_rgb:      3 channels */
+#define SSK_MODE_SPECTRAL      1   /* llvm_ad_spectral: 4 wavelengths per ray, 11 dataset bins */
+
+/* ssk_params.flags */
+#define SSK_FLAG_SUN_DIR_NORMALIZED 1u  /* sun_direction is already unit length: use it verbatim */
+
+/* ssk_params.arith */
+#define SSK_ARITH_EXACT        0   /* replay the reference's op sequence (IEEE div/sqrt, CEPHES polynomials) */
+#define SSK_ARITH_FAST         1   /* same formulas, hardware reciprocal / ex2 / lg2 where the error stays
+                                      far below the 1e-5 parity tolerance */
+
+/* The plugin's property surface (reference: src/emitters/sunsky.cpp:19-104, init_from_props :889-948). */
+typedef struct ssk_params {
+    float    turbidity;          /* [1, 10], default 3 */
+    int32_t  n_albedo;           /* 1 = one value for all channels, 3 (RGB) or 11 (spectral bins 320..720 nm) */
+    float    albedo[11];         /* each in [0, 1], default 0.3 */
+    int32_t  use_record;         /* 0: sun_direction, 1: location + date/time record */
+    float    sun_direction[3];   /* world space, pointing towards the sun */
+    float    latitude, longitude, timezone;     /* defaults 35.6894, 139.6917, 9 */
+    int32_t  year, month, day;                  /* defaults 2010, 7, 10 */
+    float    hour, minute, second;              /* defaults 15, 0, 0 */
+    float    sun_scale, sky_scale;              /* >= 0, default 1 */
+    float    sun_aperture_deg;                  /* (0, 180), default 0.5358 */
+    float    to_world[16];                      /* row-major 4x4 affine, default identity */
+    uint32_t flags;
+    int32_t  arith;
+} ssk_params;
+
+/* Interpolated per-emitter state, for parity checks against the reference's private members
+ * (m_sky_params, m_sky_radiance, m_sun_radiance, m_gaussians, m_gaussian_distr, m_sky_sampling_w,
+ * m_sun_angles, m_local_sun_frame; src/emitters/sunsky.cpp:995-1032). */
+typedef struct ssk_state {
+    int32_t n_channels;              /* 3 or 11 */
+    float   sky_params[99];          /* [channel][9] */
+    float   sky_radiance[11];
+    int32_t n_sun_radiance;          /* 3240 (RGB) or 1980 (spectral) */
+    float   sun_radiance[3240];
+    float   sun_ld[66];              /* [wavelength][6], spectral only */
+    float   gaussians[100];          /* [20][mu_phi, mu_theta, sigma_phi, sigma_theta, weight] */
+    float   pmf[20], cdf[20];
+    float   cdf_sum, cdf_normalization;
+    float   sky_sampling_w;
+    float   sun_angles[2];           /* (phi, theta) of the sun in emitter-local coordinates */
+    float   frame_s[3], frame_t[3], frame_n[3];
+    float   sun_half_aperture;       /* radians */
+    float   sun_dir_world[3];
+    float   bsphere_center[3], bsphere_radius;
+    float   spectral_pdf[10], spectral_cdf[10];   /* wavelength distribution over 360..720 nm */
+    float   spectral_integral, spectral_normalization;
+    float   area_ratio;
+    int32_t sun_below_horizon;       /* the reference logs a warning in this case */
+} ssk_state;
+
+typedef struct ssk_ctx ssk_ctx;
+
+const char *ssk_last_error(void);
+const char *ssk_version(void);
+
+/* Fill `p` with the plugin's defaults (src/emitters/sunsky.cpp:889-948). */
+void ssk_params_default(ssk_params *p);
+
+/* SunskyEmitter(const Properties&) (src/emitters/sunsky.cpp:162-218). `dataset_dir` holds the
+ * reference's resources/sunsky/datasets/ *.bin files (format: sunsky.h:515-561). `device` is the CUDA
+ * ordinal; -1 builds a host-only context (state queries work, compute entry points fail). */
+int ssk_create(const ssk_params *p, const char *dataset_dir, int device, int mode, ssk_ctx **out);
+
+/* parameters_changed() after mi.traverse(emitter) updates (src/emitters/sunsky.cpp:220-285). */
+int ssk_update(ssk_ctx *ctx, const ssk_params *p);
+
+/* set_scene(): bounding sphere from the scene bbox; NULL pointers = invalid bbox (:287-301). */
+int ssk_set_scene(ssk_ctx *ctx, const float *bbox_min, const float *bbox_max);
+
+void ssk_destroy(ssk_ctx *ctx);
+int ssk_get_state(const ssk_ctx *ctx, ssk_state *out);
+int ssk_channels(const ssk_ctx *ctx);           /* 3 (RGB) or 4 (spectral: wavelengths per ray) */
+int ssk_device(const ssk_ctx *ctx);
+
+/* to_string() (src/emitters/sunsky.cpp:502-519) */
+int ssk_to_string(const ssk_ctx *ctx, char *buf, size_t len);
+
+/* ---- device entry points ------------------------------------------------------------------- */
+
+/* eval(si) (src/emitters/sunsky.cpp:303-352): radiance arriving along -wi.
+ * wi[3]: si.wi, world space. wavelengths[4]: si.wavelengths in nm (spectral mode; NULL in RGB mode).
+ * out[C]: C = 3 or 4 planes. */
+int ssk_eval_device(const ssk_ctx *ctx, const float *const wi[3], const float *const wavelengths[4],
+                    size_t n, float *const out[4], void *stream);
+
+/* eval_direction(it, ds) (:453-461): same as eval with wi = -ds.d. */
+int ssk_eval_direction_device(const ssk_ctx *ctx, const float *const d[3], const float *const wavelengths[4],
+                              size_t n, float *const out[4], void *stream);
+
+/* pdf_direction(it, ds) (:443-451): solid-angle density of sample_direction at world direction ds.d. */
+int ssk_pdf_direction_device(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf, void *stream);
+
+/* sample_direction(it, u) (:399-441), fused: technique selection, TGMM / sun-cone sample, pdf, eval,
+ * weight = eval / pdf (non-finite -> 0).
+ *   u[2]: the Point2f sample. it_p[3]: it.p (NULL = origin). wavelengths[4]: it.wavelengths (spectral).
+ *   d[3]: ds.d. pdf: ds.pdf. weight[C]: returned spectrum.
+ *   p[3] (nullable): ds.p = it.p + d * dist. dist (nullable): ds.dist = 2 * max(r_bsphere, |it.p - c|).
+ *   ds.n = -d, ds.uv = u, ds.delta = false, ds.time = it.time are trivially reconstructed by the caller. */
+int ssk_sample_direction_device(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
+                                const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
+                                float *const weight[4], float *const p[3], float *dist, void *stream);
+
+/* Equirectangular environment maps (BASELINE configs 4 and 5): one map per context, direction
+ * generated from the pixel centre, no direction buffer is read. Pixel (x, y) looks along
+ *   phi = 2*pi*(x + 0.5)/width, theta = pi*(y + 0.5)/height, d = (sin(theta)cos(phi), sin(theta)sin(phi), cos(theta))
+ * and stores eval(wi = -d). out: n_maps * C planes of width*height floats (map-major, then channel).
+ * wavelengths4: the 4 wavelengths used for every pixel of a spectral map (n_maps * 4 floats, host memory). */
+int ssk_envmap_device(ssk_ctx *const *ctxs, int n_maps, int width, int height, const float *wavelengths4,
+                      float *out, void *stream);
+
+/* ---- host entry points (same semantics; H2D + kernel + D2H inside the call) ------------------- */
+int ssk_eval_host(const ssk_ctx *ctx, const float *const wi[3], const float *const wavelengths[4],
+                  size_t n, float *const out[4]);
+int ssk_eval_direction_host(const ssk_ctx *ctx, const float *const d[3], const float *const wavelengths[4],
+                            size_t n, float *const out[4]);
+int ssk_pdf_direction_host(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf);
+int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
+                              const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
+                              float *const weight[4], float *const p[3], float *dist);
+
+/* Number of kernel launches issued through this library since load (bench bookkeeping). */
+uint64_t ssk_launch_count(void);
+
+/* Host-side helpers that mirror src/render/python/sunsky_v.cpp and sunsky.h utilities */
+/* compute_sun_coordinates (sunsky.h:283-374): date/time/location -> local sun direction */
+int ssk_sun_coordinates(int year, int month, int day, float hour, float minute, float second,
+                        float latitude, float longitude, float timezone, float out_dir[3]);
+/* array_from_file (sunsky.h:515-561): reads a dataset as fp32. *count receives the element count;
+ * shape (nullable) receives up to 8 dims, *ndim their number. `out` may be NULL to query sizes. */
+int ssk_array_from_file(const char *path, int file_is_f64, float *out, size_t capacity, size_t *count,
+                        size_t *shape, size_t *ndim);
+/* array_to_file (sunsky.h:572-597): writes fp32 or fp64 payload with the "SKY" header. */
+int ssk_array_to_file(const char *path, const float *data, const size_t *shape, size_t ndim, int as_f64);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SUNSKY_B200_H */

@@ -1,0 +1,33 @@
+#!/usr/bin/env bash
+# TEST INFRASTRUCTURE. Builds oracle/_ref/libsunsky_ref.so: the reference's own sunsky.cpp + sunsky.h +
+# Dr.Jit/Mitsuba header-only math, compiled IN PLACE from $SSK_REFERENCE (default /root/reference).
+# Nothing from the reference is copied into the repository; generated files stay in oracle/_ref/gen/.
+# Does NOT use the reference's build system (cmake); only its resources/configure.py to emit config.h.
+set -euo pipefail
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF="${SSK_REFERENCE:-/root/reference}"
+OUT="$HERE/_ref"
+GEN="$OUT/gen"
+if [ ! -f "$REF/src/emitters/sunsky.cpp" ]; then
+    echo "build_ref: reference tree not found at $REF; keeping any prebuilt $OUT/libsunsky_ref.so" >&2
+    exit 0
+fi
+mkdir -p "$GEN"
+# 1. config.h for two scalar variants (the macro set is all the headers need)
+if [ ! -f "$GEN/include/mitsuba/core/config.h" ]; then
+    ( cd "$GEN" &&
+      sed 's/@INSERT_CONFIGURATIONS_HERE@/"scalar_rgb", "scalar_spectral"/' "$REF/resources/mitsuba.conf.template" > mitsuba.conf &&
+      python3 "$REF/resources/configure.py" GNU 13.3 "$REF" > /dev/null )
+fi
+# 2. CIE 1931 table block, lifted at build time from the reference's src/core/spectrum.cpp
+awk '/^static const Float cie1931_tbl\[/ {p=1} p {print} p && /};/ {exit}' "$REF/src/core/spectrum.cpp" > "$GEN/cie1931_tbl.inc"
+test -s "$GEN/cie1931_tbl.inc"
+# 3. compile. -mfma + -ffp-contract=off: dr::fmadd is a hardware FMA, a*b+c is not contracted
+#    (what the LLVM backend emits: llvm.fma + plain fmul/fadd, no fast-math flags).
+CXX="${CXX:-g++}"
+FLAGS="-std=c++17 -O2 -fPIC -shared -mavx2 -mfma -ffp-contract=off -fno-fast-math -w -pthread"
+INC="-I $HERE/ref_shadow -I $GEN -I $GEN/include -I $REF -I $REF/include -I $REF/ext/drjit/include \
+ -I $REF/ext/drjit/ext/drjit-core/include -I $REF/ext/drjit/ext/drjit-core/ext/nanothread/include \
+ -I $REF/ext/tinyformat -I $REF/ext/fastfloat/include -I $REF/ext/nanobind/include"
+$CXX $FLAGS $INC "$HERE/ref_harness.cpp" -o "$OUT/libsunsky_ref.so"
+echo "built $OUT/libsunsky_ref.so"
