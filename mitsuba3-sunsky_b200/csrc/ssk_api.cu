@@ -1,0 +1,619 @@
+// C ABI of the B200 sunsky hot path (include/sunsky_b200.h): context management, launch wrappers for
+// the device entry points, and the pinned-staging pipeline behind the host entry points.
+#include "ssk_host.cuh"
+#include "ssk_kernels.cuh"
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <vector>
+#include <algorithm>
+
+using namespace ssk;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<uint64_t> g_launches{ 0 };
+
+int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define SSK_CUDA(call)                                                                             \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(SSK_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));         \
+    } while (0)
+
+struct Staging {            // per-context pinned + device scratch for the *_host entry points
+    static constexpr int kStreams = 3;
+    size_t chunk = 0;       // elements per chunk
+    int planes = 0;
+    float *pinned[kStreams] = { nullptr, nullptr, nullptr };
+    float *dev[kStreams] = { nullptr, nullptr, nullptr };
+    cudaStream_t stream[kStreams] = { nullptr, nullptr, nullptr };
+    std::mutex mu;
+};
+
+} // namespace
+
+struct ssk_ctx {
+    HostEmitter E;
+    int device = -1;
+    int mode = SSK_MODE_RGB;
+    EmitterBlock *d_block = nullptr;
+    int sm_count = 0;
+    int grid_cap[8] = { 0 };    // resident CTAs per SM, per kernel family
+    mutable Staging st;
+};
+
+namespace {
+
+constexpr size_t kSmemBytes = offsetof(EmitterBlock, sun_rad);
+
+bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <typename K> int occupancy_grid(const ssk_ctx *ctx, K kernel, size_t n_items, int *grid_out) {
+    int per_sm = 0;
+    SSK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, kSmemBytes));
+    if (per_sm < 1) per_sm = 1;
+    size_t want = (n_items + (size_t) kThreads * kVec - 1) / ((size_t) kThreads * kVec);
+    size_t cap = (size_t) ctx->sm_count * per_sm;
+    *grid_out = (int) std::max<size_t>(1, std::min(want, cap));
+    return SSK_OK;
+}
+
+int upload_block(ssk_ctx *ctx) {
+    if (ctx->device < 0) return SSK_OK;
+    SSK_CUDA(cudaSetDevice(ctx->device));
+    if (!ctx->d_block) SSK_CUDA(cudaMalloc(&ctx->d_block, sizeof(EmitterBlock)));
+    // synchronous on purpose: a context is immutable between updates
+    SSK_CUDA(cudaMemcpy(ctx->d_block, &ctx->E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice));
+    return SSK_OK;
+}
+
+int need_device(const ssk_ctx *ctx) {
+    if (!ctx) return fail(SSK_ERR_INVALID, "null context");
+    if (ctx->device < 0 || !ctx->d_block)
+        return fail(SSK_ERR_CUDA, "context has no CUDA device: the sunsky kernels have no CPU fallback");
+    SSK_CUDA(cudaSetDevice(ctx->device));
+    return SSK_OK;
+}
+
+int launch_eval(const ssk_ctx *ctx, const float *const in[3], const float *const wav[4], size_t n,
+                float *const out[4], float dir_sign, cudaStream_t s) {
+    if (int rc = need_device(ctx)) return rc;
+    if (!in || !out || !in[0] || !in[1] || !in[2]) return fail(SSK_ERR_INVALID, "null direction / output planes");
+    if (n == 0) return SSK_OK;
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    const int C = spectral ? 4 : 3;
+    bool vec = aligned16(in[0]) && aligned16(in[1]) && aligned16(in[2]);
+    for (int c = 0; c < C; ++c) {
+        if (!out[c]) return fail(SSK_ERR_INVALID, "null output plane");
+        vec = vec && aligned16(out[c]);
+    }
+    int grid = 1;
+    if (spectral) {
+        if (!wav || !wav[0] || !wav[1] || !wav[2] || !wav[3])
+            return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
+        for (int c = 0; c < 4; ++c) vec = vec && aligned16(wav[c]);
+        Planes3 i3 = { in[0], in[1], in[2] };
+        Planes4 w4 = { wav[0], wav[1], wav[2], wav[3] };
+        OutPlanes4 o4 = { out[0], out[1], out[2], out[3] };
+        if (vec) {
+            if (int rc = occupancy_grid(ctx, eval_spec_kernel<true>, n, &grid)) return rc;
+            eval_spec_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, w4, o4, n, dir_sign);
+        } else {
+            if (int rc = occupancy_grid(ctx, eval_spec_kernel<false>, n, &grid)) return rc;
+            eval_spec_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, w4, o4, n, dir_sign);
+        }
+    } else {
+        Planes3 i3 = { in[0], in[1], in[2] };
+        OutPlanes3 o3 = { out[0], out[1], out[2] };
+        if (vec) {
+            if (int rc = occupancy_grid(ctx, eval_rgb_kernel<true>, n, &grid)) return rc;
+            eval_rgb_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, o3, n, dir_sign);
+        } else {
+            if (int rc = occupancy_grid(ctx, eval_rgb_kernel<false>, n, &grid)) return rc;
+            eval_rgb_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, o3, n, dir_sign);
+        }
+    }
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+int launch_pdf(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf, cudaStream_t s) {
+    if (int rc = need_device(ctx)) return rc;
+    if (!d || !d[0] || !d[1] || !d[2] || !pdf) return fail(SSK_ERR_INVALID, "null direction / pdf planes");
+    if (n == 0) return SSK_OK;
+    bool vec = aligned16(d[0]) && aligned16(d[1]) && aligned16(d[2]) && aligned16(pdf);
+    Planes3 i3 = { d[0], d[1], d[2] };
+    int grid = 1;
+    if (vec) {
+        if (int rc = occupancy_grid(ctx, pdf_kernel<true>, n, &grid)) return rc;
+        pdf_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, pdf, n);
+    } else {
+        if (int rc = occupancy_grid(ctx, pdf_kernel<false>, n, &grid)) return rc;
+        pdf_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, pdf, n);
+    }
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+template <bool Vec, bool Spectral>
+int launch_sample_t(const ssk_ctx *ctx, const SampleArgs &a, size_t n, cudaStream_t s) {
+    int grid = 1;
+    if (int rc = occupancy_grid(ctx, sample_kernel<Vec, Spectral>, n, &grid)) return rc;
+    sample_kernel<Vec, Spectral><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, a, n);
+    return SSK_OK;
+}
+
+int launch_sample(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
+                  const float *const wav[4], size_t n, float *const d[3], float *pdf, float *const weight[4],
+                  float *const p[3], float *dist, cudaStream_t s) {
+    if (int rc = need_device(ctx)) return rc;
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    const int C = spectral ? 4 : 3;
+    if (!u || !u[0] || !u[1] || !d || !d[0] || !d[1] || !d[2] || !pdf || !weight)
+        return fail(SSK_ERR_INVALID, "null sample / output planes");
+    if (n == 0) return SSK_OK;
+    SampleArgs a = {};
+    a.u0 = u[0]; a.u1 = u[1];
+    bool vec = aligned16(u[0]) && aligned16(u[1]) && aligned16(d[0]) && aligned16(d[1]) && aligned16(d[2]) && aligned16(pdf);
+    if (it_p && it_p[0]) {
+        if (!it_p[1] || !it_p[2]) return fail(SSK_ERR_INVALID, "it_p needs 3 planes");
+        a.px = it_p[0]; a.py = it_p[1]; a.pz = it_p[2];
+        vec = vec && aligned16(a.px) && aligned16(a.py) && aligned16(a.pz);
+    }
+    if (spectral) {
+        if (!wav || !wav[0] || !wav[1] || !wav[2] || !wav[3])
+            return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
+        a.w0 = wav[0]; a.w1 = wav[1]; a.w2 = wav[2]; a.w3 = wav[3];
+        for (int c = 0; c < 4; ++c) vec = vec && aligned16(wav[c]);
+    }
+    a.dx = d[0]; a.dy = d[1]; a.dz = d[2]; a.pdf = pdf;
+    float *q[4] = { nullptr, nullptr, nullptr, nullptr };
+    for (int c = 0; c < C; ++c) {
+        if (!weight[c]) return fail(SSK_ERR_INVALID, "null weight plane");
+        q[c] = weight[c]; vec = vec && aligned16(q[c]);
+    }
+    a.q0 = q[0]; a.q1 = q[1]; a.q2 = q[2]; a.q3 = q[3];
+    if (p && p[0]) {
+        if (!p[1] || !p[2]) return fail(SSK_ERR_INVALID, "p needs 3 planes");
+        a.ox = p[0]; a.oy = p[1]; a.oz = p[2];
+        vec = vec && aligned16(a.ox) && aligned16(a.oy) && aligned16(a.oz);
+    }
+    if (dist) { a.dist = dist; vec = vec && aligned16(dist); }
+    int rc;
+    if (spectral) rc = vec ? launch_sample_t<true, true>(ctx, a, n, s) : launch_sample_t<false, true>(ctx, a, n, s);
+    else rc = vec ? launch_sample_t<true, false>(ctx, a, n, s) : launch_sample_t<false, false>(ctx, a, n, s);
+    if (rc) return rc;
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+// ---- host entry points: chunked H2D -> kernel -> D2H over 3 streams with pinned staging ---------
+int ensure_staging(const ssk_ctx *ctx, int planes) {
+    Staging &st = ctx->st;
+    const size_t chunk = (size_t) 1 << 20;          // 1 Mi elements per chunk and plane (4 MiB)
+    if (st.planes >= planes && st.chunk == chunk) return SSK_OK;
+    for (int i = 0; i < Staging::kStreams; ++i) {
+        if (st.pinned[i]) cudaFreeHost(st.pinned[i]);
+        if (st.dev[i]) cudaFree(st.dev[i]);
+        st.pinned[i] = nullptr; st.dev[i] = nullptr;
+        if (!st.stream[i]) SSK_CUDA(cudaStreamCreateWithFlags(&st.stream[i], cudaStreamNonBlocking));
+        SSK_CUDA(cudaMallocHost(&st.pinned[i], (size_t) planes * chunk * sizeof(float)));
+        SSK_CUDA(cudaMalloc(&st.dev[i], (size_t) planes * chunk * sizeof(float)));
+    }
+    st.planes = planes; st.chunk = chunk;
+    return SSK_OK;
+}
+
+bool is_pinned(const void *p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost;
+}
+
+/// Generic pipeline: `n_in` input planes, `n_out` output planes, `launch(dev_in[], dev_out[], m, stream)`.
+template <typename Launch>
+int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *const *out, int n_out, size_t n,
+                  Launch &&launch) {
+    if (int rc = need_device(ctx)) return rc;
+    if (n == 0) return SSK_OK;
+    std::lock_guard<std::mutex> lock(ctx->st.mu);
+    if (int rc = ensure_staging(ctx, n_in + n_out)) return rc;
+    Staging &st = ctx->st;
+    const size_t chunk = st.chunk;
+    bool pin_in = true, pin_out = true;
+    for (int k = 0; k < n_in; ++k) pin_in = pin_in && is_pinned(in[k]);
+    for (int k = 0; k < n_out; ++k) pin_out = pin_out && is_pinned(out[k]);
+    const size_t n_chunks = (n + chunk - 1) / chunk;
+    // pending[i]: chunk index whose results still sit in staging slot i (pageable outputs only)
+    std::vector<long long> pending(Staging::kStreams, -1);
+    auto drain = [&](int slot) -> int {
+        if (pending[slot] < 0) return SSK_OK;
+        SSK_CUDA(cudaStreamSynchronize(st.stream[slot]));
+        if (!pin_out) {
+            size_t off = (size_t) pending[slot] * chunk, m = std::min(chunk, n - off);
+            for (int k = 0; k < n_out; ++k)
+                memcpy(out[k] + off, st.pinned[slot] + (size_t) (n_in + k) * chunk, m * sizeof(float));
+        }
+        pending[slot] = -1;
+        return SSK_OK;
+    };
+    for (size_t ci = 0; ci < n_chunks; ++ci) {
+        int slot = (int) (ci % Staging::kStreams);
+        if (int rc = drain(slot)) return rc;
+        size_t off = ci * chunk, m = std::min(chunk, n - off);
+        cudaStream_t s = st.stream[slot];
+        const float *din[16]; float *dout[16];
+        for (int k = 0; k < n_in; ++k) {
+            float *dst = st.dev[slot] + (size_t) k * chunk;
+            const float *src = in[k] + off;
+            if (!pin_in) {
+                float *stage = st.pinned[slot] + (size_t) k * chunk;
+                memcpy(stage, src, m * sizeof(float));
+                src = stage;
+            }
+            SSK_CUDA(cudaMemcpyAsync(dst, src, m * sizeof(float), cudaMemcpyHostToDevice, s));
+            din[k] = dst;
+        }
+        for (int k = 0; k < n_out; ++k) dout[k] = st.dev[slot] + (size_t) (n_in + k) * chunk;
+        if (int rc = launch(din, dout, m, s)) return rc;
+        for (int k = 0; k < n_out; ++k) {
+            float *dst = pin_out ? out[k] + off : st.pinned[slot] + (size_t) (n_in + k) * chunk;
+            SSK_CUDA(cudaMemcpyAsync(dst, dout[k], m * sizeof(float), cudaMemcpyDeviceToHost, s));
+        }
+        pending[slot] = (long long) ci;
+    }
+    for (int i = 0; i < Staging::kStreams; ++i)
+        if (int rc = drain(i)) return rc;
+    return SSK_OK;
+}
+
+template <typename F> int guarded(F &&f) {
+    try { return f(); }
+    catch (const std::invalid_argument &e) { return fail(SSK_ERR_INVALID, e.what()); }
+    catch (const std::runtime_error &e) {
+        std::string m = e.what();
+        bool io = m.find("file") != std::string::npos || m.find("dataset") != std::string::npos ||
+                  m.find("truncated") != std::string::npos || m.find("header") != std::string::npos;
+        return fail(io ? SSK_ERR_IO : SSK_ERR_INVALID, m);
+    }
+    catch (const std::exception &e) { return fail(SSK_ERR_INVALID, e.what()); }
+}
+
+} // namespace
+
+extern "C" {
+
+const char *ssk_last_error(void) { return g_err.c_str(); }
+const char *ssk_version(void) { return "sunsky_b200 0.1 (sm_100a)"; }
+uint64_t ssk_launch_count(void) { return g_launches.load(); }
+
+void ssk_params_default(ssk_params *p) {
+    memset(p, 0, sizeof(*p));
+    p->turbidity = 3.f;
+    p->n_albedo = 1; p->albedo[0] = 0.3f;
+    p->use_record = 1;
+    p->sun_direction[2] = 1.f;
+    p->latitude = 35.6894f; p->longitude = 139.6917f; p->timezone = 9.f;
+    p->year = 2010; p->month = 7; p->day = 10;
+    p->hour = 15.f; p->minute = 0.f; p->second = 0.f;
+    p->sun_scale = 1.f; p->sky_scale = 1.f;
+    p->sun_aperture_deg = (float) 0.5358;
+    for (int i = 0; i < 4; ++i) p->to_world[i * 5] = 1.f;
+    p->flags = 0; p->arith = SSK_ARITH_EXACT;
+}
+
+int ssk_create(const ssk_params *p, const char *dataset_dir, int device, int mode, ssk_ctx **out) {
+    if (!p || !dataset_dir || !out) return fail(SSK_ERR_INVALID, "null argument");
+    if (mode != SSK_MODE_RGB && mode != SSK_MODE_SPECTRAL)
+        return fail(SSK_ERR_UNSUPPORTED, "Unsupported spectrum type, can only render in Spectral or RGB modes!");
+    *out = nullptr;
+    ssk_ctx *ctx = new ssk_ctx();
+    int rc = guarded([&]() -> int {
+        ctx->mode = mode;
+        ctx->device = device;
+        ctx->E.spectral = mode == SSK_MODE_SPECTRAL;
+        ctx->E.n_channels = ctx->E.spectral ? 11 : 3;
+        ctx->E.data = load_datasets(dataset_dir, ctx->E.spectral);
+        build_emitter(ctx->E, *p, true);
+        if (device >= 0) {
+            int count = 0;
+            cudaError_t e = cudaGetDeviceCount(&count);
+            if (e != cudaSuccess || device >= count)
+                return fail(SSK_ERR_CUDA, std::string("CUDA device ") + std::to_string(device) + " is not available: " +
+                                              (e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range"));
+            SSK_CUDA(cudaSetDevice(device));
+            SSK_CUDA(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
+            return upload_block(ctx);
+        }
+        return SSK_OK;
+    });
+    if (rc) { ssk_destroy(ctx); return rc; }
+    *out = ctx;
+    return SSK_OK;
+}
+
+int ssk_update(ssk_ctx *ctx, const ssk_params *p) {
+    if (!ctx || !p) return fail(SSK_ERR_INVALID, "null argument");
+    return guarded([&]() -> int {
+        HostEmitter backup = ctx->E;
+        try { build_emitter(ctx->E, *p, false); }
+        catch (...) { ctx->E = backup; throw; }
+        return upload_block(ctx);
+    });
+}
+
+int ssk_set_scene(ssk_ctx *ctx, const float *bmin, const float *bmax) {
+    if (!ctx) return fail(SSK_ERR_INVALID, "null context");
+    // set_scene (sunsky.cpp:287-301); math::RayEpsilon<float> = 89.40697e-6 (Epsilon * 1500)
+    const float ray_eps = SSK_EPSILON * 1500.f;
+    HostEmitter &E = ctx->E;
+    bool valid = bmin && bmax && bmin[0] <= bmax[0] && bmin[1] <= bmax[1] && bmin[2] <= bmax[2];
+    if (valid) {
+        // ScalarBoundingBox3f::bounding_sphere(): center = (min + max) * 0.5, radius = |max - center|
+        float c[3], r2 = 0.f;
+        for (int i = 0; i < 3; ++i) { c[i] = (bmax[i] + bmin[i]) * 0.5f; }
+        for (int i = 0; i < 3; ++i) { float d = bmax[i] - c[i]; r2 += d * d; }
+        float radius = sqrtf(r2);
+        for (int i = 0; i < 3; ++i) E.bs_center[i] = c[i];
+        E.bs_radius = fmaxf(ray_eps, radius * (1.f + ray_eps));
+    } else {
+        E.bs_center[0] = E.bs_center[1] = E.bs_center[2] = 0.f;
+        E.bs_radius = ray_eps;
+    }
+    for (int i = 0; i < 3; ++i) E.block.bs_center[i] = E.bs_center[i];
+    E.block.bs_radius = E.bs_radius;
+    return upload_block(ctx);
+}
+
+void ssk_destroy(ssk_ctx *ctx) {
+    if (!ctx) return;
+    if (ctx->device >= 0) {
+        cudaSetDevice(ctx->device);
+        for (int i = 0; i < Staging::kStreams; ++i) {
+            if (ctx->st.stream[i]) { cudaStreamSynchronize(ctx->st.stream[i]); cudaStreamDestroy(ctx->st.stream[i]); }
+            if (ctx->st.pinned[i]) cudaFreeHost(ctx->st.pinned[i]);
+            if (ctx->st.dev[i]) cudaFree(ctx->st.dev[i]);
+        }
+        if (ctx->d_block) cudaFree(ctx->d_block);
+    }
+    delete ctx;
+}
+
+int ssk_channels(const ssk_ctx *ctx) { return ctx ? (ctx->mode == SSK_MODE_SPECTRAL ? 4 : 3) : 0; }
+int ssk_device(const ssk_ctx *ctx) { return ctx ? ctx->device : -1; }
+
+int ssk_get_state(const ssk_ctx *ctx, ssk_state *s) {
+    if (!ctx || !s) return fail(SSK_ERR_INVALID, "null argument");
+    const HostEmitter &E = ctx->E;
+    memset(s, 0, sizeof(*s));
+    s->n_channels = E.n_channels;
+    memcpy(s->sky_params, E.sky_params, sizeof(float) * E.n_channels * 9);
+    memcpy(s->sky_radiance, E.sky_radiance, sizeof(float) * E.n_channels);
+    s->n_sun_radiance = (int32_t) E.sun_radiance.size();
+    memcpy(s->sun_radiance, E.sun_radiance.data(), sizeof(float) * E.sun_radiance.size());
+    if (E.spectral) memcpy(s->sun_ld, E.data.sun_ld.data(), sizeof(float) * 66);
+    memcpy(s->gaussians, E.gaussians, sizeof(E.gaussians));
+    memcpy(s->pmf, E.pmf, sizeof(E.pmf)); memcpy(s->cdf, E.cdf, sizeof(E.cdf));
+    s->cdf_sum = E.cdf_sum; s->cdf_normalization = E.cdf_norm; s->sky_sampling_w = E.sky_w;
+    s->sun_angles[0] = E.sun_angles[0]; s->sun_angles[1] = E.sun_angles[1];
+    for (int i = 0; i < 3; ++i) {
+        s->frame_s[i] = E.block.sun_s[i]; s->frame_t[i] = E.block.sun_t[i]; s->frame_n[i] = E.block.sun_n[i];
+        s->bsphere_center[i] = E.bs_center[i];
+    }
+    s->sun_dir_world[0] = E.sun_dir_world.x; s->sun_dir_world[1] = E.sun_dir_world.y; s->sun_dir_world[2] = E.sun_dir_world.z;
+    s->sun_half_aperture = E.half_aperture;
+    s->bsphere_radius = E.bs_radius;
+    memcpy(s->spectral_pdf, E.spectral_pdf, sizeof(E.spectral_pdf));
+    memcpy(s->spectral_cdf, E.spectral_cdf, sizeof(E.spectral_cdf));
+    s->spectral_integral = E.spectral_integral; s->spectral_normalization = E.spectral_norm;
+    s->area_ratio = E.area_ratio;
+    s->sun_below_horizon = E.sun_below_horizon ? 1 : 0;
+    return SSK_OK;
+}
+
+int ssk_to_string(const ssk_ctx *ctx, char *buf, size_t len) {
+    if (!ctx || !buf) return fail(SSK_ERR_INVALID, "null argument");
+    const HostEmitter &E = ctx->E; const ssk_params &p = E.params;
+    char tmp[1024];
+    int k = snprintf(tmp, sizeof(tmp),
+                     "SunskyEmitter[\n  bsphere = [center = [%g, %g, %g], radius = %g]\n  turbidity = %g\n"
+                     "  sky_scale = %g\n  sun_scale = %g\n  albedo = %g%s\n  sun aperture (deg) = %g\n",
+                     E.bs_center[0], E.bs_center[1], E.bs_center[2], E.bs_radius, p.turbidity, p.sky_scale,
+                     p.sun_scale, p.albedo[0], p.n_albedo > 1 ? ", ..." : "", p.sun_aperture_deg);
+    if (E.active_record)
+        snprintf(tmp + k, sizeof(tmp) - k,
+                 "  location = LocationRecord[latitude = %g, longitude = %g, timezone = %g]\n"
+                 "  date_time = DateTimeRecord[year = %d, month= %d, day = %d, hour = %g, minute = %g, second = %g]\n]",
+                 p.latitude, p.longitude, p.timezone, p.year, p.month, p.day, p.hour, p.minute, p.second);
+    else
+        snprintf(tmp + k, sizeof(tmp) - k, "  sun_dir = [%g, %g, %g]\n]", E.sun_dir_world.x, E.sun_dir_world.y, E.sun_dir_world.z);
+    snprintf(buf, len, "%s", tmp);
+    return SSK_OK;
+}
+
+int ssk_eval_device(const ssk_ctx *ctx, const float *const wi[3], const float *const wav[4], size_t n,
+                    float *const out[4], void *stream) {
+    return launch_eval(ctx, wi, wav, n, out, 1.f, (cudaStream_t) stream);
+}
+int ssk_eval_direction_device(const ssk_ctx *ctx, const float *const d[3], const float *const wav[4], size_t n,
+                              float *const out[4], void *stream) {
+    return launch_eval(ctx, d, wav, n, out, -1.f, (cudaStream_t) stream);
+}
+int ssk_pdf_direction_device(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf, void *stream) {
+    return launch_pdf(ctx, d, n, pdf, (cudaStream_t) stream);
+}
+int ssk_sample_direction_device(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
+                                const float *const wav[4], size_t n, float *const d[3], float *pdf,
+                                float *const weight[4], float *const p[3], float *dist, void *stream) {
+    return launch_sample(ctx, u, it_p, wav, n, d, pdf, weight, p, dist, (cudaStream_t) stream);
+}
+
+int ssk_envmap_device(ssk_ctx *const *ctxs, int n_maps, int width, int height, const float *wavelengths4,
+                      float *out, void *stream) {
+    if (!ctxs || n_maps <= 0 || width <= 0 || height <= 0 || !out) return fail(SSK_ERR_INVALID, "bad envmap arguments");
+    const ssk_ctx *c0 = ctxs[0];
+    if (int rc = need_device(c0)) return rc;
+    const bool spectral = c0->mode == SSK_MODE_SPECTRAL;
+    if (spectral && !wavelengths4) return fail(SSK_ERR_INVALID, "spectral env maps need 4 wavelengths per map");
+    std::vector<const EmitterBlock *> h(n_maps);
+    for (int i = 0; i < n_maps; ++i) {
+        if (!ctxs[i] || ctxs[i]->device != c0->device || ctxs[i]->mode != c0->mode || !ctxs[i]->d_block)
+            return fail(SSK_ERR_INVALID, "env-map contexts must share device and mode");
+        h[i] = ctxs[i]->d_block;
+    }
+    cudaStream_t s = (cudaStream_t) stream;
+    const EmitterBlock **d_ptrs = nullptr; float *d_wav = nullptr;
+    SSK_CUDA(cudaMallocAsync((void **) &d_ptrs, sizeof(void *) * n_maps, s));
+    SSK_CUDA(cudaMemcpyAsync(d_ptrs, h.data(), sizeof(void *) * n_maps, cudaMemcpyHostToDevice, s));
+    if (spectral) {
+        SSK_CUDA(cudaMallocAsync((void **) &d_wav, sizeof(float) * 4 * n_maps, s));
+        SSK_CUDA(cudaMemcpyAsync(d_wav, wavelengths4, sizeof(float) * 4 * n_maps, cudaMemcpyHostToDevice, s));
+    }
+    // the pointer / wavelength tables come from pageable host memory: wait until they are consumed
+    size_t npix = (size_t) width * height;
+    size_t want = (npix + (size_t) kThreads * kVec - 1) / ((size_t) kThreads * kVec);
+    int gx = (int) std::max<size_t>(1, std::min<size_t>(want, (size_t) c0->sm_count * 8));
+    dim3 grid(gx, n_maps);
+    if (spectral) envmap_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(d_ptrs, d_wav, out, width, height);
+    else envmap_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(d_ptrs, d_wav, out, width, height);
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    SSK_CUDA(cudaFreeAsync(d_ptrs, s));
+    if (d_wav) SSK_CUDA(cudaFreeAsync(d_wav, s));
+    return SSK_OK;
+}
+
+int ssk_envmap_directions_device(const ssk_ctx *ctx, int width, int height, float *const d[3], void *stream) {
+    if (int rc = need_device(ctx)) return rc;
+    if (!d || !d[0] || !d[1] || !d[2]) return fail(SSK_ERR_INVALID, "null planes");
+    envmap_dirs_kernel<<<ctx->sm_count * 4, 256, 0, (cudaStream_t) stream>>>(d[0], d[1], d[2], width, height);
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+int ssk_eval_host(const ssk_ctx *ctx, const float *const wi[3], const float *const wav[4], size_t n, float *const out[4]) {
+    if (!ctx || !wi || !out) return fail(SSK_ERR_INVALID, "null argument");
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    if (spectral && !wav) return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
+    const float *in[7] = { wi[0], wi[1], wi[2], spectral ? wav[0] : nullptr, spectral ? wav[1] : nullptr,
+                           spectral ? wav[2] : nullptr, spectral ? wav[3] : nullptr };
+    const int n_in = spectral ? 7 : 3, n_out = spectral ? 4 : 3;
+    for (int k = 0; k < n_in; ++k) if (!in[k]) return fail(SSK_ERR_INVALID, "null input plane");
+    for (int k = 0; k < n_out; ++k) if (!out[k]) return fail(SSK_ERR_INVALID, "null output plane");
+    return host_pipeline(ctx, in, n_in, out, n_out, n, [&](const float **din, float **dout, size_t m, cudaStream_t s) {
+        return launch_eval(ctx, din, din + 3, m, dout, 1.f, s);
+    });
+}
+
+int ssk_eval_direction_host(const ssk_ctx *ctx, const float *const d[3], const float *const wav[4], size_t n,
+                            float *const out[4]) {
+    if (!ctx || !d || !out) return fail(SSK_ERR_INVALID, "null argument");
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    if (spectral && !wav) return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
+    const float *in[7] = { d[0], d[1], d[2], spectral ? wav[0] : nullptr, spectral ? wav[1] : nullptr,
+                           spectral ? wav[2] : nullptr, spectral ? wav[3] : nullptr };
+    const int n_in = spectral ? 7 : 3, n_out = spectral ? 4 : 3;
+    for (int k = 0; k < n_in; ++k) if (!in[k]) return fail(SSK_ERR_INVALID, "null input plane");
+    for (int k = 0; k < n_out; ++k) if (!out[k]) return fail(SSK_ERR_INVALID, "null output plane");
+    return host_pipeline(ctx, in, n_in, out, n_out, n, [&](const float **din, float **dout, size_t m, cudaStream_t s) {
+        return launch_eval(ctx, din, din + 3, m, dout, -1.f, s);
+    });
+}
+
+int ssk_pdf_direction_host(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf) {
+    if (!ctx || !d || !pdf || !d[0] || !d[1] || !d[2]) return fail(SSK_ERR_INVALID, "null argument");
+    const float *in[3] = { d[0], d[1], d[2] };
+    float *out[1] = { pdf };
+    return host_pipeline(ctx, in, 3, out, 1, n, [&](const float **din, float **dout, size_t m, cudaStream_t s) {
+        return launch_pdf(ctx, din, m, dout[0], s);
+    });
+}
+
+int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
+                              const float *const wav[4], size_t n, float *const d[3], float *pdf,
+                              float *const weight[4], float *const p[3], float *dist) {
+    if (!ctx || !u || !d || !pdf || !weight) return fail(SSK_ERR_INVALID, "null argument");
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    const int C = spectral ? 4 : 3;
+    const bool has_p = it_p && it_p[0], want_p = p && p[0], want_dist = dist != nullptr;
+    if (spectral && !wav) return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
+    const float *in[9]; int n_in = 0;
+    in[n_in++] = u[0]; in[n_in++] = u[1];
+    if (has_p) { in[n_in++] = it_p[0]; in[n_in++] = it_p[1]; in[n_in++] = it_p[2]; }
+    if (spectral) for (int c = 0; c < 4; ++c) in[n_in++] = wav[c];
+    float *out[12]; int n_out = 0;
+    out[n_out++] = d[0]; out[n_out++] = d[1]; out[n_out++] = d[2]; out[n_out++] = pdf;
+    for (int c = 0; c < C; ++c) out[n_out++] = weight[c];
+    if (want_p) { out[n_out++] = p[0]; out[n_out++] = p[1]; out[n_out++] = p[2]; }
+    if (want_dist) out[n_out++] = dist;
+    for (int k = 0; k < n_in; ++k) if (!in[k]) return fail(SSK_ERR_INVALID, "null input plane");
+    for (int k = 0; k < n_out; ++k) if (!out[k]) return fail(SSK_ERR_INVALID, "null output plane");
+    return host_pipeline(ctx, in, n_in, out, n_out, n, [&](const float **din, float **dout, size_t m, cudaStream_t s) {
+        int k = 2;
+        const float *dp[3] = { nullptr, nullptr, nullptr };
+        if (has_p) { dp[0] = din[k]; dp[1] = din[k + 1]; dp[2] = din[k + 2]; k += 3; }
+        const float *dw[4] = { nullptr, nullptr, nullptr, nullptr };
+        if (spectral) for (int c = 0; c < 4; ++c) dw[c] = din[k++];
+        int o = 4;
+        float *wq[4] = { nullptr, nullptr, nullptr, nullptr };
+        for (int c = 0; c < C; ++c) wq[c] = dout[o++];
+        float *op[3] = { nullptr, nullptr, nullptr };
+        if (want_p) { op[0] = dout[o]; op[1] = dout[o + 1]; op[2] = dout[o + 2]; o += 3; }
+        float *od = want_dist ? dout[o++] : nullptr;
+        return launch_sample(ctx, din, has_p ? dp : nullptr, spectral ? dw : nullptr, m, dout, dout[3], wq,
+                             want_p ? op : nullptr, od, s);
+    });
+}
+
+int ssk_sun_coordinates(int year, int month, int day, float hour, float minute, float second, float latitude,
+                        float longitude, float timezone, float out_dir[3]) {
+    if (!out_dir) return fail(SSK_ERR_INVALID, "null argument");
+    DateTime dt = { year, month, day, hour, minute, second };
+    Location loc = { latitude, longitude, timezone };
+    Vec3 v = sun_coordinates(dt, loc);
+    out_dir[0] = v.x; out_dir[1] = v.y; out_dir[2] = v.z;
+    return SSK_OK;
+}
+
+int ssk_array_from_file(const char *path, int file_is_f64, float *out, size_t capacity, size_t *count,
+                        size_t *shape, size_t *ndim) {
+    if (!path) return fail(SSK_ERR_INVALID, "null path");
+    return guarded([&]() -> int {
+        std::vector<size_t> sh;
+        std::vector<float> v = read_dataset(path, file_is_f64 != 0, &sh);
+        if (count) *count = v.size();
+        if (ndim) *ndim = sh.size();
+        if (shape) for (size_t i = 0; i < sh.size() && i < 8; ++i) shape[i] = sh[i];
+        if (out) {
+            if (capacity < v.size()) return fail(SSK_ERR_INVALID, "output buffer too small");
+            memcpy(out, v.data(), v.size() * sizeof(float));
+        }
+        return SSK_OK;
+    });
+}
+
+int ssk_array_to_file(const char *path, const float *data, const size_t *shape, size_t ndim, int as_f64) {
+    if (!path || !data || !shape || ndim == 0) return fail(SSK_ERR_INVALID, "null argument");
+    FILE *f = fopen(path, "wb");
+    if (!f) return fail(SSK_ERR_IO, std::string("cannot open ") + path);
+    size_t count = 1;
+    uint32_t version = 0; uint64_t nd = ndim;
+    fwrite("SKY", 1, 3, f); fwrite(&version, 4, 1, f); fwrite(&nd, 8, 1, f);
+    for (size_t i = 0; i < ndim; ++i) {
+        if (!shape[i]) { fclose(f); return fail(SSK_ERR_INVALID, "Got dimension with 0 elements"); }
+        uint64_t d = shape[i]; fwrite(&d, 8, 1, f); count *= shape[i];
+    }
+    if (as_f64) { for (size_t i = 0; i < count; ++i) { double v = data[i]; fwrite(&v, 8, 1, f); } }
+    else fwrite(data, 4, count, f);
+    fclose(f);
+    return SSK_OK;
+}
+
+} // extern "C"

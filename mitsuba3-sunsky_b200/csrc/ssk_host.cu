@@ -1,0 +1,281 @@
+// Host setup of a sunsky emitter: see ssk_host.cuh. Compiled by nvcc with -fmad=false and the host
+// compiler's contraction off, so the fp32 op order below is the one that executes.
+#include "ssk_host.cuh"
+#include <cstring>
+
+namespace ssk {
+
+static std::string fmt(const char *f, double v) { char b[256]; snprintf(b, sizeof(b), f, v); return b; }
+
+/// Property validation of init_from_props / parameters_changed (sunsky.cpp:243-252, 889-948, 974-975)
+void validate_params(const ssk_params &p, bool spectral) {
+    if (!(p.sun_scale >= 0.f)) throw std::invalid_argument(fmt("Invalid sun scale: %f, must be positive!", p.sun_scale));
+    if (!(p.sky_scale >= 0.f)) throw std::invalid_argument(fmt("Invalid sky scale: %f, must be positive!", p.sky_scale));
+    if (!(p.turbidity >= 1.f && p.turbidity <= 10.f))
+        throw std::invalid_argument(fmt("Turbidity value %f is out of range [1, 10]", p.turbidity));
+    float half = 0.5f * p.sun_aperture_deg * (float) (3.14159265358979323846 / 180.0);
+    if (!(half > 0.f && half < SSK_HALF_PI))
+        throw std::invalid_argument(fmt("Invalid sun aperture angle: %f, must be in ]0, 90[ degrees!", p.sun_aperture_deg));
+    int want = spectral ? 11 : 3;
+    if (p.n_albedo != 1 && p.n_albedo != want)
+        throw std::invalid_argument("albedo must hold 1 value or one value per channel (3 RGB / 11 spectral)");
+    for (int i = 0; i < p.n_albedo; ++i)
+        if (!(p.albedo[i] >= 0.f && p.albedo[i] <= 1.f))
+            throw std::invalid_argument(fmt("Albedo values must be in [0, 1], got: %f", p.albedo[i]));
+    if (!p.use_record) {
+        float n2 = p.sun_direction[0] * p.sun_direction[0] + p.sun_direction[1] * p.sun_direction[1] +
+                   p.sun_direction[2] * p.sun_direction[2];
+        if (!(n2 > 0.f) || !std::isfinite(n2)) throw std::invalid_argument("sun_direction must be a non-zero vector");
+    }
+}
+
+static void mat3_from_4x4(const float *m16, float *m9) {
+    for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) m9[r * 3 + c] = m16[r * 4 + c];
+}
+static bool invert3(const float *m, float *inv) {
+    double a = m[0], b = m[1], c = m[2], d = m[3], e = m[4], f = m[5], g = m[6], h = m[7], i = m[8];
+    double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    if (det == 0.0 || !std::isfinite(det)) return false;
+    double r = 1.0 / det;
+    double o[9] = { (e * i - f * h) * r, (c * h - b * i) * r, (b * f - c * e) * r,
+                    (f * g - d * i) * r, (a * i - c * g) * r, (c * d - a * f) * r,
+                    (d * h - e * g) * r, (b * g - a * h) * r, (a * e - b * d) * r };
+    for (int k = 0; k < 9; ++k) inv[k] = (float) o[k];
+    return true;
+}
+
+/// The constructor (from_constructor = true, sunsky.cpp:162-218) or parameters_changed()
+/// (false, sunsky.cpp:242-285) applied to `p`.
+void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
+    validate_params(p, E.spectral);
+    if (!from_constructor && (p.use_record != 0) != E.active_record)
+        throw std::invalid_argument("an emitter keeps the sun parametrisation (direction or date/location) it was created with");
+    E.params = p;
+    E.active_record = p.use_record != 0;
+    EmitterBlock &B = E.block;
+    const int C = E.n_channels;
+    memset(&B, 0, offsetof(EmitterBlock, sun_rad));
+    B.spectral = E.spectral ? 1 : 0;
+
+    // --- transforms
+    mat3_from_4x4(p.to_world, B.to_world);
+    if (!invert3(B.to_world, B.to_local)) throw std::invalid_argument("to_world is not invertible");
+
+    // --- albedo per channel (extract_albedo, sunsky.cpp:956-978)
+    float albedo[11];
+    for (int c = 0; c < C; ++c) albedo[c] = p.n_albedo == 1 ? p.albedo[0] : p.albedo[c];
+
+    // --- sun direction (init_from_props :912-946, ctor :174-179, parameters_changed :257-267)
+    E.half_aperture = 0.5f * p.sun_aperture_deg * (float) (3.14159265358979323846 / 180.0);
+    Vec3 local_sun;
+    if (E.active_record) {
+        DateTime dt = { p.year, p.month, p.day, p.hour, p.minute, p.second };
+        Location loc = { p.latitude, p.longitude, p.timezone };
+        Vec3 coords = sun_coordinates(dt, loc);
+        E.sun_below_horizon = coords.z < 0.f;
+        E.sun_dir_world = xform(B.to_world, coords);
+        local_sun = from_constructor ? xform(B.to_local, E.sun_dir_world) : coords;
+    } else {
+        Vec3 v = { p.sun_direction[0], p.sun_direction[1], p.sun_direction[2] };
+        if (!(p.flags & SSK_FLAG_SUN_DIR_NORMALIZED) && from_constructor) {
+            // dr::normalize on a scalar vector; the reference's SSE rsqrt path is CPU specific, so a
+            // caller that needs bit parity passes a unit vector and SSK_FLAG_SUN_DIR_NORMALIZED
+            float inv = 1.f / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
+            v = { v.x * inv, v.y * inv, v.z * inv };
+        }
+        E.sun_dir_world = v;
+        local_sun = xform(B.to_local, v);
+        E.sun_below_horizon = false;
+    }
+    E.sun_angles[0] = datan2(local_sun.y, local_sun.x);          // from_spherical (sunsky.h:83-89)
+    E.sun_angles[1] = unit_angle_z(local_sun);
+    Vec3 fs, ft;
+    coordinate_system(local_sun, fs, ft);
+    B.sun_n[0] = local_sun.x; B.sun_n[1] = local_sun.y; B.sun_n[2] = local_sun.z;
+    B.sun_s[0] = fs.x; B.sun_s[1] = fs.y; B.sun_s[2] = fs.z;
+    B.sun_t[0] = ft.x; B.sun_t[1] = ft.y; B.sun_t[2] = ft.z;
+    B.sun_phi_shift = E.sun_angles[0] - SSK_HALF_PI;
+    const float eta = SSK_HALF_PI - E.sun_angles[1];
+
+    // --- aperture-dependent constants
+    B.cos_cutoff = dcos(E.half_aperture);
+    B.one_minus_cos_cutoff = 1.f - B.cos_cutoff;
+    float s = dsin(E.half_aperture);
+    B.ar2 = 1.f / (s * s);
+    // get_area_ratio (sunsky.h:98-101): fp64 numerator 1 - dr::cos(deg_to_rad(0.5358 / 2.0)) (value of
+    // Dr.Jit's fp64 cosine polynomial, a compile-time constant of the reference), fp32 denominator
+    const double area_num = 0x1.6eca9ffb60000p-17;
+    E.area_ratio = B.area_ratio = (float) (area_num / (double) (1.f - dcos(E.half_aperture)));
+    B.sun_pdf_const = fdiv(SSK_INV_TWO_PI, 1.f - B.cos_cutoff);
+    B.sky_scale = p.sky_scale; B.sun_scale = p.sun_scale;
+    B.bs_center[0] = E.bs_center[0]; B.bs_center[1] = E.bs_center[1]; B.bs_center[2] = E.bs_center[2];
+    B.bs_radius = E.bs_radius;
+
+    // --- sky coefficients and mean radiance (sunsky.cpp:185-186 / 270-271)
+    radiance_params(E.data.sky_params, albedo, C, p.turbidity, eta, E.sky_params);
+    radiance_params(E.data.sky_rad, albedo, C, p.turbidity, eta, E.sky_radiance);
+    for (int c = 0; c < C; ++c) {
+        for (int k = 0; k < kSkyParams; ++k) B.sky_params[k][c] = E.sky_params[c * 9 + k];
+        B.sky_rad[c] = E.sky_radiance[c];
+    }
+    // --- sun radiance table and limb darkening (:191-195 / 274)
+    E.sun_radiance.resize(E.data.sun_rad.size() / 10);
+    sun_params(E.data.sun_rad, p.turbidity, E.sun_radiance.data());
+    memset(B.sun_rad, 0, sizeof(B.sun_rad));
+    memcpy(B.sun_rad, E.sun_radiance.data(), E.sun_radiance.size() * sizeof(float));
+    if (E.spectral)
+        for (int c = 0; c < 11; ++c)
+            for (int j = 0; j < kLd; ++j) B.sun_ld[j][c] = E.data.sun_ld[c * kLd + j];
+
+    // --- TGMM mixture, CDF (JIT DiscreteDistribution: fp32 inclusive prefix sum, 1/sum), and the
+    //     per-component constants the JIT folds at trace time (sunsky.cpp:201-204, 668-675, 742-755)
+    tgmm_distribution(E.data.tgmm, p.turbidity, eta, E.gaussians);
+    float acc = 0.f;
+    bool any_pos = false;
+    for (int i = 0; i < kGauss; ++i) {
+        E.pmf[i] = E.gaussians[i * 5 + 4];
+        any_pos |= E.pmf[i] > 0.f;
+        acc = acc + E.pmf[i];
+        E.cdf[i] = acc;
+    }
+    if (!any_pos) throw std::runtime_error("DiscreteDistribution: no probability mass found!");
+    E.cdf_sum = E.cdf[kGauss - 1];
+    E.cdf_norm = 1.f / E.cdf_sum;
+    B.cdf_sum = E.cdf_sum;
+    for (int i = 0; i < kGauss; ++i) {
+        float mu_p = E.gaussians[i * 5 + 0], mu_t = E.gaussians[i * 5 + 1],
+              sg_p = E.gaussians[i * 5 + 2], sg_t = E.gaussians[i * 5 + 3];
+        B.g_mu_phi[i] = mu_p; B.g_mu_theta[i] = mu_t; B.g_sigma_phi[i] = sg_p; B.g_sigma_theta[i] = sg_t;
+        B.g_weight[i] = E.pmf[i];
+        B.g_cdf_a_phi[i] = gaussian_cdf(mu_p, sg_p, 0.f);
+        B.g_cdf_a_theta[i] = gaussian_cdf(mu_t, sg_t, 0.f);
+        B.g_cdf_b_phi[i] = gaussian_cdf(mu_p, sg_p, SSK_TWO_PI);
+        B.g_cdf_b_theta[i] = gaussian_cdf(mu_t, sg_t, SSK_HALF_PI);
+        B.g_volume[i] = (B.g_cdf_b_phi[i] - B.g_cdf_a_phi[i]) * (B.g_cdf_b_theta[i] - B.g_cdf_a_theta[i]) * (sg_p * sg_t);
+        B.g_cdf[i] = E.cdf[i];
+        B.g_pmf_n[i] = E.pmf[i] * E.cdf_norm;
+        B.g_cdf_prev_n[i] = i > 0 ? E.cdf[i - 1] * E.cdf_norm : 0.f;
+    }
+
+    // --- sky / sun sampling weight and wavelength distribution (:207-209 / 282-284)
+    estimate_sky_sun_ratio(E);
+    B.sky_w = E.sky_w;
+}
+
+/// estimate_sky_sun_ratio, array branch (sunsky.cpp:772-886): 200x200 Gauss-Legendre quadrature of the
+/// sky over the hemisphere and of the sun over its cone, luminance ratio, and (spectral) the
+/// per-bin mean radiance that drives wavelength sampling.
+void estimate_sky_sun_ratio(HostEmitter &E) {
+    const EmitterBlock &B = E.block;
+    const int C = E.n_channels;
+    static std::vector<float> gx, gw;
+    if (gx.empty()) gauss_legendre(200, gx, gw);
+    const int N = 200;
+    std::vector<float> buf((size_t) C * N * N);
+    float sky_rad[11], sun_rad[11];
+    Vec3 n = { B.sun_n[0], B.sun_n[1], B.sun_n[2] };
+
+    {   // sky over the hemisphere: [-1,1]^2 -> [0,2pi] x [0,1]
+        const float J = 0.5f * SSK_PI;
+        for (int iy = 0; iy < N; ++iy) {
+            float cos_theta = 0.5f * (gx[iy] + 1.f);
+            float sin_theta = safe_sqrt(1.f - cos_theta * cos_theta);
+            for (int ix = 0; ix < N; ++ix) {
+                float phi = SSK_PI * (gx[ix] + 1.f), sp, cp;
+                dsincos(phi, sp, cp);
+                Vec3 wo = { sin_theta * cp, sin_theta * sp, cos_theta };
+                RayTerms r = ray_terms(cos_theta, unit_angle(n, wo));
+                for (int c = 0; c < C; ++c)
+                    buf[(size_t) c * N * N + iy * N + ix] = render_sky(B, c, r) * gw[ix] * gw[iy];
+            }
+        }
+        for (int c = 0; c < C; ++c) sky_rad[c] = llvm_block_sum(&buf[(size_t) c * N * N], N * N) * J;
+    }
+    {   // sun over its cone: [-1,1]^2 -> [0,2pi] x [cos(half aperture), 1]
+        const float cutoff = B.cos_cutoff;
+        const float J = 0.5f * SSK_PI * (1.f - cutoff);
+        for (int iy = 0; iy < N; ++iy) {
+            float cos_gamma = 0.5f * ((1.f - cutoff) * gx[iy] + (1.f + cutoff));
+            float sin_gamma = safe_sqrt(1.f - cos_gamma * cos_gamma);
+            for (int ix = 0; ix < N; ++ix) {
+                float phi = SSK_PI * (gx[ix] + 1.f), sp, cp;
+                dsincos(phi, sp, cp);
+                Vec3 v = { sin_gamma * cp, sin_gamma * sp, cos_gamma };
+                float gamma = unit_angle_z(v);
+                Vec3 wo = { fmaf(B.sun_n[0], v.z, fmaf(B.sun_t[0], v.y, B.sun_s[0] * v.x)),
+                            fmaf(B.sun_n[1], v.z, fmaf(B.sun_t[1], v.y, B.sun_s[1] * v.x)),
+                            fmaf(B.sun_n[2], v.z, fmaf(B.sun_t[2], v.y, B.sun_s[2] * v.x)) };
+                float cos_theta = wo.z;
+                bool active = cos_theta >= 0.f;
+                float xk[4], cj[6];
+                SunSeg s = { 0, 0.f };
+                if (active) {
+                    s = sun_segment(cos_theta);
+                    powers4(s.x, xk);
+                    powers6(cos_psi(B, gamma), cj);
+                }
+                for (int c = 0; c < C; ++c) {
+                    float v0 = 0.f;
+                    if (active) {
+                        if (E.spectral) {
+                            v0 = render_sun_spec(B.sun_rad, c, s, xk) * gw[ix] * gw[iy];
+                            v0 *= sun_ld(B, c, c, 0.f, cj);
+                        } else {
+                            v0 = render_sun_rgb(B.sun_rad, c, s, xk, cj) * gw[ix] * gw[iy];
+                        }
+                    }
+                    buf[(size_t) c * N * N + iy * N + ix] = v0;
+                }
+            }
+        }
+        for (int c = 0; c < C; ++c) sun_rad[c] = llvm_block_sum(&buf[(size_t) c * N * N], N * N) * J;
+    }
+
+    float sky_lum = B.sky_scale, sun_lum = B.sun_scale;
+    if (!E.spectral) {
+        // luminance(Color3f) (include/mitsuba/core/spectrum.h:431-434)
+        float ls = sky_rad[0] * 0.212671f + sky_rad[1] * 0.715160f + sky_rad[2] * 0.072169f;
+        float lu = sun_rad[0] * 0.212671f + sun_rad[1] * 0.715160f + sun_rad[2] * 0.072169f;
+        sky_lum = sky_lum * ls;
+        sun_lum = (float) ((double) sun_lum * ((double) (lu * B.area_ratio) * 467.069280386));
+    } else {
+        // luminance(spectrum, wavelengths) = mean(cie1931_y(lambda) * value) (spectrum.h:415-429, 271-295).
+        // The 11 bins sit on the 5 nm CIE grid, so the table lookup is exact: CIE 1931 2-degree y-bar at
+        // 360, 400, ..., 720 nm; 320 nm lies outside [360, 830] and contributes 0.
+        const float cie_y[11] = { 0.f, 0.000003917f, 0.000396f, 0.023f, 0.13902f, 0.71f, 0.995f, 0.631f,
+                                  0.175f, 0.017f, 0.001047f };
+        auto lum = [&](const float *v) {
+            float acc = cie_y[0] * v[0];
+            for (int c = 1; c < 11; ++c) acc += cie_y[c] * v[c];
+            return acc * (1.f / 11.f);
+        };
+        sky_lum = sky_lum * lum(sky_rad);
+        sun_lum = sun_lum * (lum(sun_rad) * B.area_ratio);
+    }
+    float res = fdiv(sky_lum, sky_lum + sun_lum);
+    E.sky_w = std::isnan(res) ? 0.f : res;
+
+    if (E.spectral) {
+        // ContinuousDistribution(range = [360, 720], 10 bins) (distr_1d.h:283-...): scalar cdf build
+        bool all_zero = true;
+        for (int i = 0; i < 10; ++i) {
+            E.spectral_pdf[i] = sun_rad[i + 1] + sky_rad[i + 1];
+            all_zero &= E.spectral_pdf[i] == 0.f;
+        }
+        if (all_zero) for (int i = 0; i < 10; ++i) E.spectral_pdf[i] += 1.f;
+        double interval = (720.0 - 360.0) / 9.0, integral = 0.0;
+        for (int i = 0; i < 9; ++i) {
+            double y0 = E.spectral_pdf[i], y1 = E.spectral_pdf[i + 1];
+            integral += 0.5 * interval * (y0 + y1);
+            E.spectral_cdf[i] = (float) integral;
+        }
+        E.spectral_cdf[9] = 0.f;
+        E.spectral_integral = (float) integral;
+        E.spectral_norm = (float) (1.0 / integral);
+    } else {
+        memset(E.spectral_pdf, 0, sizeof(E.spectral_pdf));
+        memset(E.spectral_cdf, 0, sizeof(E.spectral_cdf));
+    }
+}
+
+} // namespace ssk

@@ -1,0 +1,233 @@
+// sm_100a kernels of the sunsky hot path. One kernel per Emitter entry point, each a single fused
+// pass: planar fp32 in, planar fp32 out, 128-bit loads/stores (4 consecutive rays per thread), the
+// per-emitter coefficient block staged once per CTA into shared memory, persistent grid sized to a
+// multiple of the SM count. The work is FP32-issue bound (hundreds of flops per 24-44 bytes), so
+// there is no TMA / tensor-core path here by design.
+#pragma once
+#include "ssk_model.cuh"
+#include <cuda_runtime.h>
+
+namespace ssk {
+
+constexpr int kThreads = 256;
+constexpr int kVec = 4;
+
+/// Stage the hot part of the emitter block into shared memory (coalesced 4-byte copies).
+__device__ __forceinline__ void stage_block(EmitterBlock *dst, const EmitterBlock *src) {
+    const float *s = reinterpret_cast<const float *>(src);
+    float *d = reinterpret_cast<float *>(dst);
+    for (int i = threadIdx.x; i < kHotFloats; i += blockDim.x) d[i] = s[i];
+    __syncthreads();
+}
+
+template <bool Vec> __device__ __forceinline__ void load4(const float *p, size_t i, size_t n, float v[4]) {
+    if (Vec && i + 3 < n) {
+        float4 t = __ldg(reinterpret_cast<const float4 *>(p + i));
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = (i + k < n) ? __ldg(p + i + k) : 0.f;
+    }
+}
+template <bool Vec> __device__ __forceinline__ void store4(float *p, size_t i, size_t n, const float v[4]) {
+    if (Vec && i + 3 < n) {
+        __stcs(reinterpret_cast<float4 *>(p + i), make_float4(v[0], v[1], v[2], v[3]));
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) if (i + k < n) p[i + k] = v[k];
+    }
+}
+
+struct Planes3 { const float *x, *y, *z; };
+struct Planes4 { const float *a, *b, *c, *d; };
+struct OutPlanes3 { float *x, *y, *z; };
+struct OutPlanes4 { float *a, *b, *c, *d; };
+
+/// eval / eval_direction, RGB. dir_sign = +1: input is si.wi (the model negates it);
+/// dir_sign = -1: input is ds.d (eval_direction passes wi = -d).
+template <bool Vec>
+__global__ void __launch_bounds__(kThreads)
+eval_rgb_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out, size_t n, float dir_sign) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
+    stage_block(&P, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+        float x[4], y[4], z[4], r[4], g[4], b[4];
+        load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            Vec3 wi = { dir_sign * x[k], dir_sign * y[k], dir_sign * z[k] };
+            float o[3];
+            eval_rgb(P, sun_rad, wi, true, o);
+            r[k] = o[0]; g[k] = o[1]; b[k] = o[2];
+        }
+        store4<Vec>(out.x, i, n, r); store4<Vec>(out.y, i, n, g); store4<Vec>(out.z, i, n, b);
+    }
+}
+
+/// eval / eval_direction, spectral (4 wavelengths per ray)
+template <bool Vec>
+__global__ void __launch_bounds__(kThreads)
+eval_spec_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav, OutPlanes4 out, size_t n, float dir_sign) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
+    stage_block(&P, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+        float x[4], y[4], z[4], w0[4], w1[4], w2[4], w3[4], o0[4], o1[4], o2[4], o3[4];
+        load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
+        load4<Vec>(wav.a, i, n, w0); load4<Vec>(wav.b, i, n, w1); load4<Vec>(wav.c, i, n, w2); load4<Vec>(wav.d, i, n, w3);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            Vec3 wi = { dir_sign * x[k], dir_sign * y[k], dir_sign * z[k] };
+            float wl[4] = { w0[k], w1[k], w2[k], w3[k] }, o[4];
+            eval_spec(P, sun_rad, wi, wl, true, o);
+            o0[k] = o[0]; o1[k] = o[1]; o2[k] = o[2]; o3[k] = o[3];
+        }
+        store4<Vec>(out.a, i, n, o0); store4<Vec>(out.b, i, n, o1); store4<Vec>(out.c, i, n, o2); store4<Vec>(out.d, i, n, o3);
+    }
+}
+
+/// pdf_direction
+template <bool Vec>
+__global__ void __launch_bounds__(kThreads)
+pdf_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, float *__restrict__ pdf, size_t n) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
+    stage_block(&P, blk);
+    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+        float x[4], y[4], z[4], o[4];
+        load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            Vec3 d = { x[k], y[k], z[k] };
+            o[k] = pdf_direction(P, d);
+        }
+        store4<Vec>(pdf, i, n, o);
+    }
+}
+
+struct SampleArgs {
+    const float *u0, *u1;
+    const float *px, *py, *pz;          // it.p, nullable
+    const float *w0, *w1, *w2, *w3;     // it.wavelengths (spectral)
+    float *dx, *dy, *dz, *pdf;
+    float *q0, *q1, *q2, *q3;           // weight planes
+    float *ox, *oy, *oz, *dist;         // ds.p / ds.dist, nullable
+};
+
+/// sample_direction, fused: select technique -> sample -> pdf -> eval -> weight (sunsky.cpp:399-441)
+template <bool Vec, bool Spectral>
+__global__ void __launch_bounds__(kThreads)
+sample_kernel(const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
+    stage_block(&P, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+        float u0[4], u1[4], wl[4][4], dx[4], dy[4], dz[4], pdf[4], q[4][4];
+        float px[4] = { 0, 0, 0, 0 }, py[4] = { 0, 0, 0, 0 }, pz[4] = { 0, 0, 0, 0 };
+        float ox[4], oy[4], oz[4], dist[4];
+        load4<Vec>(a.u0, i, n, u0); load4<Vec>(a.u1, i, n, u1);
+        if (Spectral) {
+            load4<Vec>(a.w0, i, n, wl[0]); load4<Vec>(a.w1, i, n, wl[1]);
+            load4<Vec>(a.w2, i, n, wl[2]); load4<Vec>(a.w3, i, n, wl[3]);
+        }
+        if (a.px) { load4<Vec>(a.px, i, n, px); load4<Vec>(a.py, i, n, py); load4<Vec>(a.pz, i, n, pz); }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            DirSample s = sample_dir(P, u0[k], u1[k]);
+            dx[k] = s.d_world.x; dy[k] = s.d_world.y; dz[k] = s.d_world.z; pdf[k] = s.pdf;
+            // eval(si) with si.wi = -d (sunsky.cpp:430-438)
+            Vec3 wi = { -s.d_world.x, -s.d_world.y, -s.d_world.z };
+            float e[4];
+            if (Spectral) {
+                float w4[4] = { wl[0][k], wl[1][k], wl[2][k], wl[3][k] };
+                eval_spec(P, sun_rad, wi, w4, s.active, e);
+            } else {
+                eval_rgb(P, sun_rad, wi, s.active, e);
+                e[3] = 0.f;
+            }
+#pragma unroll
+            for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
+                float w = fdiv(e[c], s.pdf);
+                q[c][k] = (fabsf(w) < INFINITY) ? w : 0.f;         // res &= isfinite(res)
+            }
+            // bounding-sphere bookkeeping (sunsky.cpp:415-421)
+            Vec3 rel = { px[k] - P.bs_center[0], py[k] - P.bs_center[1], pz[k] - P.bs_center[2] };
+            float radius = fmaxf(P.bs_radius, sqrtf(sqnorm3(rel)));
+            float dd = 2.f * radius;
+            dist[k] = dd;
+            ox[k] = fmaf(s.d_world.x, dd, px[k]); oy[k] = fmaf(s.d_world.y, dd, py[k]); oz[k] = fmaf(s.d_world.z, dd, pz[k]);
+        }
+        store4<Vec>(a.dx, i, n, dx); store4<Vec>(a.dy, i, n, dy); store4<Vec>(a.dz, i, n, dz);
+        store4<Vec>(a.pdf, i, n, pdf);
+        store4<Vec>(a.q0, i, n, q[0]); store4<Vec>(a.q1, i, n, q[1]); store4<Vec>(a.q2, i, n, q[2]);
+        if (Spectral) store4<Vec>(a.q3, i, n, q[3]);
+        if (a.ox) { store4<Vec>(a.ox, i, n, ox); store4<Vec>(a.oy, i, n, oy); store4<Vec>(a.oz, i, n, oz); }
+        if (a.dist) store4<Vec>(a.dist, i, n, dist);
+    }
+}
+
+/// Direction of equirectangular pixel (x, y): phi = 2*pi*(x+.5)/W, theta = pi*(y+.5)/H
+SSK_HD Vec3 envmap_dir(int x, int y, int width, int height) {
+    float phi = fdiv(SSK_TWO_PI * ((float) x + 0.5f), (float) width),
+          theta = fdiv(SSK_PI * ((float) y + 0.5f), (float) height);
+    return sphdir(theta, phi);
+}
+
+/// Equirect env maps, one emitter block per map (blockIdx.y). Write-only: no direction buffer.
+template <bool Spectral>
+__global__ void __launch_bounds__(kThreads)
+envmap_kernel(const EmitterBlock *const *__restrict__ blks, const float *__restrict__ wav4, float *__restrict__ out,
+              int width, int height) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
+    const EmitterBlock *blk = blks[blockIdx.y];
+    stage_block(&P, blk);
+    const float *sun_rad = blk->sun_rad;
+    constexpr int C = Spectral ? 4 : 3;
+    const size_t npix = (size_t) width * height;
+    float *base = out + (size_t) blockIdx.y * C * npix;
+    float wl[4] = { 0, 0, 0, 0 };
+    if (Spectral) { wl[0] = wav4[blockIdx.y * 4 + 0]; wl[1] = wav4[blockIdx.y * 4 + 1]; wl[2] = wav4[blockIdx.y * 4 + 2]; wl[3] = wav4[blockIdx.y * 4 + 3]; }
+    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < npix; i += stride) {
+        float o[4][4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            size_t pix = i + k < npix ? i + k : npix - 1;
+            int py = (int) (pix / (size_t) width), px = (int) (pix - (size_t) py * width);
+            Vec3 d = envmap_dir(px, py, width, height);
+            Vec3 wi = { -d.x, -d.y, -d.z };
+            float e[4] = { 0, 0, 0, 0 };
+            if (Spectral) eval_spec(P, sun_rad, wi, wl, true, e);
+            else eval_rgb(P, sun_rad, wi, true, e);
+#pragma unroll
+            for (int c = 0; c < C; ++c) o[c][k] = e[c];
+        }
+        const bool vec = (npix % 4) == 0;
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            if (vec) store4<true>(base + (size_t) c * npix, i, npix, o[c]);
+            else store4<false>(base + (size_t) c * npix, i, npix, o[c]);
+        }
+    }
+}
+
+/// Directions of an env map (for parity checks of the pixel -> direction convention)
+__global__ void envmap_dirs_kernel(float *dx, float *dy, float *dz, int width, int height) {
+    size_t npix = (size_t) width * height;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += (size_t) gridDim.x * blockDim.x) {
+        int py = (int) (i / (size_t) width), px = (int) (i - (size_t) py * width);
+        Vec3 d = envmap_dir(px, py, width, height);
+        dx[i] = d.x; dy[i] = d.y; dz[i] = d.z;
+    }
+}
+
+} // namespace ssk

@@ -1,0 +1,345 @@
+"""Host-side mirror of the reference's `sunsky` emitter plugin on top of the C ABI
+(include/sunsky_b200.h -> libsunsky_b200.so).
+
+`SunskyEmitter` keeps the plugin's surface (reference: src/emitters/sunsky.cpp):
+properties `turbidity, albedo, sun_direction | latitude..second, sun_scale, sky_scale, sun_aperture,
+to_world` (:19-104), `eval` (:303), `sample_direction` (:399), `pdf_direction` (:443),
+`eval_direction` (:453), `traverse`/`parameters_changed` (:220-285, exposed as `traverse()` /
+`update()`), `set_scene` (:287) and `to_string` (:502).
+
+Array conventions: planar float32, shape (components, n). numpy arrays go through the `*_host`
+entry points (H2D + kernel + D2H inside the call); torch CUDA tensors go through the `*_device`
+entry points on torch's current stream and return torch tensors. Nothing here computes radiance on
+the CPU: without the built library and a CUDA device the compute calls raise.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _capi
+from ._capi import (MODE_RGB, MODE_SPECTRAL, FLAG_SUN_DIR_NORMALIZED, ARITH_EXACT, ARITH_FAST, DATASET_DIR,
+                    Params, State)
+
+__all__ = ["SunskyEmitter", "SunskyError", "sun_coordinates", "array_from_file", "array_to_file",
+           "launch_count", "MODE_RGB", "MODE_SPECTRAL"]
+
+
+class SunskyError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"[ssk {code}] {msg}")
+        self.code = code
+
+
+def _check(rc):
+    if rc != 0:
+        raise SunskyError(rc, _capi.lib().ssk_last_error().decode())
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _planes_np(a, k, name):
+    a = np.asarray(a, dtype=np.float32)
+    if a.ndim != 2 or a.shape[0] != k:
+        raise ValueError(f"{name}: expected shape ({k}, n), got {a.shape}")
+    return [np.ascontiguousarray(a[i]) for i in range(k)]
+
+
+def _pp(planes):
+    arr = (_capi.FP * len(planes))()
+    for i, p in enumerate(planes):
+        arr[i] = p.ctypes.data_as(_capi.FP)
+    return arr
+
+
+def _pp_t(t, k, name):
+    import torch
+    if t.dtype != torch.float32 or t.dim() != 2 or t.shape[0] != k:
+        raise ValueError(f"{name}: expected float32 tensor of shape ({k}, n), got {tuple(t.shape)} {t.dtype}")
+    if t.stride(1) != 1:
+        t = t.contiguous()
+    arr = (_capi.FP * k)()
+    for i in range(k):
+        arr[i] = C.cast(t[i].data_ptr(), _capi.FP)
+    return arr, t
+
+
+_PARAM_KEYS = ("turbidity", "albedo", "sun_direction", "latitude", "longitude", "timezone", "year", "month",
+               "day", "hour", "minute", "second", "sun_scale", "sky_scale", "sun_aperture", "to_world")
+
+
+class SunskyEmitter:
+    """Sun and sky dome background emitter (Hosek-Wilkie sky + sun, TGMM importance sampling)."""
+
+    def __init__(self, spectral=False, device=0, dataset_dir=None, sun_direction_normalized=False, **props):
+        unknown = set(props) - set(_PARAM_KEYS)
+        if unknown:
+            raise TypeError(f"unknown sunsky properties: {sorted(unknown)}")
+        record_keys = {"latitude", "longitude", "timezone", "year", "month", "day", "hour", "minute", "second"}
+        if "sun_direction" in props and record_keys & set(props):
+            # same rule as init_from_props (sunsky.cpp:912-920)
+            raise SunskyError(_capi.SSK_ERR_INVALID,
+                              "Both the 'sun_direction' and parameters for time/location were provided, "
+                              "both information cannot be given at the same time!")
+        self._L = _capi.lib()
+        self.spectral = bool(spectral)
+        self.device = device
+        self._normalized = bool(sun_direction_normalized)
+        self._props = {}
+        p = Params()
+        self._L.ssk_params_default(C.byref(p))
+        self._fill(p, props, creating=True)
+        self._params = p
+        ctx = _capi.CTX()
+        _check(self._L.ssk_create(C.byref(p), (dataset_dir or DATASET_DIR).encode(), int(device),
+                                  MODE_SPECTRAL if spectral else MODE_RGB, C.byref(ctx)))
+        self._ctx = ctx
+        self.channels = self._L.ssk_channels(ctx)
+
+    # -- property surface ---------------------------------------------------------------------
+    def _fill(self, p, props, creating):
+        for k, v in props.items():
+            if k == "albedo":
+                a = np.atleast_1d(np.asarray(v, dtype=np.float32)).ravel()
+                if a.size not in (1, 3, 11):
+                    raise SunskyError(_capi.SSK_ERR_INVALID, "albedo needs 1, 3 (RGB) or 11 (spectral) values")
+                p.n_albedo = a.size
+                for i, x in enumerate(a):
+                    p.albedo[i] = float(x)
+            elif k == "sun_direction":
+                p.use_record = 0
+                for i in range(3):
+                    p.sun_direction[i] = float(v[i])
+            elif k == "sun_aperture":
+                p.sun_aperture_deg = float(v)
+            elif k == "to_world":
+                m = np.asarray(v, dtype=np.float32).reshape(16)
+                for i in range(16):
+                    p.to_world[i] = float(m[i])
+            elif k in ("year", "month", "day"):
+                setattr(p, k, int(v))
+            else:
+                setattr(p, k, float(v))
+        if creating and "sun_direction" not in props:
+            p.use_record = 1
+        p.flags = FLAG_SUN_DIR_NORMALIZED if self._normalized else 0
+        self._props.update(props)
+
+    def traverse(self):
+        """Names and current values of the parameters `traverse()` exposes (sunsky.cpp:220-240)."""
+        p = self._params
+        out = {"turbidity": p.turbidity, "sky_scale": p.sky_scale, "sun_scale": p.sun_scale,
+               "albedo": [p.albedo[i] for i in range(p.n_albedo)]}
+        if p.use_record:
+            out.update(latitude=p.latitude, longitude=p.longitude, timezone=p.timezone, year=p.year, day=p.day,
+                       month=p.month, hour=p.hour, minute=p.minute, second=p.second)
+        else:
+            out["sun_direction"] = [p.sun_direction[i] for i in range(3)]
+        out["to_world"] = np.array(p.to_world, dtype=np.float32).reshape(4, 4)
+        return out
+
+    def update(self, **props):
+        """`params[...] = v; params.update()` -> parameters_changed() (sunsky.cpp:242-285)."""
+        unknown = set(props) - set(_PARAM_KEYS) | ({"sun_aperture"} & set(props))
+        if unknown:
+            raise TypeError(f"not a traversable sunsky parameter: {sorted(unknown)}")
+        p = Params.from_buffer_copy(self._params)
+        self._fill(p, props, creating=False)
+        _check(self._L.ssk_update(self._ctx, C.byref(p)))
+        self._params = p
+
+    parameters_changed = update
+
+    def set_scene(self, bbox_min=None, bbox_max=None):
+        a = None if bbox_min is None else np.ascontiguousarray(bbox_min, dtype=np.float32)
+        b = None if bbox_max is None else np.ascontiguousarray(bbox_max, dtype=np.float32)
+        _check(self._L.ssk_set_scene(self._ctx, None if a is None else a.ctypes.data_as(_capi.FP),
+                                     None if b is None else b.ctypes.data_as(_capi.FP)))
+
+    def state(self):
+        s = State()
+        _check(self._L.ssk_get_state(self._ctx, C.byref(s)))
+        return s
+
+    def to_string(self):
+        buf = C.create_string_buffer(2048)
+        _check(self._L.ssk_to_string(self._ctx, buf, 2048))
+        return buf.value.decode()
+
+    __repr__ = to_string
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._L.ssk_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- Emitter interface --------------------------------------------------------------------
+    def _stream(self):
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def _eval_impl(self, dirs, wavelengths, direction):
+        Cn = self.channels
+        if _is_torch(dirs):
+            import torch
+            d_pp, dirs = _pp_t(dirs, 3, "directions")
+            n = dirs.shape[1]
+            w_pp = None
+            if self.spectral:
+                if wavelengths is None:
+                    raise ValueError("spectral mode needs wavelengths of shape (4, n)")
+                w_pp, wavelengths = _pp_t(wavelengths, 4, "wavelengths")
+            out = torch.empty((Cn, n), dtype=torch.float32, device=dirs.device)
+            o_pp, _ = _pp_t(out, Cn, "out")
+            fn = self._L.ssk_eval_direction_device if direction else self._L.ssk_eval_device
+            _check(fn(self._ctx, d_pp, w_pp, n, o_pp, self._stream()))
+            return out
+        planes = _planes_np(dirs, 3, "directions")
+        n = planes[0].size
+        wp = None
+        if self.spectral:
+            if wavelengths is None:
+                raise ValueError("spectral mode needs wavelengths of shape (4, n)")
+            wpl = _planes_np(wavelengths, 4, "wavelengths")
+            wp = _pp(wpl)
+        out = np.empty((Cn, n), dtype=np.float32)
+        fn = self._L.ssk_eval_direction_host if direction else self._L.ssk_eval_host
+        _check(fn(self._ctx, _pp(planes), wp, n, _pp([out[c] for c in range(Cn)])))
+        return out
+
+    def eval(self, wi, wavelengths=None):
+        """Radiance arriving along -wi. wi: (3, n); wavelengths: (4, n) in nm (spectral). -> (C, n)"""
+        return self._eval_impl(wi, wavelengths, False)
+
+    def eval_direction(self, d, wavelengths=None):
+        """eval() for a direction sample: wi = -d."""
+        return self._eval_impl(d, wavelengths, True)
+
+    def pdf_direction(self, d):
+        """Solid-angle density of sample_direction() at world direction d: (3, n) -> (n,)"""
+        if _is_torch(d):
+            import torch
+            d_pp, d = _pp_t(d, 3, "d")
+            n = d.shape[1]
+            out = torch.empty(n, dtype=torch.float32, device=d.device)
+            _check(self._L.ssk_pdf_direction_device(self._ctx, d_pp, n, C.cast(out.data_ptr(), _capi.FP), self._stream()))
+            return out
+        planes = _planes_np(d, 3, "d")
+        n = planes[0].size
+        out = np.empty(n, dtype=np.float32)
+        _check(self._L.ssk_pdf_direction_host(self._ctx, _pp(planes), n, out.ctypes.data_as(_capi.FP)))
+        return out
+
+    def sample_direction(self, u, it_p=None, wavelengths=None, want_p=False):
+        """Importance-sample a direction. u: (2, n) in [0,1)^2; it_p: (3, n) reference points or None;
+        wavelengths: (4, n) (spectral). Returns (d (3,n), pdf (n,), weight (C,n)) and, with want_p,
+        also (p (3,n), dist (n,)) = ds.p, ds.dist."""
+        Cn = self.channels
+        if _is_torch(u):
+            import torch
+            u_pp, u = _pp_t(u, 2, "u")
+            n = u.shape[1]
+            dev = u.device
+            p_pp = w_pp = None
+            if it_p is not None:
+                p_pp, it_p = _pp_t(it_p, 3, "it_p")
+            if self.spectral:
+                if wavelengths is None:
+                    raise ValueError("spectral mode needs wavelengths of shape (4, n)")
+                w_pp, wavelengths = _pp_t(wavelengths, 4, "wavelengths")
+            d = torch.empty((3, n), dtype=torch.float32, device=dev)
+            pdf = torch.empty(n, dtype=torch.float32, device=dev)
+            wgt = torch.empty((Cn, n), dtype=torch.float32, device=dev)
+            d_pp, _ = _pp_t(d, 3, "d"); q_pp, _ = _pp_t(wgt, Cn, "weight")
+            op_pp = dist_p = None
+            if want_p:
+                op = torch.empty((3, n), dtype=torch.float32, device=dev)
+                dist = torch.empty(n, dtype=torch.float32, device=dev)
+                op_pp, _ = _pp_t(op, 3, "p"); dist_p = C.cast(dist.data_ptr(), _capi.FP)
+            _check(self._L.ssk_sample_direction_device(self._ctx, u_pp, p_pp, w_pp, n, d_pp,
+                                                       C.cast(pdf.data_ptr(), _capi.FP), q_pp, op_pp, dist_p,
+                                                       self._stream()))
+            return (d, pdf, wgt, op, dist) if want_p else (d, pdf, wgt)
+        up = _planes_np(u, 2, "u")
+        n = up[0].size
+        pp = _pp(_planes_np(it_p, 3, "it_p")) if it_p is not None else None
+        wp = None
+        if self.spectral:
+            if wavelengths is None:
+                raise ValueError("spectral mode needs wavelengths of shape (4, n)")
+            wp = _pp(_planes_np(wavelengths, 4, "wavelengths"))
+        d = np.empty((3, n), np.float32); pdf = np.empty(n, np.float32); wgt = np.empty((Cn, n), np.float32)
+        op = np.empty((3, n), np.float32) if want_p else None
+        dist = np.empty(n, np.float32) if want_p else None
+        _check(self._L.ssk_sample_direction_host(
+            self._ctx, _pp(up), pp, wp, n, _pp([d[i] for i in range(3)]), pdf.ctypes.data_as(_capi.FP),
+            _pp([wgt[c] for c in range(Cn)]), _pp([op[i] for i in range(3)]) if want_p else None,
+            dist.ctypes.data_as(_capi.FP) if want_p else None))
+        return (d, pdf, wgt, op, dist) if want_p else (d, pdf, wgt)
+
+
+def envmaps(emitters, width, height, wavelengths4=None, out=None):
+    """Equirectangular radiance maps, one per emitter (all on one device, same mode), written by one
+    kernel launch straight into a torch CUDA tensor of shape (n_maps, C, height, width)."""
+    import torch
+    L = _capi.lib()
+    e0 = emitters[0]
+    Cn = e0.channels
+    n = len(emitters)
+    dev = torch.device("cuda", e0.device)
+    if out is None:
+        out = torch.empty((n, Cn, height, width), dtype=torch.float32, device=dev)
+    ctxs = (_capi.CTX * n)(*[e._ctx for e in emitters])
+    wl = None
+    if e0.spectral:
+        wl_np = np.ascontiguousarray(np.broadcast_to(np.asarray(wavelengths4, dtype=np.float32), (n, 4)))
+        wl = wl_np.ctypes.data_as(_capi.FP)
+    with torch.cuda.device(dev):
+        _check(L.ssk_envmap_device(ctxs, n, width, height, wl, C.cast(out.data_ptr(), _capi.FP),
+                                   C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return out
+
+
+def envmap_directions(emitter, width, height):
+    """Device-generated pixel directions of `envmaps` (3, height*width), for parity checks."""
+    import torch
+    L = _capi.lib()
+    d = torch.empty((3, height * width), dtype=torch.float32, device=torch.device("cuda", emitter.device))
+    pp, _ = _pp_t(d, 3, "d")
+    _check(L.ssk_envmap_directions_device(emitter._ctx, width, height, pp,
+                                          C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    return d
+
+
+def sun_coordinates(year, month, day, hour, minute, second, latitude, longitude, timezone):
+    out = np.empty(3, np.float32)
+    _check(_capi.lib().ssk_sun_coordinates(year, month, day, hour, minute, second, latitude, longitude, timezone,
+                                           out.ctypes.data_as(_capi.FP)))
+    return out
+
+
+def array_from_file(path, file_is_f64=True):
+    """`mi.array_from_file_d / _f` (src/render/python/sunsky_v.cpp:11-20): dataset -> (fp32 array, shape)"""
+    L = _capi.lib()
+    cnt = C.c_size_t(); nd = C.c_size_t(); shape = (C.c_size_t * 8)()
+    _check(L.ssk_array_from_file(path.encode(), int(file_is_f64), None, 0, C.byref(cnt), shape, C.byref(nd)))
+    out = np.empty(cnt.value, np.float32)
+    _check(L.ssk_array_from_file(path.encode(), int(file_is_f64), out.ctypes.data_as(_capi.FP), out.size,
+                                 C.byref(cnt), shape, C.byref(nd)))
+    return out.reshape([shape[i] for i in range(nd.value)])
+
+
+def array_to_file(path, data, as_f64=False):
+    a = np.ascontiguousarray(data, dtype=np.float32)
+    shape = (C.c_size_t * a.ndim)(*a.shape)
+    _check(_capi.lib().ssk_array_to_file(path.encode(), a.ctypes.data_as(_capi.FP), shape, a.ndim, int(as_f64)))
+
+
+def launch_count():
+    return int(_capi.lib().ssk_launch_count())
