@@ -127,7 +127,7 @@ inline void sun_params(const std::vector<float> &dataset, float turbidity, float
 /// by the bilinear (turbidity, elevation) factors. out: 20 x {mu_phi, mu_theta, sigma_phi, sigma_theta, w}
 inline void tgmm_distribution(const std::vector<float> &tables, float turbidity, float eta, float *out100) {
     float eta_deg = eta * (float) (180.0 / 3.14159265358979323846);       // dr::rad_to_deg
-    float eta_idx_f = fmaxf(fminf(fdiv(eta_deg - 2.f, 3.f), 29.f), 0.f),
+    float eta_idx_f = fmaxf(fminf((eta_deg - 2.f) * (1.f / 3.f), 29.f), 0.f)   /* Float / int -> mul by rcp */,
           t_idx_f = fmaxf(fminf(turbidity - 2.f, 8.f), 0.f);
     uint32_t eta_lo = (uint32_t) (int32_t) floorf(eta_idx_f), t_lo = (uint32_t) (int32_t) floorf(t_idx_f);
     uint32_t eta_hi = eta_lo + 1 < 29u ? eta_lo + 1 : 29u, t_hi = t_lo + 1 < 8u ? t_lo + 1 : 8u;
@@ -156,11 +156,12 @@ struct Location { float latitude, longitude, timezone; };
 /// compute_sun_coordinates (sunsky.h:283-374), Blanco-Muriel et al. in fp32 as the reference runs it
 inline Vec3 sun_coordinates(const DateTime &dt, const Location &loc) {
     const float deg2rad = (float) (3.14159265358979323846 / 180.0);
-    float dec_hours = dt.hour - loc.timezone + fdiv(dt.minute + fdiv(dt.second, 60.f), 60.f);
+    // Float / scalar divisions are a1 * rcp(a2) in Dr.Jit (drjit/array_router.h:225-228)
+    float dec_hours = dt.hour - loc.timezone + (dt.minute + dt.second * (1.f / 60.f)) * (1.f / 60.f);
     int32_t aux1 = (dt.month - 14) / 12;
     int32_t aux2 = (1461 * (dt.year + 4800 + aux1)) / 4 + (367 * (dt.month - 2 - 12 * aux1)) / 12 -
                    (3 * ((dt.year + 4900 + aux1) / 100)) / 4 + dt.day - 32075;
-    float julian = (float) aux2 - 0.5f + fdiv(dec_hours, 24.f);
+    float julian = (float) aux2 - 0.5f + dec_hours * (1.f / 24.f);
     float elapsed = julian - 2451545.f;
 
     float omega = 2.1429f - 0.0010394594f * elapsed;

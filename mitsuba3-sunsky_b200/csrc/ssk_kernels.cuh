@@ -153,9 +153,11 @@ sample_kernel(const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
                 eval_rgb(P, sun_rad, wi, s.active, e);
                 e[3] = 0.f;
             }
+            // Spectrum / Float -> eval * rcp(pdf) (drjit/array_router.h:225-228)
+            const float inv_pdf = fdiv(1.f, s.pdf);
 #pragma unroll
             for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
-                float w = fdiv(e[c], s.pdf);
+                float w = e[c] * inv_pdf;
                 q[c][k] = (fabsf(w) < INFINITY) ? w : 0.f;         // res &= isfinite(res)
             }
             // bounding-sphere bookkeeping (sunsky.cpp:415-421)

@@ -59,14 +59,16 @@ SSK_HD Vec3 xform(const float *m, const Vec3 &v) {
 
 /// Quantities shared by every channel of one ray (sunsky.cpp:547-552)
 struct RayTerms {
-    float cos_theta, gamma, cos_gamma, cos_gamma_sqr, denom_c1, one_plus_cg2, sqrt_cos_theta;
+    float cos_theta, gamma, cos_gamma, cos_gamma_sqr, inv_denom_c1, one_plus_cg2, sqrt_cos_theta;
 };
 SSK_HD RayTerms ray_terms(float cos_theta, float gamma) {
     RayTerms r;
     r.cos_theta = cos_theta; r.gamma = gamma;
     r.cos_gamma = dcos(gamma);
     r.cos_gamma_sqr = r.cos_gamma * r.cos_gamma;
-    r.denom_c1 = cos_theta + 0.01f;
+    // `coefs[1] / (cos_theta + 0.01f)` divides a Spectrum by a Float: Dr.Jit routes an array divided by
+    // a shallower operand to a1 * rcp(a2) (drjit/array_router.h:218-232), rcp = 1/x on the LLVM backend
+    r.inv_denom_c1 = fdiv(1.f, cos_theta + 0.01f);
     r.one_plus_cg2 = 1.f + r.cos_gamma_sqr;
     r.sqrt_cos_theta = safe_sqrt(cos_theta);
     return r;
@@ -77,7 +79,7 @@ SSK_HD float render_sky(const EmitterBlock &P, int ch, const RayTerms &r) {
     float A0 = P.sky_params[0][ch], A1 = P.sky_params[1][ch], A2 = P.sky_params[2][ch],
           A3 = P.sky_params[3][ch], A4 = P.sky_params[4][ch], A5 = P.sky_params[5][ch],
           A6 = P.sky_params[6][ch], A7 = P.sky_params[7][ch], A8 = P.sky_params[8][ch];
-    float c1 = 1.f + A0 * dexp(fdiv(A1, r.denom_c1));
+    float c1 = 1.f + A0 * dexp(A1 * r.inv_denom_c1);
     float chi = fdiv(r.one_plus_cg2, dpow15(1.f + A8 * A8 - 2.f * A8 * r.cos_gamma));
     float c2 = A2 + A3 * dexp(A4 * r.gamma) + A5 * r.cos_gamma_sqr + A6 * chi + A7 * r.sqrt_cos_theta;
     return c1 * c2 * P.sky_rad[ch];
@@ -98,7 +100,7 @@ SSK_HD SunSeg sun_segment(float cos_theta) {
     float f = floorf(dcbrt(2.f * elevation * SSK_INV_PI) * (float) kSunSegments);
     uint32_t pos = (uint32_t) (int32_t) f;
     pos = pos < (uint32_t) (kSunSegments - 1) ? pos : (uint32_t) (kSunSegments - 1);
-    float q = fdiv((float) pos, (float) kSunSegments);
+    float q = (float) pos * (1.f / (float) kSunSegments);   // Float / int -> mul by rcp (array_router.h:225-228)
     float break_x = SSK_HALF_PI * (q * (q * q));   // dr::pow(q, 3.f) = powi: q * (q*q)
     return { pos, elevation - break_x };
 }
@@ -191,7 +193,7 @@ SSK_HD void eval_spec(const EmitterBlock &P, const float *sun_rad, const Vec3 &w
     }
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-        float nw = fdiv(wav[w] - 320.f, 40.f);
+        float nw = (wav[w] - 320.f) * (1.f / 40.f);               // Spectrum / size_t -> mul by rcp(40.f)
         bool valid = 0.f <= nw && nw <= 10.f;
         if (!valid) { out[w] = 0.f; continue; }
         int lo = (int) floorf(nw), hi = lo + 1;

@@ -1,0 +1,60 @@
+// DEBUG AID for development in the GPU-less container only (never shipped, never used by the product,
+// the GPU tests, smoke() or bench.py): runs the __host__ __device__ per-lane model of
+// mitsuba3-sunsky_b200/csrc/ssk_model.cuh on the host so restatement bugs show up before a GPU run.
+#include "../../mitsuba3-sunsky_b200/csrc/ssk_host.cuh"
+using namespace ssk;
+extern "C" {
+void *hostdbg_create(const ssk_params *p, const char *dir, int spectral) {
+    HostEmitter *E = new HostEmitter();
+    try {
+        E->spectral = spectral; E->n_channels = spectral ? 11 : 3;
+        E->data = load_datasets(dir, spectral);
+        build_emitter(*E, *p, true);
+    } catch (const std::exception &e) { fprintf(stderr, "hostdbg: %s\n", e.what()); delete E; return nullptr; }
+    return E;
+}
+void hostdbg_eval(void *h, size_t n, const float *wi, const float *wav, float *out) {
+    HostEmitter &E = *(HostEmitter *) h;
+    for (size_t i = 0; i < n; ++i) {
+        Vec3 v = { wi[i], wi[n + i], wi[2 * n + i] };
+        if (E.spectral) {
+            float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }, o[4];
+            eval_spec(E.block, E.block.sun_rad, v, w, true, o);
+            for (int c = 0; c < 4; ++c) out[c * n + i] = o[c];
+        } else {
+            float o[3];
+            eval_rgb(E.block, E.block.sun_rad, v, true, o);
+            for (int c = 0; c < 3; ++c) out[c * n + i] = o[c];
+        }
+    }
+}
+void hostdbg_pdf(void *h, size_t n, const float *d, float *pdf) {
+    HostEmitter &E = *(HostEmitter *) h;
+    for (size_t i = 0; i < n; ++i) pdf[i] = pdf_direction(E.block, Vec3{ d[i], d[n + i], d[2 * n + i] });
+}
+void hostdbg_sample(void *h, size_t n, const float *u, const float *wav, float *d, float *pdf, float *weight) {
+    HostEmitter &E = *(HostEmitter *) h;
+    int C = E.spectral ? 4 : 3;
+    for (size_t i = 0; i < n; ++i) {
+        DirSample s = sample_dir(E.block, u[i], u[n + i]);
+        d[i] = s.d_world.x; d[n + i] = s.d_world.y; d[2 * n + i] = s.d_world.z; pdf[i] = s.pdf;
+        Vec3 wi = { -s.d_world.x, -s.d_world.y, -s.d_world.z };
+        float e[4];
+        if (E.spectral) { float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }; eval_spec(E.block, E.block.sun_rad, wi, w, s.active, e); }
+        else eval_rgb(E.block, E.block.sun_rad, wi, s.active, e);
+        for (int c = 0; c < C; ++c) { float w = e[c] * (1.f / s.pdf); weight[c * n + i] = (fabsf(w) < INFINITY) ? w : 0.f; }
+    }
+}
+void hostdbg_math(int op, size_t n, const float *a, const float *b, float *o) {
+    for (size_t i = 0; i < n; ++i) {
+        float x = a[i];
+        switch (op) {
+            case 0: o[i] = dsin(x); break; case 1: o[i] = dcos(x); break; case 2: o[i] = dasin(x); break;
+            case 3: o[i] = dacos(x); break; case 4: o[i] = datan2(x, b[i]); break; case 5: o[i] = dexp(x); break;
+            case 6: o[i] = dexp2(x); break; case 7: o[i] = dlog(x); break; case 8: o[i] = dlog2(x); break;
+            case 9: o[i] = dcbrt(x); break; case 10: o[i] = derf(x); break; case 11: o[i] = derfinv(x); break;
+            case 12: o[i] = dpow15(x); break; case 13: o[i] = dtan(x); break; case 14: o[i] = sqrtf(x); break;
+        }
+    }
+}
+}
