@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""Benchmark of the sunsky hot path (see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+One JSON line on stdout. A "step" is one pass of SunskyEmitter.eval (spectral, sun + sky) over the
+BASELINE configs[1] batch: 2^24 random upper-hemisphere directions with 4 wavelengths each, resident in
+HBM (470 MB of inputs per step, larger than the 126 MB L2, so no flush is needed between steps).
+`value` = Gevals/s over all ranks (device time, CUDA events, max over ranks); `e2e` = the same through
+ssk_eval_host with pinned host buffers (H2D + kernel + D2H inside the timed region). `extra` carries the
+other kernels of the path (RGB eval, pdf_direction, fused sample_direction on the configs[2] batch)."""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(REPO, "mitsuba3-sunsky_b200"), os.path.join(REPO, "oracle"), os.path.join(REPO, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+N_EVAL = 1 << 24            # BASELINE configs[1]: 16M directions
+N_SAMPLE = 1 << 26          # BASELINE configs[2]: 64M samples
+FLOPS = dict(eval_spectral=1013, eval_rgb=426, pdf=761, sample_rgb=1776)
+BYTES = dict(eval_spectral=44, eval_rgb=24, pdf=16, sample_rgb=36)
+METRIC = "sky+sun radiance Gevals/s (spectral eval, 16M directions)"
+
+
+def peaks():
+    p = dict(hbm_gbs=6650.0, sm_max_mhz=1965.0, source="fallback")
+    try:
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        p.update(hbm_gbs=float(m["hbm_gbs"]), sm_max_mhz=float(m["sm_max_mhz"]), source="measured")
+    except Exception:
+        pass
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index; self.rows = []; self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) > 8:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=sorted(reasons), samples=len(sm))
+
+
+def emitter_kwargs():
+    import common
+    return dict(turbidity=3.0, albedo=0.3, sun_direction=common.sun_dir_from_elevation(30.0))
+
+
+def cpu_reference_rate(n_sample, threads, spectral=True, seed=0):
+    """Times the reference's own CPU code (oracle/_ref: its sunsky.cpp compiled in place, array flavour)
+    on `n_sample` directions with `threads` host threads. Returns (Gevals/s, seconds)."""
+    import ref_oracle
+    import common
+    rng = np.random.default_rng(seed)
+    wo = common.hemisphere_dirs(n_sample, rng)
+    wav = np.minimum(360.0 + 360.0 * rng.random((4, n_sample), dtype=np.float32), 719.99).astype(np.float32) if spectral else None
+    r = ref_oracle.RefEmitter(spectral=spectral, flavour=1, **emitter_kwargs())
+    r.eval(-wo[:, :4096], None if wav is None else wav[:, :4096], threads=1)
+    t0 = time.perf_counter()
+    r.eval(-wo, wav, threads=threads)
+    dt = time.perf_counter() - t0
+    return n_sample / dt / 1e9, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import ref_oracle
+    if not ref_oracle.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libsunsky_ref.so was not built"}))
+        return 0
+    cores = os.cpu_count() or 1
+    threads = min(cores, 64)
+    n_sample = 1 << 19
+    rates = []
+    for i in range(args.warmup + args.steps):
+        rate, dt = cpu_reference_rate(n_sample, threads, True, seed=i)
+        if i >= args.warmup:
+            rates.append((rate, dt))
+    total_t = sum(dt for _, dt in rates)
+    value = n_sample * len(rates) / total_t / 1e9
+    sample = f"{n_sample} of the {N_EVAL} directions per step (same distribution), {threads} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / len(rates) * (N_EVAL / n_sample),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths, t=3 a=0.3 eta=30deg, sun+sky"},
+        "cpu_baseline": {"value": value, "unit": "Gevals/s", "cores": threads, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": "Gevals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extra", action="store_true", help="skip the secondary kernels and the CPU baseline")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import sunsky_b200 as ssk
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the sunsky kernels have no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    warm = max(args.warmup, 3)
+    gen = torch.Generator(device=dev); gen.manual_seed(1234 + rank)
+
+    def hemisphere(n):
+        u1 = torch.rand(n, device=dev, generator=gen); u2 = torch.rand(n, device=dev, generator=gen)
+        st = torch.sqrt(torch.clamp(1 - u1 * u1, min=0)); ph = 2 * np.pi * u2
+        return torch.stack([st * torch.cos(ph), st * torch.sin(ph), u1]).contiguous()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
+        l0 = ssk.launch_count()
+        ev0.record()
+        for _ in range(steps):
+            fn()
+        ev1.record()
+        barrier()
+        return max_over_ranks(ev0.elapsed_time(ev1)), ssk.launch_count() - l0
+
+    kw = emitter_kwargs()
+    em_spec = ssk.SunskyEmitter(spectral=True, device=local, **kw)
+    em_rgb = ssk.SunskyEmitter(spectral=False, device=local, **kw)
+    pk = peaks()
+    sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    fp32_peak = sm_count * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12          # TFLOP/s at max SM clock
+
+    # ---- headline: spectral eval, inputs resident in HBM ------------------------------------------
+    wo = hemisphere(N_EVAL); wi = (-wo).contiguous(); del wo
+    wav = (360.0 + 360.0 * torch.rand((4, N_EVAL), device=dev, generator=gen)).clamp_(max=719.99).contiguous()
+    out = torch.empty((4, N_EVAL), device=dev)
+    import ctypes as C
+    from sunsky_b200 import _capi
+
+    def planes(t):
+        arr = (_capi.FP * t.shape[0])()
+        for i in range(t.shape[0]):
+            arr[i] = C.cast(t[i].data_ptr(), _capi.FP)
+        return arr
+    L = _capi.lib()
+    wi_pp, wav_pp, out_pp = planes(wi), planes(wav), planes(out)
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def step_eval():
+        rc = L.ssk_eval_device(em_spec._ctx, wi_pp, wav_pp, N_EVAL, out_pp, stream)
+        assert rc == 0, L.ssk_last_error()
+
+    sampler = ClockSampler(local); sampler.start()
+    ms, launches = timed(step_eval, args.steps, warm)
+    clocks = sampler.stop()
+    ms_per_step = ms / args.steps
+    value = world * N_EVAL / (ms_per_step * 1e-3) / 1e9
+    per_gpu = value / world
+    achieved_tf = per_gpu * 1e9 * FLOPS["eval_spectral"] / 1e12
+    roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                "frac": achieved_tf / fp32_peak, "traffic": None,
+                "peak_source": f"{sm_count} SMs x 128 lanes x 2 flop x {pk['sm_max_mhz']:.0f} MHz ({pk['source']} max SM clock)",
+                "kernel": "eval_spec_kernel", "flops_per_eval": FLOPS["eval_spectral"],
+                "hbm": {"achieved": per_gpu * BYTES["eval_spectral"], "peak": pk["hbm_gbs"], "unit": "GB/s",
+                        "frac": per_gpu * BYTES["eval_spectral"] / pk["hbm_gbs"], "bytes_per_eval": BYTES["eval_spectral"]}}
+
+    # ---- e2e: same workload through the host entry point with pinned buffers ------------------------
+    n_e2e = N_EVAL
+    h_wi = torch.empty((3, n_e2e), pin_memory=True); h_wi.copy_(wi)
+    h_wav = torch.empty((4, n_e2e), pin_memory=True); h_wav.copy_(wav)
+    h_out = torch.empty((4, n_e2e), pin_memory=True)
+    hwi_pp, hwav_pp, hout_pp = planes(h_wi), planes(h_wav), planes(h_out)
+
+    def step_e2e():
+        rc = L.ssk_eval_host(em_spec._ctx, hwi_pp, hwav_pp, n_e2e, hout_pp)
+        assert rc == 0, L.ssk_last_error()
+
+    e2e_steps = max(3, min(args.steps, 5))
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    e2e_ms = max_over_ranks(e2e_s * 1e3)
+    e2e = {"value": world * n_e2e / (e2e_ms * 1e-3) / 1e9, "unit": "Gevals/s",
+           "h2d_bytes_per_step": 7 * 4 * n_e2e, "d2h_bytes_per_step": 4 * 4 * n_e2e, "ms_per_step": e2e_ms}
+    del h_wi, h_wav, h_out
+
+    # ---- the other kernels of the path ---------------------------------------------------------------
+    extra = {}
+    if not args.no_extra:
+        def rate(ms_total, steps, n, key):
+            r = world * n / (ms_total / steps * 1e-3) / 1e9
+            return {"value": r, "unit": "G/s", "ms": ms_total / steps,
+                    "fp32_frac": r / world * 1e9 * FLOPS[key] / 1e12 / fp32_peak,
+                    "hbm_gbs": r / world * BYTES[key]}
+        out3 = torch.empty((3, N_EVAL), device=dev)
+        o3_pp = planes(out3)
+
+        def step_rgb():
+            assert L.ssk_eval_device(em_rgb._ctx, wi_pp, None, N_EVAL, o3_pp, stream) == 0
+        ms_r, _ = timed(step_rgb, args.steps, warm)
+        extra["eval_rgb_Gevals_s"] = rate(ms_r, args.steps, N_EVAL, "eval_rgb")
+        pdf = torch.empty(N_EVAL, device=dev)
+
+        def step_pdf():
+            assert L.ssk_pdf_direction_device(em_rgb._ctx, wi_pp, N_EVAL, C.cast(pdf.data_ptr(), _capi.FP), stream) == 0
+        ms_p, _ = timed(step_pdf, args.steps, warm)
+        extra["pdf_direction_Gpdf_s"] = rate(ms_p, args.steps, N_EVAL, "pdf")
+        del out, out3, wav, pdf
+        # configs[2]: fused TGMM sample + pdf + eval + weight on 2^26 samples (t=6, a=0.5, eta=50.2 deg)
+        import common
+        em_s = ssk.SunskyEmitter(spectral=False, device=local, turbidity=6.0, albedo=0.5,
+                                 sun_direction=common.sun_dir_from_elevation(50.2))
+        u = torch.rand((2, N_SAMPLE), device=dev, generator=gen)
+        d = torch.empty((3, N_SAMPLE), device=dev); spdf = torch.empty(N_SAMPLE, device=dev)
+        wgt = torch.empty((3, N_SAMPLE), device=dev)
+        u_pp, d_pp, w_pp = planes(u), planes(d), planes(wgt)
+
+        def step_sample():
+            assert L.ssk_sample_direction_device(em_s._ctx, u_pp, None, None, N_SAMPLE, d_pp,
+                                                 C.cast(spdf.data_ptr(), _capi.FP), w_pp, None, None, stream) == 0
+        s_steps = max(3, args.steps // 4)
+        ms_s, _ = timed(step_sample, s_steps, 3)
+        extra["sample_direction_Gsamples_s"] = rate(ms_s, s_steps, N_SAMPLE, "sample_rgb")
+        extra["sample_direction_lower_hemisphere"] = int((d[2] < 0).sum().item())
+        del u, d, spdf, wgt
+
+    # ---- CPU baseline: the reference's own CPU code on the box's host cores (rank 0, N = 1 only) -------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_extra:
+        try:
+            import ref_oracle
+            if ref_oracle.available():
+                cores = os.cpu_count() or 1
+                threads = min(cores, 64)
+                n_s = 1 << 20
+                r, dt = cpu_reference_rate(n_s, threads, True)
+                r1, dt1 = cpu_reference_rate(1 << 16, 1, True)
+                cpu = {"value": r, "unit": "Gevals/s", "cores": threads, "kind": "reference",
+                       "sample": f"{n_s} of the {N_EVAL} directions (same distribution), {dt:.1f} s; "
+                                 f"1 thread: {r1 * 1e3:.3f} Mevals/s; host has {cores} logical cores",
+                       "single_thread_value": r1}
+        except Exception as ex:  # the baseline is reported, never required
+            cpu = {"error": str(ex)}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": world, "steps": args.steps,
+            "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths per GPU, "
+                                   "t=3 a=0.3 eta=30deg, sun+sky",
+                       "l2": "inputs (470 MB/step) exceed the 126 MB L2; no flush needed", "arith": "exact (reference op order)"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "extra": extra,
+        }))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

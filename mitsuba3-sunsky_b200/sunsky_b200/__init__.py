@@ -143,6 +143,12 @@ class SunskyEmitter:
         unknown = set(props) - set(_PARAM_KEYS) | ({"sun_aperture"} & set(props))
         if unknown:
             raise TypeError(f"not a traversable sunsky parameter: {sorted(unknown)}")
+        record_keys = {"latitude", "longitude", "timezone", "year", "month", "day", "hour", "minute", "second"}
+        if (self._params.use_record and "sun_direction" in props) or \
+                (not self._params.use_record and record_keys & set(props)):
+            # traverse() only exposes the parametrisation the emitter was created with (sunsky.cpp:226-238)
+            raise SunskyError(_capi.SSK_ERR_INVALID, "an emitter keeps the sun parametrisation (direction or "
+                              "date/location) it was created with")
         p = Params.from_buffer_copy(self._params)
         self._fill(p, props, creating=False)
         _check(self._L.ssk_update(self._ctx, C.byref(p)))

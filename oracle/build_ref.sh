@@ -24,7 +24,7 @@ awk '/^static const Float cie1931_tbl\[/ {p=1} p {print} p && /};/ {exit}' "$REF
 test -s "$GEN/cie1931_tbl.inc"
 # 3. compile. -mfma + -ffp-contract=off: dr::fmadd is a hardware FMA, a*b+c is not contracted
 #    (what the LLVM backend emits: llvm.fma + plain fmul/fadd, no fast-math flags).
-CXX="${CXX:-g++}"
+CXX="${SSK_CXX:-/usr/bin/g++}"   # the system compiler: links libstdc++ dynamically (a static copy clashes with numpy/torch's)
 FLAGS="-std=c++17 -O2 -fPIC -shared -mavx2 -mfma -ffp-contract=off -fno-fast-math -w -pthread"
 INC="-I $HERE/ref_shadow -I $GEN -I $GEN/include -I $REF -I $REF/include -I $REF/ext/drjit/include \
  -I $REF/ext/drjit/ext/drjit-core/include -I $REF/ext/drjit/ext/drjit-core/ext/nanothread/include \

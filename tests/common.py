@@ -81,7 +81,7 @@ def parity_inputs(sun_dir_world, spectral, seed=1234, n_rand=2048):
     n = wo.shape[1]
     wav = None
     if spectral:
-        wav = (360.0 + 360.0 * rng.random((4, n), dtype=np.float32)).astype(np.float32)
+        wav = np.minimum(360.0 + 360.0 * rng.random((4, n), dtype=np.float32), 719.99).astype(np.float32)
         wav[:, :12] = np.array([[320.0, 360.0, 719.999, 719.99, 300.0, 730.0, 400.0, 440.0, 480.0, 520.0, 680.0, 321.0]] * 4,
                                dtype=np.float32)
         wav[1, :4] = [359.9, 500.0, 640.0, 700.0]

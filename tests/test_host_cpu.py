@@ -1,0 +1,194 @@
+"""CPU-only tests (`-m "not gpu"`): the C ABI loads and exports every declared symbol, host-side setup
+(dataset loading, coefficient interpolation, TGMM mixture, sun position, sampling weight) reproduces
+the reference's emitter state bit for bit, property validation mirrors the plugin, and the compute
+entry points fail loudly without a CUDA device (no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import common
+import emitters
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_capi_exports_every_declared_symbol(ssk):
+    from sunsky_b200 import _capi
+    hdr = open(os.path.join(REPO, "include", "sunsky_b200.h")).read()
+    declared = set(re.findall(r"\b(ssk_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    L = _capi.lib()
+    for name in sorted(declared):
+        assert hasattr(L, name), f"{name} declared in include/sunsky_b200.h but not exported"
+    assert declared == set(_capi.SYMBOLS), (declared ^ set(_capi.SYMBOLS))
+    assert b"sm_100a" in L.ssk_version()
+
+
+STATE_EXACT = ["sky_params", "sky_radiance", "sun_radiance", "sun_ld", "gaussians", "pmf", "cdf", "cdf_sum",
+               "cdf_normalization", "sky_sampling_w", "sun_angles", "frame_s", "frame_t", "frame_n",
+               "sun_half_aperture"]
+
+
+@pytest.mark.parametrize("name", list(common.CONFIGS))
+def test_state_matches_reference_bitwise(ssk, name):
+    """Every interpolated coefficient, the TGMM mixture + CDF, the sun frame and the quadrature-based
+    sampling weight are bit-identical to the reference's private members (golden from oracle/_ref)."""
+    g = emitters.golden(name)
+    e = emitters.make(ssk, name, device=-1, g=g)
+    s = e.state()
+    nc = s.n_channels
+    assert nc == int(g["state_n_channels"])
+    sizes = dict(sky_params=nc * 9, sky_radiance=nc, sun_radiance=s.n_sun_radiance, sun_ld=66 if nc == 11 else 0)
+    for f in STATE_EXACT:
+        mine = np.atleast_1d(np.array(getattr(s, f), dtype=np.float32))
+        ref = np.atleast_1d(g["state_" + f])
+        k = sizes.get(f, min(mine.size, ref.size))
+        assert common.bit_equal(mine[:k], ref[:k]), f"{name}: {f} differs (max abs {np.abs(mine[:k] - ref[:k]).max()})"
+
+
+def test_state_against_live_reference(ssk, ref):
+    """Same check against the reference library itself on configurations that are not in the fixtures."""
+    rng = np.random.default_rng(5)
+    for spectral in (False, True):
+        for _ in range(4):
+            t = float(rng.uniform(1, 10)); a = float(rng.uniform(0, 1))
+            sd = common.sun_dir_from_elevation(float(rng.uniform(0.5, 89.5)), float(rng.uniform(-3, 3)))
+            r = ref.RefEmitter(spectral=spectral, flavour=1, turbidity=t, albedo=a, sun_direction=sd)
+            rs = r.state()
+            e = ssk.SunskyEmitter(spectral=spectral, device=-1, sun_direction_normalized=True, turbidity=t, albedo=a,
+                                  sun_direction=list(rs.sun_dir_world))
+            s = e.state()
+            for f in ("gaussians", "cdf", "sun_angles", "frame_s", "frame_t"):
+                assert common.bit_equal(np.array(getattr(s, f)), np.array(getattr(rs, f))), f
+            assert common.bit_equal(np.array(s.sky_params[:s.n_channels * 9]), np.array(rs.sky_params[:s.n_channels * 9]))
+            assert s.sky_sampling_w == rs.sky_sampling_w
+
+
+def test_sun_coordinates_match_reference(ssk):
+    g = emitters.golden("drjit_math")
+    for rec, want in zip(g["sun_coord_in"], g["sun_coord_out"]):
+        got = ssk.sun_coordinates(int(rec[0]), int(rec[1]), int(rec[2]), *[float(v) for v in rec[3:]])
+        assert common.bit_equal(got, want), (rec, got, want)
+
+
+def test_default_record_and_traverse_surface(ssk):
+    e = ssk.SunskyEmitter(device=-1)
+    names = list(e.traverse())
+    # traverse() order of the reference (sunsky.cpp:220-240)
+    assert names == ["turbidity", "sky_scale", "sun_scale", "albedo", "latitude", "longitude", "timezone", "year",
+                     "day", "month", "hour", "minute", "second", "to_world"]
+    e2 = ssk.SunskyEmitter(device=-1, sun_direction=[0, 0, 1])
+    assert list(e2.traverse()) == ["turbidity", "sky_scale", "sun_scale", "albedo", "sun_direction", "to_world"]
+    assert "SunskyEmitter[" in e.to_string() and "turbidity = 3" in e.to_string()
+    assert abs(e.state().sun_half_aperture - np.radians(0.5358 / 2)) < 1e-9
+
+
+def test_traverse_names_match_reference(ssk, ref):
+    r = ref.RefEmitter(spectral=False, flavour=0, turbidity=3.0, albedo=0.3, sun_direction=[0, 0, 1])
+    assert r.traverse_names() == list(ssk.SunskyEmitter(device=-1, sun_direction=[0, 0, 1]).traverse())
+    r = ref.RefEmitter(spectral=False, flavour=0, turbidity=3.0, albedo=0.3, hour=12.0)
+    assert r.traverse_names() == list(ssk.SunskyEmitter(device=-1, hour=12.0).traverse())
+
+
+@pytest.mark.parametrize("bad", [dict(turbidity=0.5), dict(turbidity=10.5), dict(sun_scale=-1.0), dict(sky_scale=-0.1),
+                                 dict(albedo=1.5), dict(albedo=-0.1), dict(sun_aperture=0.0), dict(sun_aperture=180.0),
+                                 dict(sun_direction=[0, 0, 1], hour=3.0)])
+def test_invalid_properties_are_rejected(ssk, bad):
+    """Same validation as init_from_props / parameters_changed (sunsky.cpp:243-252, 889-948, 974)."""
+    with pytest.raises(ssk.SunskyError):
+        ssk.SunskyEmitter(device=-1, **bad)
+
+
+def test_invalid_properties_match_reference(ssk, ref):
+    for bad in (dict(turbidity=0.5), dict(turbidity=11.0), dict(sun_scale=-1.0), dict(albedo=1.5), dict(sun_aperture=190.0)):
+        kw = dict(turbidity=3.0, albedo=0.3, sun_direction=[0, 0, 1]); kw.update(bad)
+        with pytest.raises(RuntimeError):
+            ref.RefEmitter(spectral=False, flavour=0, **kw)
+        with pytest.raises(ssk.SunskyError):
+            ssk.SunskyEmitter(device=-1, **kw)
+
+
+def test_update_is_parameters_changed(ssk):
+    g = emitters.golden("cfg3_rgb_sunsky")
+    e = emitters.make(ssk, "cfg1_rgb", device=-1, g=emitters.golden("cfg1_rgb"))
+    e.update(turbidity=6.0, albedo=0.5, sun_direction=[float(v) for v in g["state_sun_dir_world"]])
+    s = e.state()
+    assert common.bit_equal(np.array(s.sky_params[:27]), g["state_sky_params"][:27])
+    assert common.bit_equal(np.array(s.gaussians), g["state_gaussians"])
+    assert s.sky_sampling_w == float(g["state_sky_sampling_w"])
+    with pytest.raises(ssk.SunskyError):
+        e.update(turbidity=42.0)
+    assert e.state().sky_sampling_w == float(g["state_sky_sampling_w"])      # failed update leaves state intact
+    with pytest.raises(ssk.SunskyError):
+        e.update(hour=3.0)                                                    # cannot switch parametrisation
+
+
+def test_missing_dataset_is_an_io_error(ssk, tmp_path):
+    with pytest.raises(ssk.SunskyError) as ei:
+        ssk.SunskyEmitter(device=-1, dataset_dir=str(tmp_path))
+    assert ei.value.code == -2 and "does not exist" in str(ei.value)
+    bad = tmp_path / "d"; bad.mkdir()
+    for f in os.listdir(ssk.DATASET_DIR):
+        (bad / f).write_bytes(b"XYZ" + open(os.path.join(ssk.DATASET_DIR, f), "rb").read()[3:])
+    with pytest.raises(ssk.SunskyError):
+        ssk.SunskyEmitter(device=-1, dataset_dir=str(bad))
+
+
+def test_dataset_file_roundtrip(ssk, tmp_path):
+    """array_from_file / array_to_file (sunsky.h:515-597): shapes of the shipped datasets, write/read."""
+    a = ssk.array_from_file(os.path.join(ssk.DATASET_DIR, "sky_rgb_params.bin"), True)
+    assert a.shape == (10, 2, 6, 3, 9)
+    t = ssk.array_from_file(os.path.join(ssk.DATASET_DIR, "tgmm_tables.bin"), False)
+    assert t.shape == (9, 30, 5, 5) and abs(t[..., 4].sum(axis=-1) - 1).max() < 1e-4
+    p = str(tmp_path / "x.bin")
+    ssk.array_to_file(p, t, as_f64=False)
+    assert common.bit_equal(ssk.array_from_file(p, False), t)
+    ssk.array_to_file(p, a, as_f64=True)
+    assert common.bit_equal(ssk.array_from_file(p, True), a)
+
+
+def test_no_cpu_fallback(ssk):
+    """Host-only contexts answer state queries but every compute entry point refuses to run."""
+    e = ssk.SunskyEmitter(device=-1, sun_direction=[0, 0, 1])
+    wi = np.zeros((3, 8), np.float32); wi[2] = -1
+    for call in (lambda: e.eval(wi), lambda: e.pdf_direction(wi), lambda: e.sample_direction(np.zeros((2, 8), np.float32)),
+                 lambda: e.eval_direction(wi)):
+        with pytest.raises(ssk.SunskyError) as ei:
+            call()
+        assert ei.value.code == -3 and "no CPU fallback" in str(ei.value)
+
+
+def test_cuda_device_missing_is_loud(ssk):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(ssk.SunskyError) as ei:
+        ssk.SunskyEmitter(device=0, sun_direction=[0, 0, 1])
+    assert ei.value.code == -3
+
+
+def test_reference_scalar_and_array_flavours_differ(ref):
+    """Documents SURVEY fact 4: scalar_* and llvm_ad_*-like arithmetic are different functions
+    (sampling weight 0.5 vs quadrature; erf branch), which is why parity targets the array flavour."""
+    kw = dict(turbidity=3.0, albedo=0.3, sun_direction=common.sun_dir_from_elevation(30.0))
+    a = ref.RefEmitter(spectral=False, flavour=1, **kw).state().sky_sampling_w
+    s = ref.RefEmitter(spectral=False, flavour=0, **kw).state().sky_sampling_w
+    assert s == 0.5 and abs(a - 0.352) < 1e-3
+    x = np.linspace(-3, 3, 2001).astype(np.float32)
+    assert not common.bit_equal(ref.math("erf", x, flavour=0), ref.math("erf", x, flavour=1))
+
+
+def test_golden_reproducible_from_reference(ref):
+    """The committed fixtures are what the reference library produces here (guards against stale goldens)."""
+    for name in ("cfg1_rgb", "cfg2_spec", "rgb_record_h9p5"):
+        spectral, kw = common.CONFIGS[name]
+        g = emitters.golden(name)
+        r = ref.RefEmitter(spectral=spectral, flavour=1, **kw)
+        wav = g["wav"] if spectral else None
+        assert common.bit_equal(r.eval(-g["wo"], wav), g["eval"])
+        assert common.bit_equal(r.pdf_direction(g["wo"]), g["pdf"])
+        d, pdf, w = r.sample_direction(g["u"], None, wav)
+        assert common.bit_equal(d, g["s_d"]) and common.bit_equal(pdf, g["s_pdf"]) and common.bit_equal(w, g["s_weight"])
