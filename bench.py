@@ -43,43 +43,68 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons of one GPU, polled through NVML from a thread while the timed regions
+    run (nvidia-smi's own loop mode starts too slowly for a sub-second region). Samples carry a host
+    timestamp so the ones inside a timed region can be told apart from the rest of the run."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
-    def __init__(self, gpu_index):
-        self.idx = gpu_index; self.rows = []; self.proc = None
+    def __init__(self, uuid, period_s=0.01):
+        self.uuid = uuid; self.period = period_s; self.rows = []; self.h = None; self.stop_flag = False
+        self.max_mhz = None; self.t = None; self.nv = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
-        except Exception:
-            self.proc = None
+            import pynvml as nv
+            nv.nvmlInit()
+            try:
+                self.h = nv.nvmlDeviceGetHandleByUUID(self.uuid.encode() if isinstance(self.uuid, str) else self.uuid)
+            except Exception:
+                self.h = nv.nvmlDeviceGetHandleByUUID(self.uuid)
+            self.nv = nv
+            self.max_mhz = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.t = threading.Thread(target=self._poll, daemon=True); self.t.start()
+        except Exception as ex:
+            self.err = str(ex); self.h = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+    def _poll(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                try:
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1e3
+                except Exception:
+                    pw = None
+                self.rows.append((time.perf_counter(), float(mhz), int(rs), pw))
+            except Exception:
+                pass
+            time.sleep(self.period)
 
     def stop(self):
-        if self.proc:
-            self.proc.terminate()
-            try:
-                self.proc.wait(timeout=2)
-            except Exception:
-                self.proc.kill()
-        sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
+        self.stop_flag = True
+        if self.t:
+            self.t.join(timeout=1)
+
+    def summary(self, windows):
+        """Median SM clock over the samples that fall inside any (t0, t1) window; falls back to the whole
+        run when the windows are too short to hold a sample."""
+        inside = [r for r in self.rows if any(a <= r[0] <= b for a, b in windows)]
+        where = "timed regions"
+        if not inside:
+            inside = self.rows; where = "whole run (timed regions shorter than the polling period)"
         reasons = set()
-        for r in self.rows:
-            if len(r) > 8:
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
-                    reasons=sorted(reasons), samples=len(sm))
+        for r in inside:
+            for name, bit in self.REASONS:
+                if r[2] & bit:
+                    reasons.add(name)
+        pw = [r[3] for r in inside if r[3] is not None]
+        return dict(sm_mhz=float(np.median([r[1] for r in inside])) if inside else None, sm_max_mhz=self.max_mhz,
+                    reasons=sorted(reasons), samples=len(inside), window=where,
+                    power_w_max=max(pw) if pw else None)
 
 
 def emitter_kwargs():
@@ -138,8 +163,8 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary kernels and the CPU baseline")
     args = ap.parse_args()
@@ -180,17 +205,21 @@ def main():
         st = torch.sqrt(torch.clamp(1 - u1 * u1, min=0)); ph = 2 * np.pi * u2
         return torch.stack([st * torch.cos(ph), st * torch.sin(ph), u1]).contiguous()
 
+    windows = []                                    # host-time (t0, t1) of every timed region, for the clock record
+
     def timed(fn, steps, warmup):
         for _ in range(warmup):
             fn()
         barrier()
         ev0 = torch.cuda.Event(enable_timing=True); ev1 = torch.cuda.Event(enable_timing=True)
         l0 = ssk.launch_count()
+        t0 = time.perf_counter()
         ev0.record()
         for _ in range(steps):
             fn()
         ev1.record()
         barrier()
+        windows.append((t0, time.perf_counter()))
         return max_over_ranks(ev0.elapsed_time(ev1)), ssk.launch_count() - l0
 
     kw = emitter_kwargs()
@@ -201,7 +230,7 @@ def main():
     fp32_peak = sm_count * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12          # TFLOP/s at max SM clock
 
     # ---- headline: spectral eval, inputs resident in HBM ------------------------------------------
-    wo = hemisphere(N_EVAL); wi = (-wo).contiguous(); del wo
+    wo = hemisphere(N_EVAL); wi = (-wo).contiguous()
     wav = (360.0 + 360.0 * torch.rand((4, N_EVAL), device=dev, generator=gen)).clamp_(max=719.99).contiguous()
     out = torch.empty((4, N_EVAL), device=dev)
     import ctypes as C
@@ -213,16 +242,16 @@ def main():
             arr[i] = C.cast(t[i].data_ptr(), _capi.FP)
         return arr
     L = _capi.lib()
-    wi_pp, wav_pp, out_pp = planes(wi), planes(wav), planes(out)
+    wi_pp, wo_pp, wav_pp, out_pp = planes(wi), planes(wo), planes(wav), planes(out)
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def step_eval():
         rc = L.ssk_eval_device(em_spec._ctx, wi_pp, wav_pp, N_EVAL, out_pp, stream)
         assert rc == 0, L.ssk_last_error()
 
-    sampler = ClockSampler(local); sampler.start()
+    sampler = ClockSampler("GPU-" + str(torch.cuda.get_device_properties(dev).uuid)); sampler.start()
     ms, launches = timed(step_eval, args.steps, warm)
-    clocks = sampler.stop()
+    headline_window = list(windows)
     ms_per_step = ms / args.steps
     value = world * N_EVAL / (ms_per_step * 1e-3) / 1e9
     per_gpu = value / world
@@ -245,14 +274,15 @@ def main():
         rc = L.ssk_eval_host(em_spec._ctx, hwi_pp, hwav_pp, n_e2e, hout_pp)
         assert rc == 0, L.ssk_last_error()
 
-    e2e_steps = max(3, min(args.steps, 5))
+    e2e_steps = max(3, min(args.steps, 20))
     step_e2e()
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         step_e2e()
     barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    windows.append((t0, time.perf_counter()))
+    e2e_s = (windows[-1][1] - t0) / e2e_steps
     e2e_ms = max_over_ranks(e2e_s * 1e3)
     e2e = {"value": world * n_e2e / (e2e_ms * 1e-3) / 1e9, "unit": "Gevals/s",
            "h2d_bytes_per_step": 7 * 4 * n_e2e, "d2h_bytes_per_step": 4 * 4 * n_e2e, "ms_per_step": e2e_ms}
@@ -276,7 +306,7 @@ def main():
         pdf = torch.empty(N_EVAL, device=dev)
 
         def step_pdf():
-            assert L.ssk_pdf_direction_device(em_rgb._ctx, wi_pp, N_EVAL, C.cast(pdf.data_ptr(), _capi.FP), stream) == 0
+            assert L.ssk_pdf_direction_device(em_rgb._ctx, wo_pp, N_EVAL, C.cast(pdf.data_ptr(), _capi.FP), stream) == 0
         ms_p, _ = timed(step_pdf, args.steps, warm)
         extra["pdf_direction_Gpdf_s"] = rate(ms_p, args.steps, N_EVAL, "pdf")
         del out, out3, wav, pdf
@@ -316,6 +346,10 @@ def main():
         except Exception as ex:  # the baseline is reported, never required
             cpu = {"error": str(ex)}
 
+    sampler.stop()
+    clocks = sampler.summary(headline_window)
+    if clocks.get("window", "").startswith("whole"):
+        clocks = sampler.summary(windows)
     if rank == 0:
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": world, "steps": args.steps,

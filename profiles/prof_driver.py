@@ -1,0 +1,67 @@
+#!/usr/bin/env python
+"""Launches each kernel of the sunsky hot path a few times on bench-sized inputs, for `ncu`:
+
+  python profiles/prof_driver.py [--kernels eval_spec,eval_rgb,pdf,sample_rgb,sample_spec,envmap] [--reps 3] [--n-log2 24]
+
+Same emitters and input distributions as bench.py (configs[1] for eval/pdf, configs[2] for sampling).
+It also prints CUDA-event times per kernel, so the plain run doubles as a quick timing check."""
+import argparse
+import os
+import sys
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(REPO, "mitsuba3-sunsky_b200"), os.path.join(REPO, "tests")):
+    sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--kernels", default="eval_spec,eval_rgb,pdf,sample_rgb")
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--n-log2", type=int, default=24)
+    ap.add_argument("--arith", default="exact")
+    args = ap.parse_args()
+    import torch
+    import common
+    import sunsky_b200 as ssk
+    dev = torch.device("cuda", 0)
+    n = 1 << args.n_log2
+    gen = torch.Generator(device=dev); gen.manual_seed(1234)
+    u1 = torch.rand(n, device=dev, generator=gen); u2 = torch.rand(n, device=dev, generator=gen)
+    st = torch.sqrt(torch.clamp(1 - u1 * u1, min=0)); ph = 2 * np.pi * u2
+    wo = torch.stack([st * torch.cos(ph), st * torch.sin(ph), u1]).contiguous()
+    wi = (-wo).contiguous()
+    wav = (360.0 + 360.0 * torch.rand((4, n), device=dev, generator=gen)).clamp_(max=719.99).contiguous()
+    u = torch.rand((2, n), device=dev, generator=gen)
+    extra = {}
+    if args.arith != "exact":
+        extra["arith"] = args.arith
+    kw = dict(turbidity=3.0, albedo=0.3, sun_direction=common.sun_dir_from_elevation(30.0), **extra)
+    kw3 = dict(turbidity=6.0, albedo=0.5, sun_direction=common.sun_dir_from_elevation(50.2), **extra)
+    es, er = ssk.SunskyEmitter(spectral=True, **kw), ssk.SunskyEmitter(spectral=False, **kw)
+    ss, sr = ssk.SunskyEmitter(spectral=True, **kw3), ssk.SunskyEmitter(spectral=False, **kw3)
+    runs = {
+        "eval_spec": lambda: es.eval(wi, wav),
+        "eval_rgb": lambda: er.eval(wi),
+        "pdf": lambda: er.pdf_direction(wo),
+        "sample_rgb": lambda: sr.sample_direction(u),
+        "sample_spec": lambda: ss.sample_direction(u, None, wav),
+        "envmap": lambda: ssk.envmaps([er], 4096, 2048),
+    }
+    for name in args.kernels.split(","):
+        fn = runs[name]
+        fn(); torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.reps):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / args.reps
+        units = n if name != "envmap" else 4096 * 2048
+        print(f"{name}: {ms:.4f} ms per launch incl. output allocation, {units / ms / 1e6:.2f} G/s")
+
+
+if __name__ == "__main__":
+    main()

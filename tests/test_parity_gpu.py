@@ -157,6 +157,7 @@ def test_to_world_rotation_against_reference(ssk, ref):
     wo_world = (M[:3, :3] @ inp["wo"]).astype(np.float32)
     got, want = e.eval(-wo_world), r.eval(-wo_world)
     lit = want.max(axis=0) < 1e3                     # exclude the sun-disc edge where a 1-ulp angle flips the mask
+    lit &= np.abs(inp["wo"][2]) > 1e-5               # ... and the local horizon, where it flips cos_theta >= 0
     err, _ = common.max_rel_err(got[:, lit], want[:, lit])
     assert err < 2e-4, err                           # c2 cancellation amplifies the ~1e-7 direction difference
     d, pdf, w = e.sample_direction(inp["u"])
