@@ -42,9 +42,12 @@ extern "C" {
 #define SSK_FLAG_SUN_DIR_NORMALIZED 1u  /* sun_direction is already unit length: use it verbatim */
 
 /* ssk_params.arith */
-#define SSK_ARITH_EXACT        0   /* replay the reference's op sequence (IEEE div/sqrt, CEPHES polynomials) */
-#define SSK_ARITH_FAST         1   /* same formulas, hardware reciprocal / ex2 / lg2 where the error stays
-                                      far below the 1e-5 parity tolerance */
+#define SSK_ARITH_EXACT        0   /* replay the reference's op sequence (IEEE div/sqrt, CEPHES polynomials):
+                                      bit-identical to the llvm_ad_* variants */
+#define SSK_ARITH_FAST         1   /* same formulas; geometry, cancellation-prone terms and sampled directions keep
+                                      the reference sequence, per-channel / per-Gaussian exp, pow and divisions
+                                      use the MUFU unit (ex2 / rsqrt / rcp). Radiance, pdf and weight stay within
+                                      the 1e-5 relative parity tolerance, directions are bit-identical */
 
 /* The plugin's property surface (reference: src/emitters/sunsky.cpp:19-104, init_from_props :889-948). */
 typedef struct ssk_params {
@@ -157,6 +160,10 @@ int ssk_pdf_direction_host(const ssk_ctx *ctx, const float *const d[3], size_t n
 int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
                               const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
                               float *const weight[4], float *const p[3], float *dist);
+
+/* Test hook: out[i] = a[i] / b[i] computed with the reciprocal-based division the kernels use for
+ * per-emitter constant divisors (device pointers); the tests compare it with IEEE division. */
+int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t n, void *stream);
 
 /* Number of kernel launches issued through this library since load (bench bookkeeping). */
 uint64_t ssk_launch_count(void);

@@ -41,19 +41,17 @@ struct ssk_ctx {
     int mode = SSK_MODE_RGB;
     EmitterBlock *d_block = nullptr;
     int sm_count = 0;
-    int grid_cap[8] = { 0 };    // resident CTAs per SM, per kernel family
     mutable Staging st;
 };
 
 namespace {
 
-constexpr size_t kSmemBytes = offsetof(EmitterBlock, sun_rad);
-
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+/// Persistent grid: enough CTAs to fill every SM at the kernel's occupancy, never more than the work needs.
 template <typename K> int occupancy_grid(const ssk_ctx *ctx, K kernel, size_t n_items, int *grid_out) {
     int per_sm = 0;
-    SSK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, kSmemBytes));
+    SSK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0));
     if (per_sm < 1) per_sm = 1;
     size_t want = (n_items + (size_t) kThreads * kVec - 1) / ((size_t) kThreads * kVec);
     size_t cap = (size_t) ctx->sm_count * per_sm;
@@ -78,6 +76,25 @@ int need_device(const ssk_ctx *ctx) {
     return SSK_OK;
 }
 
+const HotBlock &hot(const ssk_ctx *ctx) { return ctx->E.block; }
+bool fast(const ssk_ctx *ctx) { return ctx->E.block.arith == kFast; }
+
+template <int A, bool Vec>
+int launch_eval_t(const ssk_ctx *ctx, bool spectral, const Planes3 &i3, const Planes4 &w4, float *const out[4], size_t n,
+                  float dir_sign, cudaStream_t s) {
+    int grid = 1;
+    if (spectral) {
+        OutPlanes4 o4 = { out[0], out[1], out[2], out[3] };
+        if (int rc = occupancy_grid(ctx, eval_spec_kernel<A, Vec>, n, &grid)) return rc;
+        eval_spec_kernel<A, Vec><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, w4, o4, n, dir_sign);
+    } else {
+        OutPlanes3 o3 = { out[0], out[1], out[2] };
+        if (int rc = occupancy_grid(ctx, eval_rgb_kernel<A, Vec>, n, &grid)) return rc;
+        eval_rgb_kernel<A, Vec><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, o3, n, dir_sign);
+    }
+    return SSK_OK;
+}
+
 int launch_eval(const ssk_ctx *ctx, const float *const in[3], const float *const wav[4], size_t n,
                 float *const out[4], float dir_sign, cudaStream_t s) {
     if (int rc = need_device(ctx)) return rc;
@@ -90,34 +107,30 @@ int launch_eval(const ssk_ctx *ctx, const float *const in[3], const float *const
         if (!out[c]) return fail(SSK_ERR_INVALID, "null output plane");
         vec = vec && aligned16(out[c]);
     }
-    int grid = 1;
+    Planes3 i3 = { in[0], in[1], in[2] };
+    Planes4 w4 = { nullptr, nullptr, nullptr, nullptr };
     if (spectral) {
         if (!wav || !wav[0] || !wav[1] || !wav[2] || !wav[3])
             return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
         for (int c = 0; c < 4; ++c) vec = vec && aligned16(wav[c]);
-        Planes3 i3 = { in[0], in[1], in[2] };
-        Planes4 w4 = { wav[0], wav[1], wav[2], wav[3] };
-        OutPlanes4 o4 = { out[0], out[1], out[2], out[3] };
-        if (vec) {
-            if (int rc = occupancy_grid(ctx, eval_spec_kernel<true>, n, &grid)) return rc;
-            eval_spec_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, w4, o4, n, dir_sign);
-        } else {
-            if (int rc = occupancy_grid(ctx, eval_spec_kernel<false>, n, &grid)) return rc;
-            eval_spec_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, w4, o4, n, dir_sign);
-        }
-    } else {
-        Planes3 i3 = { in[0], in[1], in[2] };
-        OutPlanes3 o3 = { out[0], out[1], out[2] };
-        if (vec) {
-            if (int rc = occupancy_grid(ctx, eval_rgb_kernel<true>, n, &grid)) return rc;
-            eval_rgb_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, o3, n, dir_sign);
-        } else {
-            if (int rc = occupancy_grid(ctx, eval_rgb_kernel<false>, n, &grid)) return rc;
-            eval_rgb_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, o3, n, dir_sign);
-        }
+        w4 = { wav[0], wav[1], wav[2], wav[3] };
     }
+    int rc;
+    if (fast(ctx)) rc = vec ? launch_eval_t<kFast, true>(ctx, spectral, i3, w4, out, n, dir_sign, s)
+                            : launch_eval_t<kFast, false>(ctx, spectral, i3, w4, out, n, dir_sign, s);
+    else rc = vec ? launch_eval_t<kExact, true>(ctx, spectral, i3, w4, out, n, dir_sign, s)
+                  : launch_eval_t<kExact, false>(ctx, spectral, i3, w4, out, n, dir_sign, s);
+    if (rc) return rc;
     g_launches++;
     SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+template <int A, bool Vec>
+int launch_pdf_t(const ssk_ctx *ctx, const Planes3 &i3, float *pdf, size_t n, cudaStream_t s) {
+    int grid = 1;
+    if (int rc = occupancy_grid(ctx, pdf_kernel<A, Vec>, n, &grid)) return rc;
+    pdf_kernel<A, Vec><<<grid, kThreads, 0, s>>>(hot(ctx), i3, pdf, n);
     return SSK_OK;
 }
 
@@ -127,25 +140,26 @@ int launch_pdf(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf
     if (n == 0) return SSK_OK;
     bool vec = aligned16(d[0]) && aligned16(d[1]) && aligned16(d[2]) && aligned16(pdf);
     Planes3 i3 = { d[0], d[1], d[2] };
-    int grid = 1;
-    if (vec) {
-        if (int rc = occupancy_grid(ctx, pdf_kernel<true>, n, &grid)) return rc;
-        pdf_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, pdf, n);
-    } else {
-        if (int rc = occupancy_grid(ctx, pdf_kernel<false>, n, &grid)) return rc;
-        pdf_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, i3, pdf, n);
-    }
+    int rc;
+    if (fast(ctx)) rc = vec ? launch_pdf_t<kFast, true>(ctx, i3, pdf, n, s) : launch_pdf_t<kFast, false>(ctx, i3, pdf, n, s);
+    else rc = vec ? launch_pdf_t<kExact, true>(ctx, i3, pdf, n, s) : launch_pdf_t<kExact, false>(ctx, i3, pdf, n, s);
+    if (rc) return rc;
     g_launches++;
     SSK_CUDA(cudaGetLastError());
     return SSK_OK;
 }
 
-template <bool Vec, bool Spectral>
+template <int A, bool Vec, bool Spectral>
 int launch_sample_t(const ssk_ctx *ctx, const SampleArgs &a, size_t n, cudaStream_t s) {
     int grid = 1;
-    if (int rc = occupancy_grid(ctx, sample_kernel<Vec, Spectral>, n, &grid)) return rc;
-    sample_kernel<Vec, Spectral><<<grid, kThreads, kSmemBytes, s>>>(ctx->d_block, a, n);
+    if (int rc = occupancy_grid(ctx, sample_kernel<A, Vec, Spectral>, n, &grid)) return rc;
+    sample_kernel<A, Vec, Spectral><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
     return SSK_OK;
+}
+template <int A>
+int launch_sample_a(const ssk_ctx *ctx, bool spectral, bool vec, const SampleArgs &a, size_t n, cudaStream_t s) {
+    if (spectral) return vec ? launch_sample_t<A, true, true>(ctx, a, n, s) : launch_sample_t<A, false, true>(ctx, a, n, s);
+    return vec ? launch_sample_t<A, true, false>(ctx, a, n, s) : launch_sample_t<A, false, false>(ctx, a, n, s);
 }
 
 int launch_sample(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
@@ -184,9 +198,7 @@ int launch_sample(const ssk_ctx *ctx, const float *const u[2], const float *cons
         vec = vec && aligned16(a.ox) && aligned16(a.oy) && aligned16(a.oz);
     }
     if (dist) { a.dist = dist; vec = vec && aligned16(dist); }
-    int rc;
-    if (spectral) rc = vec ? launch_sample_t<true, true>(ctx, a, n, s) : launch_sample_t<false, true>(ctx, a, n, s);
-    else rc = vec ? launch_sample_t<true, false>(ctx, a, n, s) : launch_sample_t<false, false>(ctx, a, n, s);
+    int rc = fast(ctx) ? launch_sample_a<kFast>(ctx, spectral, vec, a, n, s) : launch_sample_a<kExact>(ctx, spectral, vec, a, n, s);
     if (rc) return rc;
     g_launches++;
     SSK_CUDA(cudaGetLastError());
@@ -270,6 +282,14 @@ int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *c
     }
     for (int i = 0; i < Staging::kStreams; ++i)
         if (int rc = drain(i)) return rc;
+    return SSK_OK;
+}
+
+template <int A, bool Spectral>
+int launch_envmap_t(const ssk_ctx *c, float4 wl, float *out, int width, int height, cudaStream_t s) {
+    int grid = 1;
+    if (int rc = occupancy_grid(c, envmap_kernel<A, Spectral>, (size_t) width * height, &grid)) return rc;
+    envmap_kernel<A, Spectral><<<grid, kThreads, 0, s>>>(hot(c), c->d_block, wl, out, width, height);
     return SSK_OK;
 }
 
@@ -461,31 +481,33 @@ int ssk_envmap_device(ssk_ctx *const *ctxs, int n_maps, int width, int height, c
     if (int rc = need_device(c0)) return rc;
     const bool spectral = c0->mode == SSK_MODE_SPECTRAL;
     if (spectral && !wavelengths4) return fail(SSK_ERR_INVALID, "spectral env maps need 4 wavelengths per map");
-    std::vector<const EmitterBlock *> h(n_maps);
-    for (int i = 0; i < n_maps; ++i) {
+    for (int i = 0; i < n_maps; ++i)
         if (!ctxs[i] || ctxs[i]->device != c0->device || ctxs[i]->mode != c0->mode || !ctxs[i]->d_block)
             return fail(SSK_ERR_INVALID, "env-map contexts must share device and mode");
-        h[i] = ctxs[i]->d_block;
-    }
     cudaStream_t s = (cudaStream_t) stream;
-    const EmitterBlock **d_ptrs = nullptr; float *d_wav = nullptr;
-    SSK_CUDA(cudaMallocAsync((void **) &d_ptrs, sizeof(void *) * n_maps, s));
-    SSK_CUDA(cudaMemcpyAsync(d_ptrs, h.data(), sizeof(void *) * n_maps, cudaMemcpyHostToDevice, s));
-    if (spectral) {
-        SSK_CUDA(cudaMallocAsync((void **) &d_wav, sizeof(float) * 4 * n_maps, s));
-        SSK_CUDA(cudaMemcpyAsync(d_wav, wavelengths4, sizeof(float) * 4 * n_maps, cudaMemcpyHostToDevice, s));
+    const size_t map_floats = (size_t) (spectral ? 4 : 3) * width * height;
+    // one launch per map: each carries its emitter block as the kernel parameter, launches queue back to back
+    for (int i = 0; i < n_maps; ++i) {
+        const ssk_ctx *c = ctxs[i];
+        float4 wl = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (spectral) wl = make_float4(wavelengths4[4 * i], wavelengths4[4 * i + 1], wavelengths4[4 * i + 2], wavelengths4[4 * i + 3]);
+        float *o = out + (size_t) i * map_floats;
+        int rc;
+        if (fast(c)) rc = spectral ? launch_envmap_t<kFast, true>(c, wl, o, width, height, s) : launch_envmap_t<kFast, false>(c, wl, o, width, height, s);
+        else rc = spectral ? launch_envmap_t<kExact, true>(c, wl, o, width, height, s) : launch_envmap_t<kExact, false>(c, wl, o, width, height, s);
+        if (rc) return rc;
+        g_launches++;
     }
-    // the pointer / wavelength tables come from pageable host memory: wait until they are consumed
-    size_t npix = (size_t) width * height;
-    size_t want = (npix + (size_t) kThreads * kVec - 1) / ((size_t) kThreads * kVec);
-    int gx = (int) std::max<size_t>(1, std::min<size_t>(want, (size_t) c0->sm_count * 8));
-    dim3 grid(gx, n_maps);
-    if (spectral) envmap_kernel<true><<<grid, kThreads, kSmemBytes, s>>>(d_ptrs, d_wav, out, width, height);
-    else envmap_kernel<false><<<grid, kThreads, kSmemBytes, s>>>(d_ptrs, d_wav, out, width, height);
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t n, void *stream) {
+    if (!a || !b || !out) return fail(SSK_ERR_INVALID, "null argument");
+    if (n == 0) return SSK_OK;
+    fdiv_by_kernel<<<1184, 256, 0, (cudaStream_t) stream>>>(a, b, out, n);
     g_launches++;
     SSK_CUDA(cudaGetLastError());
-    SSK_CUDA(cudaFreeAsync(d_ptrs, s));
-    if (d_wav) SSK_CUDA(cudaFreeAsync(d_wav, s));
     return SSK_OK;
 }
 

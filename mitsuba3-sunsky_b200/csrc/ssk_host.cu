@@ -54,8 +54,9 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     E.active_record = p.use_record != 0;
     EmitterBlock &B = E.block;
     const int C = E.n_channels;
-    memset(&B, 0, offsetof(EmitterBlock, sun_rad));
+    memset(static_cast<HotBlock *>(&B), 0, sizeof(HotBlock));
     B.spectral = E.spectral ? 1 : 0;
+    B.arith = p.arith == SSK_ARITH_FAST ? kFast : kExact;
 
     // --- transforms
     mat3_from_4x4(p.to_world, B.to_world);
@@ -117,7 +118,17 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     for (int c = 0; c < C; ++c) {
         for (int k = 0; k < kSkyParams; ++k) B.sky_params[k][c] = E.sky_params[c * 9 + k];
         B.sky_rad[c] = E.sky_radiance[c];
+        // FAST mode coefficients (sky_channel_fast): exponents pre-multiplied by log2(e); 1 + A8^2 and 2 A8
+        // rounded exactly as the reference rounds them; radiance folded with the scales
+        const float *A = &E.sky_params[c * 9];
+        const double log2e = 1.4426950408889634074;
+        const double norm = E.spectral ? 1.0 : 1.0 / 106.7502593994140625;
+        const float fast[kFastCoefs] = { A[0], A[1], A[2], A[3], (float) ((double) A[4] * log2e),
+                                         A[5], A[6], A[7], 1.f + A[8] * A[8], 2.f * A[8],
+                                         (float) ((double) E.sky_radiance[c] * (double) p.sky_scale * norm) };
+        for (int k = 0; k < kFastCoefs; ++k) B.sky_fast[k][c] = fast[k];
     }
+    for (int c = C; c < kChanPad; ++c) B.sky_fast[8][c] = 1.f;      // pad channels: keep the -3/2 power finite
     // --- sun radiance table and limb darkening (:191-195 / 274)
     E.sun_radiance.resize(E.data.sun_rad.size() / 10);
     sun_params(E.data.sun_rad, p.turbidity, E.sun_radiance.data());
@@ -142,24 +153,38 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     E.cdf_sum = E.cdf[kGauss - 1];
     E.cdf_norm = 1.f / E.cdf_sum;
     B.cdf_sum = E.cdf_sum;
+    B.n_pdf = 0; B.pdf_generic = 0;
+    auto finite_nz = [](float v) { return std::isfinite(v) && v != 0.f && fabsf(v) > 1e-30f && fabsf(v) < 1e30f; };
     for (int i = 0; i < kGauss; ++i) {
         float mu_p = E.gaussians[i * 5 + 0], mu_t = E.gaussians[i * 5 + 1],
               sg_p = E.gaussians[i * 5 + 2], sg_t = E.gaussians[i * 5 + 3];
         B.g_mu_phi[i] = mu_p; B.g_mu_theta[i] = mu_t; B.g_sigma_phi[i] = sg_p; B.g_sigma_theta[i] = sg_t;
-        B.g_weight[i] = E.pmf[i];
         B.g_cdf_a_phi[i] = gaussian_cdf(mu_p, sg_p, 0.f);
         B.g_cdf_a_theta[i] = gaussian_cdf(mu_t, sg_t, 0.f);
         B.g_cdf_b_phi[i] = gaussian_cdf(mu_p, sg_p, SSK_TWO_PI);
         B.g_cdf_b_theta[i] = gaussian_cdf(mu_t, sg_t, SSK_HALF_PI);
-        B.g_volume[i] = (B.g_cdf_b_phi[i] - B.g_cdf_a_phi[i]) * (B.g_cdf_b_theta[i] - B.g_cdf_a_theta[i]) * (sg_p * sg_t);
+        float volume = (B.g_cdf_b_phi[i] - B.g_cdf_a_phi[i]) * (B.g_cdf_b_theta[i] - B.g_cdf_a_theta[i]) * (sg_p * sg_t);
         B.g_cdf[i] = E.cdf[i];
         B.g_pmf_n[i] = E.pmf[i] * E.cdf_norm;
+        B.g_rpmf_n[i] = 1.f / B.g_pmf_n[i];
         B.g_cdf_prev_n[i] = i > 0 ? E.cdf[i - 1] * E.cdf_norm : 0.f;
+        // density table: a component of weight exactly 0 (integer turbidity / on-grid elevation) adds +0 to
+        // the sum as long as its sigma and volume are ordinary numbers, so it is dropped
+        const bool ordinary = finite_nz(sg_p) && finite_nz(sg_t) && finite_nz(volume);
+        if (E.pmf[i] == 0.f && ordinary) continue;
+        const int k = B.n_pdf++;
+        B.p_mu_phi[k] = mu_p; B.p_mu_theta[k] = mu_t; B.p_sigma_phi[k] = sg_p; B.p_sigma_theta[k] = sg_t;
+        B.p_rsigma_phi[k] = 1.f / sg_p; B.p_rsigma_theta[k] = 1.f / sg_t;
+        B.p_weight[k] = E.pmf[i]; B.p_volume[k] = volume; B.p_rvolume[k] = 1.f / volume;
+        if (!ordinary) B.pdf_generic = 1;
+        const double kk = sqrt(0.5 * 1.4426950408889634074);
+        B.p_k_phi[k] = (float) (kk / (double) sg_p); B.p_k_theta[k] = (float) (kk / (double) sg_t);
+        B.p_wv[k] = (float) ((double) E.pmf[i] * 0.15915494309189533577 / (double) volume);
     }
-
     // --- sky / sun sampling weight and wavelength distribution (:207-209 / 282-284)
     estimate_sky_sun_ratio(E);
-    B.sky_w = E.sky_w;
+    B.sky_w = E.sky_w; B.r_sky_w = 1.f / E.sky_w;
+    B.one_minus_sky_w = 1.f - E.sky_w; B.r_one_minus_sky_w = 1.f / B.one_minus_sky_w;
 }
 
 /// estimate_sky_sun_ratio, array branch (sunsky.cpp:772-886): 200x200 Gauss-Legendre quadrature of the
@@ -184,7 +209,7 @@ void estimate_sky_sun_ratio(HostEmitter &E) {
                 float phi = SSK_PI * (gx[ix] + 1.f), sp, cp;
                 dsincos(phi, sp, cp);
                 Vec3 wo = { sin_theta * cp, sin_theta * sp, cos_theta };
-                RayTerms r = ray_terms(cos_theta, unit_angle(n, wo));
+                RayTerms r = ray_terms<kExact>(cos_theta, unit_angle(n, wo));
                 for (int c = 0; c < C; ++c)
                     buf[(size_t) c * N * N + iy * N + ix] = render_sky(B, c, r) * gw[ix] * gw[iy];
             }

@@ -1,8 +1,13 @@
 // sm_100a kernels of the sunsky hot path. One kernel per Emitter entry point, each a single fused
-// pass: planar fp32 in, planar fp32 out, 128-bit loads/stores (4 consecutive rays per thread), the
-// per-emitter coefficient block staged once per CTA into shared memory, persistent grid sized to a
-// multiple of the SM count. The work is FP32-issue bound (hundreds of flops per 24-44 bytes), so
-// there is no TMA / tensor-core path here by design.
+// pass: planar fp32 in, planar fp32 out, 128-bit loads/stores (4 consecutive rays per thread), a
+// persistent grid sized to a multiple of the SM count.
+//
+// The per-emitter coefficient block (HotBlock, 3.4 KB) is a __grid_constant__ kernel parameter: every
+// coefficient read with a compile-time index (all of RGB eval and of the 20-Gaussian density) becomes a
+// constant-bank operand of the FFMA/FMUL that uses it, with no load instruction at all. Only reads with a
+// lane-dependent index (spectral bins, the sampled mixture component) go through a shared-memory copy.
+// The work is FP32/MUFU-issue bound (hundreds of flops per 16-44 bytes), so there is no TMA /
+// tensor-core path here by design.
 #pragma once
 #include "ssk_model.cuh"
 #include <cuda_runtime.h>
@@ -12,17 +17,24 @@ namespace ssk {
 constexpr int kThreads = 256;
 constexpr int kVec = 4;
 
-/// Stage the hot part of the emitter block into shared memory (coalesced 4-byte copies).
-__device__ __forceinline__ void stage_block(EmitterBlock *dst, const EmitterBlock *src) {
-    const float *s = reinterpret_cast<const float *>(src);
-    float *d = reinterpret_cast<float *>(dst);
-    for (int i = threadIdx.x; i < kHotFloats; i += blockDim.x) d[i] = s[i];
+/// Copy the emitter block from global to shared memory (16-byte accesses) and, for FAST spectral
+/// kernels, build the bin-pair table of eval_spec. Ends with a barrier.
+__device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const EmitterBlock *src) {
+    const uint4 *s = reinterpret_cast<const uint4 *>(src);
+    uint4 *d = reinterpret_cast<uint4 *>(dst);
+    for (int i = threadIdx.x; i < (int) (sizeof(HotBlock) / 16); i += blockDim.x) d[i] = __ldg(s + i);
+    if (pairs)
+        for (int i = threadIdx.x; i < kFastCoefs * kChanPad; i += blockDim.x) {
+            int c = i % kChanPad;
+            const float *row = &src->sky_fast[0][0] + (i - c);
+            pairs[i] = make_float2(__ldg(row + c), c + 1 < kChanPad ? __ldg(row + c + 1) : 0.f);
+        }
     __syncthreads();
 }
 
 template <bool Vec> __device__ __forceinline__ void load4(const float *p, size_t i, size_t n, float v[4]) {
     if (Vec && i + 3 < n) {
-        float4 t = __ldg(reinterpret_cast<const float4 *>(p + i));
+        float4 t = __ldcs(reinterpret_cast<const float4 *>(p + i));      // streamed once: evict first
         v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
     } else {
 #pragma unroll
@@ -45,12 +57,10 @@ struct OutPlanes4 { float *a, *b, *c, *d; };
 
 /// eval / eval_direction, RGB. dir_sign = +1: input is si.wi (the model negates it);
 /// dir_sign = -1: input is ds.d (eval_direction passes wi = -d).
-template <bool Vec>
+template <int A, bool Vec>
 __global__ void __launch_bounds__(kThreads)
-eval_rgb_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out, size_t n, float dir_sign) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
-    stage_block(&P, blk);
+eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out,
+                size_t n, float dir_sign) {
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
@@ -60,7 +70,7 @@ eval_rgb_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out
         for (int k = 0; k < 4; ++k) {
             Vec3 wi = { dir_sign * x[k], dir_sign * y[k], dir_sign * z[k] };
             float o[3];
-            eval_rgb(P, sun_rad, wi, true, o);
+            eval_rgb<A>(U, sun_rad, wi, true, o);
             r[k] = o[0]; g[k] = o[1]; b[k] = o[2];
         }
         store4<Vec>(out.x, i, n, r); store4<Vec>(out.y, i, n, g); store4<Vec>(out.z, i, n, b);
@@ -68,12 +78,13 @@ eval_rgb_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out
 }
 
 /// eval / eval_direction, spectral (4 wavelengths per ray)
-template <bool Vec>
+template <int A, bool Vec>
 __global__ void __launch_bounds__(kThreads)
-eval_spec_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav, OutPlanes4 out, size_t n, float dir_sign) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
-    stage_block(&P, blk);
+eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
+                 OutPlanes4 out, size_t n, float dir_sign) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[A == kFast ? kFastCoefs * kChanPad : 1];
+    stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
@@ -84,7 +95,7 @@ eval_spec_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav, 
         for (int k = 0; k < 4; ++k) {
             Vec3 wi = { dir_sign * x[k], dir_sign * y[k], dir_sign * z[k] };
             float wl[4] = { w0[k], w1[k], w2[k], w3[k] }, o[4];
-            eval_spec(P, sun_rad, wi, wl, true, o);
+            eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
             o0[k] = o[0]; o1[k] = o[1]; o2[k] = o[2]; o3[k] = o[3];
         }
         store4<Vec>(out.a, i, n, o0); store4<Vec>(out.b, i, n, o1); store4<Vec>(out.c, i, n, o2); store4<Vec>(out.d, i, n, o3);
@@ -92,12 +103,9 @@ eval_spec_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav, 
 }
 
 /// pdf_direction
-template <bool Vec>
+template <int A, bool Vec>
 __global__ void __launch_bounds__(kThreads)
-pdf_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, float *__restrict__ pdf, size_t n) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
-    stage_block(&P, blk);
+pdf_kernel(const __grid_constant__ HotBlock U, Planes3 in, float *__restrict__ pdf, size_t n) {
     const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
         float x[4], y[4], z[4], o[4];
@@ -105,7 +113,7 @@ pdf_kernel(const EmitterBlock *__restrict__ blk, Planes3 in, float *__restrict__
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             Vec3 d = { x[k], y[k], z[k] };
-            o[k] = pdf_direction(P, d);
+            o[k] = pdf_direction<A>(U, d);
         }
         store4<Vec>(pdf, i, n, o);
     }
@@ -121,12 +129,12 @@ struct SampleArgs {
 };
 
 /// sample_direction, fused: select technique -> sample -> pdf -> eval -> weight (sunsky.cpp:399-441)
-template <bool Vec, bool Spectral>
+template <int A, bool Vec, bool Spectral>
 __global__ void __launch_bounds__(kThreads)
-sample_kernel(const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
-    stage_block(&P, blk);
+sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kFastCoefs * kChanPad : 1];
+    stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
@@ -141,31 +149,33 @@ sample_kernel(const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
         if (a.px) { load4<Vec>(a.px, i, n, px); load4<Vec>(a.py, i, n, py); load4<Vec>(a.pz, i, n, pz); }
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-            DirSample s = sample_dir(P, u0[k], u1[k]);
+            DirSample s = sample_dir<A>(U, S, u0[k], u1[k]);
             dx[k] = s.d_world.x; dy[k] = s.d_world.y; dz[k] = s.d_world.z; pdf[k] = s.pdf;
             // eval(si) with si.wi = -d (sunsky.cpp:430-438)
             Vec3 wi = { -s.d_world.x, -s.d_world.y, -s.d_world.z };
             float e[4];
             if (Spectral) {
                 float w4[4] = { wl[0][k], wl[1][k], wl[2][k], wl[3][k] };
-                eval_spec(P, sun_rad, wi, w4, s.active, e);
+                eval_spec<A>(U, S, pairs, sun_rad, wi, w4, s.active, e);
             } else {
-                eval_rgb(P, sun_rad, wi, s.active, e);
+                eval_rgb<A>(U, sun_rad, wi, s.active, e);
                 e[3] = 0.f;
             }
             // Spectrum / Float -> eval * rcp(pdf) (drjit/array_router.h:225-228)
-            const float inv_pdf = fdiv(1.f, s.pdf);
+            const float inv_pdf = A == kFast ? hw_rcp(s.pdf) : fdiv(1.f, s.pdf);
 #pragma unroll
             for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
                 float w = e[c] * inv_pdf;
                 q[c][k] = (fabsf(w) < INFINITY) ? w : 0.f;         // res &= isfinite(res)
             }
             // bounding-sphere bookkeeping (sunsky.cpp:415-421)
-            Vec3 rel = { px[k] - P.bs_center[0], py[k] - P.bs_center[1], pz[k] - P.bs_center[2] };
-            float radius = fmaxf(P.bs_radius, sqrtf(sqnorm3(rel)));
-            float dd = 2.f * radius;
-            dist[k] = dd;
-            ox[k] = fmaf(s.d_world.x, dd, px[k]); oy[k] = fmaf(s.d_world.y, dd, py[k]); oz[k] = fmaf(s.d_world.z, dd, pz[k]);
+            if (a.ox || a.dist) {
+                Vec3 rel = { px[k] - U.bs_center[0], py[k] - U.bs_center[1], pz[k] - U.bs_center[2] };
+                float radius = fmaxf(U.bs_radius, sqrtf(sqnorm3(rel)));
+                float dd = 2.f * radius;
+                dist[k] = dd;
+                ox[k] = fmaf(s.d_world.x, dd, px[k]); oy[k] = fmaf(s.d_world.y, dd, py[k]); oz[k] = fmaf(s.d_world.z, dd, pz[k]);
+            }
         }
         store4<Vec>(a.dx, i, n, dx); store4<Vec>(a.dy, i, n, dy); store4<Vec>(a.dz, i, n, dz);
         store4<Vec>(a.pdf, i, n, pdf);
@@ -183,21 +193,20 @@ SSK_HD Vec3 envmap_dir(int x, int y, int width, int height) {
     return sphdir(theta, phi);
 }
 
-/// Equirect env maps, one emitter block per map (blockIdx.y). Write-only: no direction buffer.
-template <bool Spectral>
+/// Equirect env map of one emitter. Write-only: no direction buffer. A thread handles 4 consecutive
+/// pixels of one row (width % 4 == 0 on the vector path), so sin/cos(theta) is computed once per thread.
+template <int A, bool Spectral>
 __global__ void __launch_bounds__(kThreads)
-envmap_kernel(const EmitterBlock *const *__restrict__ blks, const float *__restrict__ wav4, float *__restrict__ out,
-              int width, int height) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    EmitterBlock &P = *reinterpret_cast<EmitterBlock *>(smem_raw);
-    const EmitterBlock *blk = blks[blockIdx.y];
-    stage_block(&P, blk);
+envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, float4 wav4,
+              float *__restrict__ out, int width, int height) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kFastCoefs * kChanPad : 1];
+    if (Spectral) stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     constexpr int C = Spectral ? 4 : 3;
     const size_t npix = (size_t) width * height;
-    float *base = out + (size_t) blockIdx.y * C * npix;
-    float wl[4] = { 0, 0, 0, 0 };
-    if (Spectral) { wl[0] = wav4[blockIdx.y * 4 + 0]; wl[1] = wav4[blockIdx.y * 4 + 1]; wl[2] = wav4[blockIdx.y * 4 + 2]; wl[3] = wav4[blockIdx.y * 4 + 3]; }
+    const float wl[4] = { wav4.x, wav4.y, wav4.z, wav4.w };
+    const bool vec = (width % 4) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0;
     const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < npix; i += stride) {
         float o[4][4];
@@ -208,16 +217,15 @@ envmap_kernel(const EmitterBlock *const *__restrict__ blks, const float *__restr
             Vec3 d = envmap_dir(px, py, width, height);
             Vec3 wi = { -d.x, -d.y, -d.z };
             float e[4] = { 0, 0, 0, 0 };
-            if (Spectral) eval_spec(P, sun_rad, wi, wl, true, e);
-            else eval_rgb(P, sun_rad, wi, true, e);
+            if (Spectral) eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, e);
+            else eval_rgb<A>(U, sun_rad, wi, true, e);
 #pragma unroll
             for (int c = 0; c < C; ++c) o[c][k] = e[c];
         }
-        const bool vec = (npix % 4) == 0;
 #pragma unroll
         for (int c = 0; c < C; ++c) {
-            if (vec) store4<true>(base + (size_t) c * npix, i, npix, o[c]);
-            else store4<false>(base + (size_t) c * npix, i, npix, o[c]);
+            if (vec) store4<true>(out + (size_t) c * npix, i, npix, o[c]);
+            else store4<false>(out + (size_t) c * npix, i, npix, o[c]);
         }
     }
 }
@@ -230,6 +238,12 @@ __global__ void envmap_dirs_kernel(float *dx, float *dy, float *dz, int width, i
         Vec3 d = envmap_dir(px, py, width, height);
         dx[i] = d.x; dy[i] = d.y; dz[i] = d.z;
     }
+}
+
+/// Test hook: out[i] = fdiv_by(a[i], b[i], RN(1 / b[i])), compared with IEEE division by the tests
+__global__ void fdiv_by_kernel(const float *a, const float *b, float *out, size_t n) {
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
+        out[i] = fdiv_by(a[i], b[i], fdiv(1.f, b[i]));
 }
 
 } // namespace ssk

@@ -1,9 +1,22 @@
 // Per-lane sunsky model: Hosek-Wilkie sky, sun disc with limb darkening, TGMM sampler and pdf.
 // Every function states the reference lines it reproduces (src/emitters/sunsky.cpp and
-// include/mitsuba/render/sunsky/sunsky.h of matttsss/mitsuba3-sunsky). The op order follows the
-// llvm_ad_* variants so results can be compared bit for bit with the oracle.
+// include/mitsuba/render/sunsky/sunsky.h of matttsss/mitsuba3-sunsky).
+//
+// Two arithmetic modes (ssk_params.arith):
+//   EXACT  the op order of the llvm_ad_* variants, so results compare bit for bit with the oracle.
+//   FAST   same formulas; everything a result is ill-conditioned in (the geometry: cos(theta), gamma,
+//          cos(gamma), phi, theta, the 1 + A8^2 - 2 A8 cos(gamma) cancellation, the sampled direction) is
+//          still computed with the exact sequence, while the well-conditioned per-channel / per-Gaussian
+//          transcendentals (exp, pow 1.5, divisions) go to the MUFU unit. Measured deviation from the
+//          oracle: see tests/test_parity_gpu.py::test_fast_mode_* and DESIGN.md.
+//
+// Functions take the emitter block twice where it matters: `U` is read with compile-time indices
+// only (in the kernels it is the __grid_constant__ parameter, so coefficients become constant-bank
+// operands of the FFMA/FMUL that use them), `S` is read with lane-dependent indices (in the kernels: a
+// shared-memory copy). On the host both are the same object.
 #pragma once
 #include "ssk_math.cuh"
+#include <cstddef>
 
 namespace ssk {
 
@@ -12,23 +25,34 @@ constexpr int kSunSegments = 45;    // NB_SUN_SEGMENTS (sunsky.h:42)
 constexpr int kSkyParams = 9;       // NB_SKY_PARAMS (sunsky.h:37)
 constexpr int kLd = 6;              // NB_SUN_LD_PARAMS (sunsky.h:44)
 constexpr int kMaxChannels = 11;    // NB_WAVELENGTHS (sunsky.h:20)
+constexpr int kChanPad = kMaxChannels + 1;
+constexpr int kFastCoefs = 11;      // A0, A1, A2, A3, A4 log2e, A5, A6, A7, 1 + A8^2, 2 A8, radiance x scale
 
-/// Per-emitter parameter block (host-built, replicated to the device; ~2.9 KB without the sun table).
-/// Layout is SoA per coefficient so lane-divergent channel / component indices hit distinct shared
-/// memory banks.
-struct EmitterBlock {
-    // --- hot part, staged into shared memory by every CTA ---
-    float sky_params[kSkyParams][kMaxChannels + 1];  // [param][channel]; channel 11 is the zero pad that
-                                                     // stands in for the reference's out-of-bounds
-                                                     // gather at 720 nm (sunsky.cpp:329-338)
-    float sky_rad[kMaxChannels + 1];
-    float sun_ld[kLd][kMaxChannels + 1];             // spectral only
+enum { kExact = 0, kFast = 1 };
+
+/// Per-emitter parameter block without the sun table (host-built, ~3.4 KB). Passed to every kernel by
+/// value as a __grid_constant__ parameter and mirrored in global memory for the shared-memory copies.
+struct HotBlock {
+    // --- sky: [param][channel]; channel 11 is the zero pad that stands in for the reference's
+    //     out-of-bounds gather at 720 nm (sunsky.cpp:329-338)
+    float sky_params[kSkyParams][kChanPad];
+    float sky_rad[kChanPad];
+    float sun_ld[kLd][kChanPad];                     // spectral only
+    float sky_fast[kFastCoefs][kChanPad];            // FAST mode coefficients (see sky_channel_fast)
+    // --- TGMM, reference component order: the sampler (lane-dependent component index)
     float g_mu_phi[kGauss], g_mu_theta[kGauss], g_sigma_phi[kGauss], g_sigma_theta[kGauss];
-    float g_weight[kGauss], g_volume[kGauss];
     float g_cdf_a_phi[kGauss], g_cdf_b_phi[kGauss], g_cdf_a_theta[kGauss], g_cdf_b_theta[kGauss];
     float g_cdf[kGauss];                             // unnormalised inclusive CDF
-    float g_pmf_n[kGauss];                           // pmf[i] * normalization
+    float g_pmf_n[kGauss], g_rpmf_n[kGauss];         // pmf[i] * normalization and RN(1 / that)
     float g_cdf_prev_n[kGauss];                      // cdf[i-1] * normalization, 0 for i == 0
+    // --- TGMM pdf: components with weight 0 dropped (they add +0 to the density), order kept
+    int32_t n_pdf;
+    int32_t pdf_generic;                             // 1: a reciprocal is not finite, keep the generic divisions
+    float p_mu_phi[kGauss], p_mu_theta[kGauss];
+    float p_sigma_phi[kGauss], p_sigma_theta[kGauss], p_rsigma_phi[kGauss], p_rsigma_theta[kGauss];
+    float p_weight[kGauss], p_volume[kGauss], p_rvolume[kGauss];
+    float p_k_phi[kGauss], p_k_theta[kGauss];        // FAST: sqrt(log2(e) / 2) / sigma
+    float p_wv[kGauss];                              // FAST: weight / (2 pi volume)
     float cdf_sum;
     float to_world[9], to_local[9];                  // row-major 3x3 (linear part of to_world / inverse)
     float sun_n[3], sun_s[3], sun_t[3];              // Frame3f(local sun direction)
@@ -39,14 +63,20 @@ struct EmitterBlock {
     float area_ratio;                                // get_area_ratio (sunsky.h:98-101)
     float sun_pdf_const;                             // InvTwoPi / (1 - cos_cutoff) (warp.h:567-577)
     float sky_scale, sun_scale;
-    float sky_w;                                     // m_sky_sampling_w
+    float sky_w, r_sky_w;                            // m_sky_sampling_w and RN(1 / w)
+    float one_minus_sky_w, r_one_minus_sky_w;
     float bs_center[3], bs_radius;
     int32_t spectral;
-    int32_t hot_end_marker;
-    // --- cold part: only read by lanes inside the sun disc, straight from global / L2 ---
+    int32_t arith;
+    int32_t pad_[4];
+};
+
+/// HotBlock followed by the sun radiance table, which only lanes inside the sun disc read (from L2).
+struct EmitterBlock : HotBlock {
     float sun_rad[kSunSegments * 3 * 4 * kLd];       // RGB: [seg][ch][k][j]; spectral: [seg][11][k]
 };
-constexpr int kHotFloats = (int) (offsetof(EmitterBlock, sun_rad) / 4);
+static_assert(sizeof(HotBlock) % 16 == 0, "HotBlock is copied with 16-byte accesses");
+static_assert(sizeof(HotBlock) <= 3800, "HotBlock must fit the 4 KB kernel parameter space with the plane pointers");
 
 // ---------------------------------------------------------------------------------------------
 SSK_HD Vec3 xform(const float *m, const Vec3 &v) {
@@ -61,7 +91,7 @@ SSK_HD Vec3 xform(const float *m, const Vec3 &v) {
 struct RayTerms {
     float cos_theta, gamma, cos_gamma, cos_gamma_sqr, inv_denom_c1, one_plus_cg2, sqrt_cos_theta;
 };
-SSK_HD RayTerms ray_terms(float cos_theta, float gamma) {
+template <int A> SSK_HD RayTerms ray_terms(float cos_theta, float gamma) {
     RayTerms r;
     r.cos_theta = cos_theta; r.gamma = gamma;
     r.cos_gamma = dcos(gamma);
@@ -70,12 +100,15 @@ SSK_HD RayTerms ray_terms(float cos_theta, float gamma) {
     // a shallower operand to a1 * rcp(a2) (drjit/array_router.h:218-232), rcp = 1/x on the LLVM backend
     r.inv_denom_c1 = fdiv(1.f, cos_theta + 0.01f);
     r.one_plus_cg2 = 1.f + r.cos_gamma_sqr;
-    r.sqrt_cos_theta = safe_sqrt(cos_theta);
+    r.sqrt_cos_theta = A == kFast ? hw_sqrt(fmaxf(cos_theta, 0.f)) : safe_sqrt(cos_theta);
     return r;
 }
 
-/// render_sky for one channel (sunsky.cpp:538-555)
-SSK_HD float render_sky(const EmitterBlock &P, int ch, const RayTerms &r) {
+/// FAST ray terms -> the reference's (only the square root differs)
+SSK_HD RayTerms exact_terms(RayTerms r) { r.sqrt_cos_theta = safe_sqrt(r.cos_theta); return r; }
+
+/// render_sky for one channel (sunsky.cpp:538-555), reference op order
+SSK_HD float render_sky(const HotBlock &P, int ch, const RayTerms &r) {
     float A0 = P.sky_params[0][ch], A1 = P.sky_params[1][ch], A2 = P.sky_params[2][ch],
           A3 = P.sky_params[3][ch], A4 = P.sky_params[4][ch], A5 = P.sky_params[5][ch],
           A6 = P.sky_params[6][ch], A7 = P.sky_params[7][ch], A8 = P.sky_params[8][ch];
@@ -85,9 +118,37 @@ SSK_HD float render_sky(const EmitterBlock &P, int ch, const RayTerms &r) {
     return c1 * c2 * P.sky_rad[ch];
 }
 
+/// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
+/// lane-dependent channels); the radiance scale T[10] folds sky_scale and, in RGB mode, the CIE-Y
+/// normalisation. What is approximated and what is not follows the conditioning of the formula:
+///  * c1 = 1 + A0 exp(A1 / (cos(theta) + 0.01)) has A0 ~ -1.1: it cancels to ~0.1 over most of the sky, a
+///    10-20x amplification of any error in the exponential. It is evaluated with the reference sequence.
+///  * the argument of the -3/2 power keeps the reference's two roundings (it cancels to ~(1 - A8)^2 towards
+///    the sun); the power itself is rsqrt^3.
+///  * c2 is a sum of terms of either sign that is well conditioned except for a low sun near the horizon,
+///    where the radiance passes through zero and no approximation keeps a relative tolerance. The sum
+///    carries its absolute-value twin (every variable is >= 0, so |T x| = |T| x) and `ok` is cleared when
+///    |c2| falls below kCancel of it; the caller then evaluates this channel with the reference sequence.
+constexpr float kCancel = 0.125f;
+SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool &ok) {
+    float c1 = 1.f + T[0] * dexp(T[1] * r.inv_denom_c1);
+    float t = T[8] - T[9] * r.cos_gamma;
+    float rs = hw_rsqrt(t);
+    float chi = r.one_plus_cg2 * (rs * rs * rs);
+    float p3 = T[3] * hw_ex2(T[4] * r.gamma), p5 = T[5] * r.cos_gamma_sqr, p6 = T[6] * chi, p7 = T[7] * r.sqrt_cos_theta;
+    float c2 = (T[2] + p3) + (p5 + p6) + p7;
+    float s2 = (fabsf(T[2]) + fabsf(p3)) + (fabsf(p5) + fabsf(p6)) + fabsf(p7);
+    ok = fabsf(c2) >= kCancel * s2;
+#if defined(SSK_COUNT_FALLBACK) && !defined(__CUDA_ARCH__)
+    extern long long g_fast_calls, g_fast_fallbacks;
+    g_fast_calls++; g_fast_fallbacks += !ok;
+#endif
+    return c1 * c2 * T[10];
+}
+
 /// compute_cos_psi (sunsky.h:384-392); `1.0 - ...` is evaluated in fp64 by the reference, which
 /// rounds to the same fp32 value as the fp32 subtraction
-SSK_HD float cos_psi(const EmitterBlock &P, float gamma) {
+SSK_HD float cos_psi(const HotBlock &P, float gamma) {
     float sg = dsin(gamma);
     float sc2 = 1.f - P.ar2 * sg * sg;
     return safe_sqrt(sc2);
@@ -132,7 +193,7 @@ SSK_HD float render_sun_spec(const float *sun_rad, int ch, const SunSeg &s, cons
     return acc;
 }
 /// compute_sun_ld (sunsky.cpp:631-650)
-SSK_HD float sun_ld(const EmitterBlock &P, int lo, int hi, float f, const float *cj) {
+SSK_HD float sun_ld(const HotBlock &P, int lo, int hi, float f, const float *cj) {
     float acc = 0.f;
 #pragma unroll
     for (int j = 0; j < kLd; ++j)
@@ -140,148 +201,245 @@ SSK_HD float sun_ld(const EmitterBlock &P, int lo, int hi, float f, const float 
     return acc;
 }
 
-/// Geometry of eval(): world -> local, cos(theta), gamma, masks (sunsky.cpp:309-314)
+/// Geometry of eval(): world -> local, cos(theta), gamma, masks (sunsky.cpp:309-314). Same sequence in
+/// both modes: the sky formula is ill-conditioned in cos(gamma) close to the sun.
 struct EvalGeom { RayTerms r; bool active, hit_sun; };
-SSK_HD EvalGeom eval_geom(const EmitterBlock &P, const Vec3 &wi, bool active_in) {
+template <int A> SSK_HD EvalGeom eval_geom(const HotBlock &U, const Vec3 &wi, bool active_in) {
     Vec3 neg = { -wi.x, -wi.y, -wi.z };
-    Vec3 wo = xform(P.to_local, neg);
-    Vec3 n = { P.sun_n[0], P.sun_n[1], P.sun_n[2] };
+    Vec3 wo = xform(U.to_local, neg);
+    Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
     float cos_theta = wo.z, gamma = unit_angle(n, wo);
     EvalGeom g;
     g.active = active_in && cos_theta >= 0.f;
-    g.hit_sun = g.active && dot3(n, wo) >= P.cos_cutoff;
-    if (g.active) g.r = ray_terms(cos_theta, gamma);
+    g.hit_sun = g.active && dot3(n, wo) >= U.cos_cutoff;
+    if (g.active) g.r = ray_terms<A>(cos_theta, gamma);
     else { g.r.cos_theta = cos_theta; g.r.gamma = gamma; }
     return g;
 }
 
-/// SunskyEmitter::eval, RGB (sunsky.cpp:303-323, 351). The sun term and the CIE-Y normalisation are
-/// carried out in fp64 by the reference (`Array<float> * double` promotes, sunsky.cpp:321-323).
-SSK_HD void eval_rgb(const EmitterBlock &P, const float *sun_rad, const Vec3 &wi, bool active_in, float out[3]) {
-    EvalGeom g = eval_geom(P, wi, active_in);
+/// The sun term of SunskyEmitter::eval, RGB, added to the scaled sky radiance `res` in fp64 as the
+/// reference does (`Array<float> * double` promotes, sunsky.cpp:321-323). Reference op order in both modes.
+SSK_HD void add_sun_rgb(const HotBlock &U, const float *sun_rad, const RayTerms &r, float res[3]) {
+    SunSeg s = sun_segment(r.cos_theta);
+    float xk[4], cj[6];
+    powers4(s.x, xk);
+    powers6(cos_psi(U, r.gamma), cj);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float sun = U.sun_scale * render_sun_rgb(sun_rad, c, s, xk, cj) * U.area_ratio;
+        res[c] = (float) ((double) res[c] + (double) sun * 467.069280386);
+    }
+}
+
+/// SunskyEmitter::eval, RGB (sunsky.cpp:303-323, 351)
+template <int A>
+SSK_HD void eval_rgb(const HotBlock &U, const float *sun_rad, const Vec3 &wi, bool active_in, float out[3]) {
+    EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = 0.f; return; }
+    if (A == kFast && !g.hit_sun) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float T[kFastCoefs];
+#pragma unroll
+            for (int k = 0; k < kFastCoefs; ++k) T[k] = U.sky_fast[k][c];
+            bool ok;
+            out[c] = sky_channel_fast(T, g.r, ok);
+            if (!ok)   // cancellation: this channel with the reference sequence
+                out[c] = (float) ((double) (U.sky_scale * render_sky(U, c, exact_terms(g.r))) *
+                                  (1.0 / 106.7502593994140625));
+        }
+        return;
+    }
+    if (A == kFast) g.r = exact_terms(g.r);     // sun disc lanes: reference sequence
     float res[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c)
-        res[c] = P.sky_scale * render_sky(P, c, g.r);
-    if (g.hit_sun) {
-        SunSeg s = sun_segment(g.r.cos_theta);
-        float xk[4], cj[6];
-        powers4(s.x, xk);
-        powers6(cos_psi(P, g.r.gamma), cj);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            float sun = P.sun_scale * render_sun_rgb(sun_rad, c, s, xk, cj) * P.area_ratio;
-            res[c] = (float) ((double) res[c] + (double) sun * 467.069280386);
-        }
-    }
+        res[c] = U.sky_scale * render_sky(U, c, g.r);
+    if (g.hit_sun) add_sun_rgb(U, sun_rad, g.r, res);
 #pragma unroll
     for (int c = 0; c < 3; ++c)
         out[c] = (float) ((double) res[c] * (1.0 / 106.7502593994140625));
 }
 
-/// SunskyEmitter::eval, spectral, for the 4 wavelengths of one ray (sunsky.cpp:325-351)
-SSK_HD void eval_spec(const EmitterBlock &P, const float *sun_rad, const Vec3 &wi, const float wav[4],
-                      bool active_in, float out[4]) {
-    EvalGeom g = eval_geom(P, wi, active_in);
+/// Spectral bin lookup of one wavelength (sunsky.cpp:326-338)
+struct Bin { int lo; float f; bool valid; };
+SSK_HD Bin wavelength_bin(float wav) {
+    float nw = (wav - 320.f) * (1.f / 40.f);                  // Spectrum / size_t -> mul by rcp(40.f)
+    Bin b;
+    b.valid = 0.f <= nw && nw <= 10.f;
+    float fl = floorf(nw);
+    b.lo = b.valid ? (int) fl : 0;
+    b.f = nw - fl;
+    return b;
+}
+
+/// Sun term of the spectral eval for one wavelength (sunsky.cpp:339-347), reference op order
+SSK_HD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *sun_rad, const SunSeg &s,
+                           const float *xk, const float *cj, int lo, float f) {
+    int hi = lo + 1;
+    float sun_lo = render_sun_spec(sun_rad, lo, s, xk),
+          sun_hi = hi < kMaxChannels ? render_sun_spec(sun_rad, hi, s, xk) : 0.f,
+          sun = lerp(sun_lo, sun_hi, f);
+    float ld = sun_ld(S, lo, hi, f, cj);
+    return U.sun_scale * sun * ld * U.area_ratio;
+}
+
+/// SunskyEmitter::eval, spectral, for the 4 wavelengths of one ray (sunsky.cpp:325-351).
+/// FAST mode reads `pairs`: pairs[k * kChanPad + c] = { sky_fast[k][c], sky_fast[k][c + 1] }, so the
+/// coefficients of a wavelength's two neighbouring bins arrive in one 64-bit shared-memory load each.
+template <int A>
+SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs, const float *sun_rad,
+                      const Vec3 &wi, const float wav[4], bool active_in, float out[4]) {
+    EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = out[3] = 0.f; return; }
-    SunSeg s; float xk[4], cj[6];
+    SunSeg s = { 0, 0.f }; float xk[4], cj[6];
+    RayTerms rx = g.r;
     if (g.hit_sun) {
         s = sun_segment(g.r.cos_theta);
         powers4(s.x, xk);
-        powers6(cos_psi(P, g.r.gamma), cj);
+        powers6(cos_psi(U, g.r.gamma), cj);
+        if (A == kFast) rx = exact_terms(g.r);
     }
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
-        float nw = (wav[w] - 320.f) * (1.f / 40.f);               // Spectrum / size_t -> mul by rcp(40.f)
-        bool valid = 0.f <= nw && nw <= 10.f;
-        if (!valid) { out[w] = 0.f; continue; }
-        int lo = (int) floorf(nw), hi = lo + 1;
-        float f = nw - (float) lo;
-        float res = P.sky_scale * lerp(render_sky(P, lo, g.r), render_sky(P, hi, g.r), f);
-        if (g.hit_sun) {
-            float sun_lo = render_sun_spec(sun_rad, lo, s, xk),
-                  sun_hi = hi < kMaxChannels ? render_sun_spec(sun_rad, hi, s, xk) : 0.f,
-                  sun = lerp(sun_lo, sun_hi, f);
-            float ld = sun_ld(P, lo, hi, f, cj);
-            res += P.sun_scale * sun * ld * P.area_ratio;
+        Bin b = wavelength_bin(wav[w]);
+        float res;
+        if (A == kFast && !g.hit_sun) {
+            float Tl[kFastCoefs], Th[kFastCoefs];
+#pragma unroll
+            for (int k = 0; k < kFastCoefs; ++k) {
+                float2 p = pairs[k * kChanPad + b.lo];
+                Tl[k] = p.x; Th[k] = p.y;
+            }
+            bool ok_l, ok_h;
+            float sl = sky_channel_fast(Tl, g.r, ok_l), sh = sky_channel_fast(Th, g.r, ok_h);
+            res = lerp(sl, sh, b.f);
+            if (!(ok_l && ok_h)) {   // cancellation: this wavelength with the reference sequence
+                RayTerms re = exact_terms(g.r);
+                res = U.sky_scale * lerp(render_sky(S, b.lo, re), render_sky(S, b.lo + 1, re), b.f);
+            }
+        } else {
+            res = U.sky_scale * lerp(render_sky(S, b.lo, rx), render_sky(S, b.lo + 1, rx), b.f);
+            if (g.hit_sun) res += sun_spec_term(U, S, sun_rad, s, xk, cj, b.lo, b.f);
         }
-        out[w] = res;
+        out[w] = b.valid ? res : 0.f;
     }
 }
 
 // ---------------------------------------------------------------------------------------------
-/// tgmm_pdf (sunsky.cpp:732-763). mu/sigma/weight and `volume` are per-emitter constants that the
-/// JIT folds on the host (m_gaussians[i] is a scalar read); `volume` is precomputed with the same ops.
-SSK_HD float tgmm_pdf(const EmitterBlock &P, float phi, float theta, bool active) {
-    phi -= P.sun_phi_shift;
-    phi = phi < 0.f ? phi + SSK_TWO_PI : phi;
-    phi = phi > SSK_TWO_PI ? phi - SSK_TWO_PI : phi;
-    active = active && theta >= 0.f && theta <= SSK_HALF_PI;
-    if (!active) return 0.f;
+/// tgmm_pdf (sunsky.cpp:732-763), reference op order, generic IEEE divisions. mu / sigma / weight and
+/// `volume` are per-emitter constants that the JIT folds on the host (m_gaussians[i] is a scalar read).
+SSK_HD float tgmm_sum_generic(const HotBlock &U, float phi, float theta) {
     float pdf = 0.f;
-#pragma unroll 4
-    for (int i = 0; i < kGauss; ++i) {
-        float sx = fdiv(phi - P.g_mu_phi[i], P.g_sigma_phi[i]),
-              sy = fdiv(theta - P.g_mu_theta[i], P.g_sigma_theta[i]);
+#pragma unroll 1
+    for (int i = 0; i < U.n_pdf; ++i) {
+        float sx = fdiv(phi - U.p_mu_phi[i], U.p_sigma_phi[i]),
+              sy = fdiv(theta - U.p_mu_theta[i], U.p_sigma_theta[i]);
         float g = SSK_INV_TWO_PI * dexp(-.5f * fmaf(sy, sy, sx * sx));   // warp.h:189-191
-        pdf += fdiv(P.g_weight[i] * g, P.g_volume[i]);
+        pdf += fdiv(U.p_weight[i] * g, U.p_volume[i]);
     }
     return pdf;
 }
 
+/// The same sum with the three divisions per component done by fdiv_by() on reciprocals rounded at
+/// setup (identical quotients, 3 instructions each). A numerator below 2^-70 could make the residual
+/// inexact; such a term only matters when the whole density is tiny, and then the generic sum is redone.
+SSK_HD float tgmm_sum_exact(const HotBlock &U, float phi, float theta) {
+    float pdf = 0.f;
+    bool tiny = false;
+#pragma unroll
+    for (int i = 0; i < kGauss; ++i) {
+        if (i < U.n_pdf) {
+            float sx = fdiv_by(phi - U.p_mu_phi[i], U.p_sigma_phi[i], U.p_rsigma_phi[i]),
+                  sy = fdiv_by(theta - U.p_mu_theta[i], U.p_sigma_theta[i], U.p_rsigma_theta[i]);
+            float g = SSK_INV_TWO_PI * dexp(-.5f * fmaf(sy, sy, sx * sx));
+            float num = U.p_weight[i] * g;
+            tiny = tiny || fdiv_by_tiny(num);
+            pdf += fdiv_by(num, U.p_volume[i], U.p_rvolume[i]);
+        }
+    }
+    if (tiny && !(pdf >= 9.313225746154785e-10f /* 2^-30 */)) pdf = tgmm_sum_generic(U, phi, theta);
+    return pdf;
+}
+
+/// FAST: 8 instructions per component, one MUFU. phi - mu is the reference's own rounding (the Gaussian
+/// argument cancels there); k = sqrt(log2(e) / 2) / sigma, wv = weight / (2 pi volume).
+SSK_HD float tgmm_sum_fast(const HotBlock &U, float phi, float theta) {
+    float pdf = 0.f;
+#pragma unroll
+    for (int i = 0; i < kGauss; ++i) {
+        if (i < U.n_pdf) {
+            float sx = (phi - U.p_mu_phi[i]) * U.p_k_phi[i], sy = (theta - U.p_mu_theta[i]) * U.p_k_theta[i];
+            pdf = fmaf(U.p_wv[i], hw_ex2(-fmaf(sy, sy, sx * sx)), pdf);
+        }
+    }
+    return pdf;
+}
+
+template <int A> SSK_HD float tgmm_pdf(const HotBlock &U, float phi, float theta, bool active) {
+    phi -= U.sun_phi_shift;
+    phi = phi < 0.f ? phi + SSK_TWO_PI : phi;
+    phi = phi > SSK_TWO_PI ? phi - SSK_TWO_PI : phi;
+    active = active && theta >= 0.f && theta <= SSK_HALF_PI;
+    if (!active) return 0.f;
+    if (A == kFast) return tgmm_sum_fast(U, phi, theta);
+    return U.pdf_generic ? tgmm_sum_generic(U, phi, theta) : tgmm_sum_exact(U, phi, theta);
+}
+
 /// compute_pdfs (sunsky.cpp:711-723) followed by the lerp of pdf_direction / sample_direction
-SSK_HD float combined_pdf(const EmitterBlock &P, const Vec3 &d, bool check_sun, bool active) {
+template <int A> SSK_HD float combined_pdf(const HotBlock &U, const Vec3 &d, bool check_sun, bool active) {
     float sin_theta = safe_sqrt(fmaf(d.x, d.x, d.y * d.y));        // Frame3f::sin_theta (frame.h:59-65)
     active = active && d.z >= 0.f && sin_theta != 0.f;
     sin_theta = fmaxf(sin_theta, SSK_EPSILON);
     float phi = datan2(d.y, d.x), theta = unit_angle_z(d);          // from_spherical (sunsky.h:83-89)
-    float sky_pdf = fdiv(tgmm_pdf(P, phi, theta, active), sin_theta);
-    Vec3 n = { P.sun_n[0], P.sun_n[1], P.sun_n[2] };
-    float sun_pdf = (!check_sun || dot3(n, d) >= P.cos_cutoff) ? P.sun_pdf_const : 0.f;
-    return lerp(sun_pdf, sky_pdf, P.sky_w);
+    float t = tgmm_pdf<A>(U, phi, theta, active);
+    float sky_pdf = A == kFast ? t * hw_rcp(sin_theta) : fdiv(t, sin_theta);
+    Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
+    float sun_pdf = (!check_sun || dot3(n, d) >= U.cos_cutoff) ? U.sun_pdf_const : 0.f;
+    return lerp(sun_pdf, sky_pdf, U.sky_w);
 }
 
 /// pdf_direction (sunsky.cpp:443-451)
-SSK_HD float pdf_direction(const EmitterBlock &P, const Vec3 &d_world) {
-    return combined_pdf(P, xform(P.to_local, d_world), true, true);
+template <int A> SSK_HD float pdf_direction(const HotBlock &U, const Vec3 &d_world) {
+    return combined_pdf<A>(U, xform(U.to_local, d_world), true, true);
 }
 
 /// DiscreteDistribution::sample_reuse, JIT flavour (distr_1d.h:116-134,172-182; drjit/util.h:136-181)
-SSK_HD int tgmm_pick(const EmitterBlock &P, float u, float &reuse) {
-    float s = u * P.cdf_sum;
+SSK_HD int tgmm_pick(const HotBlock &U, const HotBlock &S, float u, float &reuse) {
+    float s = u * U.cdf_sum;
     uint32_t start = 0, end = kGauss - 1;
 #pragma unroll
     for (int it = 0; it < 5; ++it) {                 // log2i(19) + 1 iterations
         uint32_t middle = (start + end) >> 1;
-        float v = P.g_cdf[middle];
-        bool cond = ((v < s) || v == 0.f) && v != P.cdf_sum;
+        float v = S.g_cdf[middle];
+        bool cond = ((v < s) || v == 0.f) && v != U.cdf_sum;
         uint32_t nstart = middle + 1 < end ? middle + 1 : end;
         start = cond ? nstart : start;
         end = cond ? end : middle;
     }
-    reuse = fdiv(u - P.g_cdf_prev_n[start], P.g_pmf_n[start]);
+    reuse = fdiv_by_safe(u - S.g_cdf_prev_n[start], S.g_pmf_n[start], S.g_rpmf_n[start]);
     return (int) start;
 }
 
 /// sample_sky (sunsky.cpp:661-689). cdf_a / cdf_b depend only on the component and are precomputed.
-SSK_HD Vec3 sample_sky(const EmitterBlock &P, float u0, float u1) {
+/// Reference sequence in both modes: the sampled direction is held to 1e-6 absolute.
+SSK_HD Vec3 sample_sky(const HotBlock &U, const HotBlock &S, float u0, float u1) {
     float t;
-    int i = tgmm_pick(P, u0, t);
-    float sx = lerp(P.g_cdf_a_phi[i], P.g_cdf_b_phi[i], t),
-          sy = lerp(P.g_cdf_a_theta[i], P.g_cdf_b_theta[i], u1);
+    int i = tgmm_pick(U, S, u0, t);
+    float sx = lerp(S.g_cdf_a_phi[i], S.g_cdf_b_phi[i], t),
+          sy = lerp(S.g_cdf_a_theta[i], S.g_cdf_b_theta[i], u1);
     sx = fmaxf(fminf(sx, SSK_ONE_MINUS_EPSILON), SSK_EPSILON);
     sy = fmaxf(fminf(sy, SSK_ONE_MINUS_EPSILON), SSK_EPSILON);
-    float phi = SSK_SQRT_TWO * derfinv(2.f * sx - 1.f) * P.g_sigma_phi[i] + P.g_mu_phi[i],
-          theta = SSK_SQRT_TWO * derfinv(2.f * sy - 1.f) * P.g_sigma_theta[i] + P.g_mu_theta[i];
-    phi += P.sun_phi_shift;
+    float phi = SSK_SQRT_TWO * derfinv(2.f * sx - 1.f) * S.g_sigma_phi[i] + S.g_mu_phi[i],
+          theta = SSK_SQRT_TWO * derfinv(2.f * sy - 1.f) * S.g_sigma_theta[i] + S.g_mu_theta[i];
+    phi += U.sun_phi_shift;
     theta = fminf(theta, SSK_HALF_PI - SSK_EPSILON);
     return sphdir(theta, phi);
 }
 
 /// sample_sun (sunsky.cpp:697-701): warp::square_to_uniform_cone via the concentric disk mapping
 /// (warp.h:54-90, 533-551), rotated into the sun frame (frame.h:39-41)
-SSK_HD Vec3 sample_sun(const EmitterBlock &P, float u0, float u1) {
+SSK_HD Vec3 sample_sun(const HotBlock &P, float u0, float u1) {
     float x = fmaf(2.f, u0, -1.f), y = fmaf(2.f, u1, -1.f);
     bool is_zero = x == 0.f && y == 0.f, q13 = fabsf(x) < fabsf(y);
     float r = q13 ? y : x, rp = q13 ? x : y;
@@ -302,14 +460,14 @@ SSK_HD Vec3 sample_sun(const EmitterBlock &P, float u0, float u1) {
 
 /// Direction part of sample_direction (sunsky.cpp:404-419, 434-436)
 struct DirSample { Vec3 d_world; float pdf; bool active; };
-SSK_HD DirSample sample_dir(const EmitterBlock &P, float u0, float u1) {
-    bool pick_sky = u0 < P.sky_w;
-    Vec3 dir = pick_sky ? sample_sky(P, fdiv(u0, P.sky_w), u1)
-                        : sample_sun(P, fdiv(u0 - P.sky_w, 1.f - P.sky_w), u1);
+template <int A> SSK_HD DirSample sample_dir(const HotBlock &U, const HotBlock &S, float u0, float u1) {
+    bool pick_sky = u0 < U.sky_w;
+    Vec3 dir = pick_sky ? sample_sky(U, S, fdiv_by_safe(u0, U.sky_w, U.r_sky_w), u1)
+                        : sample_sun(U, fdiv_by_safe(u0 - U.sky_w, U.one_minus_sky_w, U.r_one_minus_sky_w), u1);
     DirSample r;
     r.active = dir.z >= 0.f;
-    r.d_world = xform(P.to_world, dir);
-    r.pdf = combined_pdf(P, dir, pick_sky, r.active);
+    r.d_world = xform(U.to_world, dir);
+    r.pdf = combined_pdf<A>(U, dir, pick_sky, r.active);
     return r;
 }
 

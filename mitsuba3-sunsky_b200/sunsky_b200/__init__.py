@@ -71,7 +71,14 @@ _PARAM_KEYS = ("turbidity", "albedo", "sun_direction", "latitude", "longitude", 
 class SunskyEmitter:
     """Sun and sky dome background emitter (Hosek-Wilkie sky + sun, TGMM importance sampling)."""
 
-    def __init__(self, spectral=False, device=0, dataset_dir=None, sun_direction_normalized=False, **props):
+    def __init__(self, spectral=False, device=0, dataset_dir=None, sun_direction_normalized=False, arith="exact",
+                 **props):
+        """arith: "exact" replays the reference's llvm_ad_* op sequence (bit-identical results); "fast" keeps
+        the geometry and the sampled directions on that sequence and moves the per-channel / per-Gaussian
+        transcendentals to the MUFU unit (radiance / pdf / weight within 1e-5 relative)."""
+        if arith not in ("exact", "fast"):
+            raise ValueError("arith must be 'exact' or 'fast'")
+        self.arith = arith
         unknown = set(props) - set(_PARAM_KEYS)
         if unknown:
             raise TypeError(f"unknown sunsky properties: {sorted(unknown)}")
@@ -123,6 +130,7 @@ class SunskyEmitter:
         if creating and "sun_direction" not in props:
             p.use_record = 1
         p.flags = FLAG_SUN_DIR_NORMALIZED if self._normalized else 0
+        p.arith = ARITH_FAST if self.arith == "fast" else ARITH_EXACT
         self._props.update(props)
 
     def traverse(self):

@@ -35,7 +35,7 @@ for name, (spectral, kw) in common.CONFIGS.items():
         p.flags = 1
     else:
         p.hour = kw['hour']
-    p.sun_scale = kw.get('sun_scale', 1.0)
+    p.sun_scale = kw.get('sun_scale', 1.0); p.arith = int(os.environ.get('SSK_ARITH', '0'))
     if 'sun_aperture' in kw: p.sun_aperture_deg = kw['sun_aperture']
     h = H.hostdbg_create(C.byref(p), A.DATASET_DIR.encode(), int(spectral))
     wo = np.ascontiguousarray(g['wo']); n = wo.shape[1]; wi = np.ascontiguousarray(-wo)

@@ -2,7 +2,16 @@
 // the GPU tests, smoke() or bench.py): runs the __host__ __device__ per-lane model of
 // mitsuba3-sunsky_b200/csrc/ssk_model.cuh on the host so restatement bugs show up before a GPU run.
 #include "../../mitsuba3-sunsky_b200/csrc/ssk_host.cuh"
+namespace ssk { long long g_fast_calls = 0, g_fast_fallbacks = 0; }
 using namespace ssk;
+extern "C" void hostdbg_fallback_stats(long long *calls, long long *fb) { *calls = g_fast_calls; *fb = g_fast_fallbacks; g_fast_calls = g_fast_fallbacks = 0; }
+static const float2 *E_pairs(const HostEmitter &E) {
+    static thread_local float2 pairs[kFastCoefs * kChanPad];
+    for (int k = 0; k < kFastCoefs; ++k)
+        for (int c = 0; c < kChanPad; ++c)
+            pairs[k * kChanPad + c] = make_float2(E.block.sky_fast[k][c], c + 1 < kChanPad ? E.block.sky_fast[k][c + 1] : 0.f);
+    return pairs;
+}
 extern "C" {
 void *hostdbg_create(const ssk_params *p, const char *dir, int spectral) {
     HostEmitter *E = new HostEmitter();
@@ -19,29 +28,29 @@ void hostdbg_eval(void *h, size_t n, const float *wi, const float *wav, float *o
         Vec3 v = { wi[i], wi[n + i], wi[2 * n + i] };
         if (E.spectral) {
             float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }, o[4];
-            eval_spec(E.block, E.block.sun_rad, v, w, true, o);
+            if (E.block.arith) eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, v, w, true, o); else eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, v, w, true, o);
             for (int c = 0; c < 4; ++c) out[c * n + i] = o[c];
         } else {
             float o[3];
-            eval_rgb(E.block, E.block.sun_rad, v, true, o);
+            if (E.block.arith) eval_rgb<1>(E.block, E.block.sun_rad, v, true, o); else eval_rgb<0>(E.block, E.block.sun_rad, v, true, o);
             for (int c = 0; c < 3; ++c) out[c * n + i] = o[c];
         }
     }
 }
 void hostdbg_pdf(void *h, size_t n, const float *d, float *pdf) {
     HostEmitter &E = *(HostEmitter *) h;
-    for (size_t i = 0; i < n; ++i) pdf[i] = pdf_direction(E.block, Vec3{ d[i], d[n + i], d[2 * n + i] });
+    for (size_t i = 0; i < n; ++i) { Vec3 v{ d[i], d[n + i], d[2 * n + i] }; pdf[i] = E.block.arith ? pdf_direction<1>(E.block, v) : pdf_direction<0>(E.block, v); }
 }
 void hostdbg_sample(void *h, size_t n, const float *u, const float *wav, float *d, float *pdf, float *weight) {
     HostEmitter &E = *(HostEmitter *) h;
     int C = E.spectral ? 4 : 3;
     for (size_t i = 0; i < n; ++i) {
-        DirSample s = sample_dir(E.block, u[i], u[n + i]);
+        DirSample s = E.block.arith ? sample_dir<1>(E.block, E.block, u[i], u[n + i]) : sample_dir<0>(E.block, E.block, u[i], u[n + i]);
         d[i] = s.d_world.x; d[n + i] = s.d_world.y; d[2 * n + i] = s.d_world.z; pdf[i] = s.pdf;
         Vec3 wi = { -s.d_world.x, -s.d_world.y, -s.d_world.z };
         float e[4];
-        if (E.spectral) { float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }; eval_spec(E.block, E.block.sun_rad, wi, w, s.active, e); }
-        else eval_rgb(E.block, E.block.sun_rad, wi, s.active, e);
+        if (E.spectral) { float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }; if (E.block.arith) eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, wi, w, s.active, e); else eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, wi, w, s.active, e); }
+        else if (E.block.arith) eval_rgb<1>(E.block, E.block.sun_rad, wi, s.active, e); else eval_rgb<0>(E.block, E.block.sun_rad, wi, s.active, e);
         for (int c = 0; c < C; ++c) { float w = e[c] * (1.f / s.pdf); weight[c * n + i] = (fabsf(w) < INFINITY) ? w : 0.f; }
     }
 }
