@@ -29,6 +29,9 @@ N_SAMPLE = 1 << 26          # BASELINE configs[2]: 64M samples
 FLOPS = dict(eval_spectral=1013, eval_rgb=426, pdf=761, sample_rgb=1776)
 BYTES = dict(eval_spectral=44, eval_rgb=24, pdf=16, sample_rgb=36)
 METRIC = "sky+sun radiance Gevals/s (spectral eval, 16M directions)"
+# dram__bytes_read.sum + dram__bytes_write.sum of one eval_spec_kernel launch on 2^24 rays (ncu --set full,
+# profiles/r1_ncu_summary.md); the algorithmic figure is 44 B x 2^24 = 738 MB (part of the output is still in L2)
+NCU_TRAFFIC = {"fast": 698.3e6, "exact": 701.3e6}
 
 
 def peaks():
@@ -167,6 +170,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extra", action="store_true", help="skip the secondary kernels and the CPU baseline")
+    ap.add_argument("--arith", default="fast", choices=["fast", "exact"],
+                    help="arithmetic mode of the headline kernel: fast (within 1e-5 of the reference, default) or exact "
+                         "(bit-identical to the reference)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -223,27 +229,38 @@ def main():
         return max_over_ranks(ev0.elapsed_time(ev1)), ssk.launch_count() - l0
 
     kw = emitter_kwargs()
-    em_spec = ssk.SunskyEmitter(spectral=True, device=local, **kw)
-    em_rgb = ssk.SunskyEmitter(spectral=False, device=local, **kw)
     pk = peaks()
     sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
     fp32_peak = sm_count * 128 * 2 * pk["sm_max_mhz"] * 1e6 / 1e12          # TFLOP/s at max SM clock
-
-    # ---- headline: spectral eval, inputs resident in HBM ------------------------------------------
-    wo = hemisphere(N_EVAL); wi = (-wo).contiguous()
-    wav = (360.0 + 360.0 * torch.rand((4, N_EVAL), device=dev, generator=gen)).clamp_(max=719.99).contiguous()
-    out = torch.empty((4, N_EVAL), device=dev)
     import ctypes as C
     from sunsky_b200 import _capi
+    import common
+    L = _capi.lib()
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
     def planes(t):
         arr = (_capi.FP * t.shape[0])()
         for i in range(t.shape[0]):
             arr[i] = C.cast(t[i].data_ptr(), _capi.FP)
         return arr
-    L = _capi.lib()
+
+    def fp(t):
+        return C.cast(t.data_ptr(), _capi.FP)
+
+    # ---- inputs, resident in HBM ----------------------------------------------------------------------
+    wo = hemisphere(N_EVAL); wi = (-wo).contiguous()
+    wav = (360.0 + 360.0 * torch.rand((4, N_EVAL), device=dev, generator=gen)).clamp_(max=719.99).contiguous()
+    out = torch.empty((4, N_EVAL), device=dev)
     wi_pp, wo_pp, wav_pp, out_pp = planes(wi), planes(wo), planes(wav), planes(out)
-    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def rate(ms_total, steps, n, key):
+        r = world * n / (ms_total / steps * 1e-3) / 1e9
+        return {"value": r, "unit": "G/s", "ms": ms_total / steps,
+                "fp32_frac": r / world * 1e9 * FLOPS[key] / 1e12 / fp32_peak,
+                "hbm_gbs": r / world * BYTES[key], "hbm_frac": r / world * BYTES[key] / pk["hbm_gbs"]}
+
+    # ---- headline: spectral eval (configs[1]) in the arithmetic mode under test --------------------------
+    em_spec = ssk.SunskyEmitter(spectral=True, device=local, arith=args.arith, **kw)
 
     def step_eval():
         rc = L.ssk_eval_device(em_spec._ctx, wi_pp, wav_pp, N_EVAL, out_pp, stream)
@@ -257,9 +274,12 @@ def main():
     per_gpu = value / world
     achieved_tf = per_gpu * 1e9 * FLOPS["eval_spectral"] / 1e12
     roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
-                "frac": achieved_tf / fp32_peak, "traffic": None,
-                "peak_source": f"{sm_count} SMs x 128 lanes x 2 flop x {pk['sm_max_mhz']:.0f} MHz ({pk['source']} max SM clock)",
-                "kernel": "eval_spec_kernel", "flops_per_eval": FLOPS["eval_spectral"],
+                "frac": achieved_tf / fp32_peak, "traffic": NCU_TRAFFIC.get(args.arith),
+                "peak_source": f"{sm_count} SMs x 128 lanes x 2 flop x {pk['sm_max_mhz']:.0f} MHz ({pk['source']} max SM clock); "
+                               "not a tensor-core path",
+                "kernel": f"eval_spec_kernel<{args.arith}>", "flops_per_eval": FLOPS["eval_spectral"],
+                "flops_note": "algorithmic flops of the reference op sequence (SURVEY.md 8d), not executed instructions",
+                "traffic_note": "dram read+write bytes per launch from the ncu capture under profiles/ (algorithmic: 738 MB)",
                 "hbm": {"achieved": per_gpu * BYTES["eval_spectral"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": per_gpu * BYTES["eval_spectral"] / pk["hbm_gbs"], "bytes_per_eval": BYTES["eval_spectral"]}}
 
@@ -275,9 +295,11 @@ def main():
         assert rc == 0, L.ssk_last_error()
 
     e2e_steps = max(3, min(args.steps, 20))
-    step_e2e()
+    for _ in range(2):
+        step_e2e()
     barrier()
     t0 = time.perf_counter()
+    l0 = ssk.launch_count()
     for _ in range(e2e_steps):
         step_e2e()
     barrier()
@@ -285,48 +307,63 @@ def main():
     e2e_s = (windows[-1][1] - t0) / e2e_steps
     e2e_ms = max_over_ranks(e2e_s * 1e3)
     e2e = {"value": world * n_e2e / (e2e_ms * 1e-3) / 1e9, "unit": "Gevals/s",
-           "h2d_bytes_per_step": 7 * 4 * n_e2e, "d2h_bytes_per_step": 4 * 4 * n_e2e, "ms_per_step": e2e_ms}
+           "h2d_bytes_per_step": 7 * 4 * n_e2e, "d2h_bytes_per_step": 4 * 4 * n_e2e, "ms_per_step": e2e_ms,
+           "launches_per_step": (ssk.launch_count() - l0) // e2e_steps,
+           "pcie_gbs": (7 + 4) * 4 * n_e2e / (e2e_ms * 1e-3) / 1e9,
+           "note": "ssk_eval_host: pinned host planes, 1 Mi-ray chunks over 3 streams, H2D + kernel + D2H inside the timed region"}
     del h_wi, h_wav, h_out
 
-    # ---- the other kernels of the path ---------------------------------------------------------------
+    # ---- the other kernels of the path, both arithmetic modes ----------------------------------------------
     extra = {}
     if not args.no_extra:
-        def rate(ms_total, steps, n, key):
-            r = world * n / (ms_total / steps * 1e-3) / 1e9
-            return {"value": r, "unit": "G/s", "ms": ms_total / steps,
-                    "fp32_frac": r / world * 1e9 * FLOPS[key] / 1e12 / fp32_peak,
-                    "hbm_gbs": r / world * BYTES[key]}
-        out3 = torch.empty((3, N_EVAL), device=dev)
-        o3_pp = planes(out3)
-
-        def step_rgb():
-            assert L.ssk_eval_device(em_rgb._ctx, wi_pp, None, N_EVAL, o3_pp, stream) == 0
-        ms_r, _ = timed(step_rgb, args.steps, warm)
-        extra["eval_rgb_Gevals_s"] = rate(ms_r, args.steps, N_EVAL, "eval_rgb")
+        out3 = torch.empty((3, N_EVAL), device=dev); o3_pp = planes(out3)
         pdf = torch.empty(N_EVAL, device=dev)
-
-        def step_pdf():
-            assert L.ssk_pdf_direction_device(em_rgb._ctx, wo_pp, N_EVAL, C.cast(pdf.data_ptr(), _capi.FP), stream) == 0
-        ms_p, _ = timed(step_pdf, args.steps, warm)
-        extra["pdf_direction_Gpdf_s"] = rate(ms_p, args.steps, N_EVAL, "pdf")
-        del out, out3, wav, pdf
-        # configs[2]: fused TGMM sample + pdf + eval + weight on 2^26 samples (t=6, a=0.5, eta=50.2 deg)
-        import common
-        em_s = ssk.SunskyEmitter(spectral=False, device=local, turbidity=6.0, albedo=0.5,
-                                 sun_direction=common.sun_dir_from_elevation(50.2))
         u = torch.rand((2, N_SAMPLE), device=dev, generator=gen)
         d = torch.empty((3, N_SAMPLE), device=dev); spdf = torch.empty(N_SAMPLE, device=dev)
         wgt = torch.empty((3, N_SAMPLE), device=dev)
         u_pp, d_pp, w_pp = planes(u), planes(d), planes(wgt)
+        s_steps = max(3, args.steps // 10)
+        for mode in ("fast", "exact"):
+            ex = {}
+            es = ssk.SunskyEmitter(spectral=True, device=local, arith=mode, **kw)
+            er = ssk.SunskyEmitter(spectral=False, device=local, arith=mode, **kw)
+            # configs[2] = sunsky-testing/sampling_test.py: t=6, a=0.5, eta=50.2 deg, sky only; and its sun+sky twin
+            kw3 = dict(turbidity=6.0, albedo=0.5, sun_direction=common.sun_dir_from_elevation(50.2))
+            e_sky = ssk.SunskyEmitter(spectral=False, device=local, arith=mode, sun_scale=0.0, **kw3)
+            e_sun = ssk.SunskyEmitter(spectral=False, device=local, arith=mode, **kw3)
 
-        def step_sample():
-            assert L.ssk_sample_direction_device(em_s._ctx, u_pp, None, None, N_SAMPLE, d_pp,
-                                                 C.cast(spdf.data_ptr(), _capi.FP), w_pp, None, None, stream) == 0
-        s_steps = max(3, args.steps // 4)
-        ms_s, _ = timed(step_sample, s_steps, 3)
-        extra["sample_direction_Gsamples_s"] = rate(ms_s, s_steps, N_SAMPLE, "sample_rgb")
-        extra["sample_direction_lower_hemisphere"] = int((d[2] < 0).sum().item())
-        del u, d, spdf, wgt
+            def step_spec():
+                assert L.ssk_eval_device(es._ctx, wi_pp, wav_pp, N_EVAL, out_pp, stream) == 0
+
+            def step_rgb():
+                assert L.ssk_eval_device(er._ctx, wi_pp, None, N_EVAL, o3_pp, stream) == 0
+
+            def step_pdf():
+                assert L.ssk_pdf_direction_device(er._ctx, wo_pp, N_EVAL, fp(pdf), stream) == 0
+
+            def step_sample(e):
+                def f():
+                    assert L.ssk_sample_direction_device(e._ctx, u_pp, None, None, N_SAMPLE, d_pp, fp(spdf), w_pp,
+                                                         None, None, stream) == 0
+                return f
+            if mode != args.arith:
+                ms_x, _ = timed(step_spec, args.steps, warm)
+                ex["eval_spectral_Gevals_s"] = rate(ms_x, args.steps, N_EVAL, "eval_spectral")
+            ms_r, _ = timed(step_rgb, args.steps, warm)
+            ex["eval_rgb_Gevals_s"] = rate(ms_r, args.steps, N_EVAL, "eval_rgb")
+            ms_p, _ = timed(step_pdf, args.steps, warm)
+            ex["pdf_direction_Gpdf_s"] = rate(ms_p, args.steps, N_EVAL, "pdf")
+            ms_s, _ = timed(step_sample(e_sky), s_steps, 3)
+            ex["sample_direction_sky_only_Gsamples_s"] = rate(ms_s, s_steps, N_SAMPLE, "sample_rgb")
+            ex["sample_direction_lower_hemisphere"] = int((d[2] < 0).sum().item())      # sampling_test.py:36-44
+            ms_s, _ = timed(step_sample(e_sun), s_steps, 3)
+            ex["sample_direction_sun_and_sky_Gsamples_s"] = rate(ms_s, s_steps, N_SAMPLE, "sample_rgb")
+            extra[mode] = ex
+            for e in (es, er, e_sky, e_sun):
+                e.close()
+        extra["note"] = ("configs[1] inputs for eval/pdf (2^24 directions), configs[2] for sample_direction (2^26 samples, "
+                         "t=6 a=0.5 eta=50.2deg; sky only = sampling_test.py). fp32_frac uses the algorithmic flops of SURVEY 8d.")
+        del out3, pdf, u, d, spdf, wgt
 
     # ---- CPU baseline: the reference's own CPU code on the box's host cores (rank 0, N = 1 only) -------
     cpu = None
@@ -357,7 +394,10 @@ def main():
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths per GPU, "
                                    "t=3 a=0.3 eta=30deg, sun+sky",
-                       "l2": "inputs (470 MB/step) exceed the 126 MB L2; no flush needed", "arith": "exact (reference op order)"},
+                       "l2": "inputs (470 MB/step) exceed the 126 MB L2; no flush needed",
+                       "arith": args.arith + (" (MUFU transcendentals for well-conditioned terms, within 1e-5 of the reference; "
+                                              "directions bit-identical)" if args.arith == "fast" else
+                                              " (reference op order, bit-identical results)")},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
             "extra": extra,
         }))

@@ -50,6 +50,17 @@ template <bool Vec> __device__ __forceinline__ void store4(float *p, size_t i, s
     }
 }
 
+/// Element k of a 4-vector held in registers, k not known at compile time (3 selects, no local memory).
+/// The per-ray body is deliberately NOT unrolled over the 4 rays of a thread: unrolled, the kernels grow to
+/// 14-30 k instructions and stall on instruction fetch (ncu: `no_instructions` was the top stall reason).
+__device__ __forceinline__ float getk(const float v[4], int k) {
+    float a = k & 1 ? v[1] : v[0], b = k & 1 ? v[3] : v[2];
+    return k & 2 ? b : a;
+}
+__device__ __forceinline__ void setk(float v[4], int k, float x) {
+    v[0] = k == 0 ? x : v[0]; v[1] = k == 1 ? x : v[1]; v[2] = k == 2 ? x : v[2]; v[3] = k == 3 ? x : v[3];
+}
+
 struct Planes3 { const float *x, *y, *z; };
 struct Planes4 { const float *a, *b, *c, *d; };
 struct OutPlanes3 { float *x, *y, *z; };
@@ -66,12 +77,12 @@ eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restri
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
         float x[4], y[4], z[4], r[4], g[4], b[4];
         load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < 4; ++k) {
-            Vec3 wi = { dir_sign * x[k], dir_sign * y[k], dir_sign * z[k] };
+            Vec3 wi = { dir_sign * getk(x, k), dir_sign * getk(y, k), dir_sign * getk(z, k) };
             float o[3];
             eval_rgb<A>(U, sun_rad, wi, true, o);
-            r[k] = o[0]; g[k] = o[1]; b[k] = o[2];
+            setk(r, k, o[0]); setk(g, k, o[1]); setk(b, k, o[2]);
         }
         store4<Vec>(out.x, i, n, r); store4<Vec>(out.y, i, n, g); store4<Vec>(out.z, i, n, b);
     }
@@ -91,12 +102,12 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
         float x[4], y[4], z[4], w0[4], w1[4], w2[4], w3[4], o0[4], o1[4], o2[4], o3[4];
         load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
         load4<Vec>(wav.a, i, n, w0); load4<Vec>(wav.b, i, n, w1); load4<Vec>(wav.c, i, n, w2); load4<Vec>(wav.d, i, n, w3);
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < 4; ++k) {
-            Vec3 wi = { dir_sign * x[k], dir_sign * y[k], dir_sign * z[k] };
-            float wl[4] = { w0[k], w1[k], w2[k], w3[k] }, o[4];
+            Vec3 wi = { dir_sign * getk(x, k), dir_sign * getk(y, k), dir_sign * getk(z, k) };
+            float wl[4] = { getk(w0, k), getk(w1, k), getk(w2, k), getk(w3, k) }, o[4];
             eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
-            o0[k] = o[0]; o1[k] = o[1]; o2[k] = o[2]; o3[k] = o[3];
+            setk(o0, k, o[0]); setk(o1, k, o[1]); setk(o2, k, o[2]); setk(o3, k, o[3]);
         }
         store4<Vec>(out.a, i, n, o0); store4<Vec>(out.b, i, n, o1); store4<Vec>(out.c, i, n, o2); store4<Vec>(out.d, i, n, o3);
     }
@@ -110,10 +121,10 @@ pdf_kernel(const __grid_constant__ HotBlock U, Planes3 in, float *__restrict__ p
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
         float x[4], y[4], z[4], o[4];
         load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < 4; ++k) {
-            Vec3 d = { x[k], y[k], z[k] };
-            o[k] = pdf_direction<A>(U, d);
+            Vec3 d = { getk(x, k), getk(y, k), getk(z, k) };
+            setk(o, k, pdf_direction<A>(U, d));
         }
         store4<Vec>(pdf, i, n, o);
     }
@@ -140,22 +151,22 @@ sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
         float u0[4], u1[4], wl[4][4], dx[4], dy[4], dz[4], pdf[4], q[4][4];
         float px[4] = { 0, 0, 0, 0 }, py[4] = { 0, 0, 0, 0 }, pz[4] = { 0, 0, 0, 0 };
-        float ox[4], oy[4], oz[4], dist[4];
+        float ox[4] = { 0, 0, 0, 0 }, oy[4] = { 0, 0, 0, 0 }, oz[4] = { 0, 0, 0, 0 }, dist[4] = { 0, 0, 0, 0 };
         load4<Vec>(a.u0, i, n, u0); load4<Vec>(a.u1, i, n, u1);
         if (Spectral) {
             load4<Vec>(a.w0, i, n, wl[0]); load4<Vec>(a.w1, i, n, wl[1]);
             load4<Vec>(a.w2, i, n, wl[2]); load4<Vec>(a.w3, i, n, wl[3]);
         }
         if (a.px) { load4<Vec>(a.px, i, n, px); load4<Vec>(a.py, i, n, py); load4<Vec>(a.pz, i, n, pz); }
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < 4; ++k) {
-            DirSample s = sample_dir<A>(U, S, u0[k], u1[k]);
-            dx[k] = s.d_world.x; dy[k] = s.d_world.y; dz[k] = s.d_world.z; pdf[k] = s.pdf;
+            DirSample s = sample_dir<A>(U, S, getk(u0, k), getk(u1, k));
+            setk(dx, k, s.d_world.x); setk(dy, k, s.d_world.y); setk(dz, k, s.d_world.z); setk(pdf, k, s.pdf);
             // eval(si) with si.wi = -d (sunsky.cpp:430-438)
             Vec3 wi = { -s.d_world.x, -s.d_world.y, -s.d_world.z };
             float e[4];
             if (Spectral) {
-                float w4[4] = { wl[0][k], wl[1][k], wl[2][k], wl[3][k] };
+                float w4[4] = { getk(wl[0], k), getk(wl[1], k), getk(wl[2], k), getk(wl[3], k) };
                 eval_spec<A>(U, S, pairs, sun_rad, wi, w4, s.active, e);
             } else {
                 eval_rgb<A>(U, sun_rad, wi, s.active, e);
@@ -166,15 +177,16 @@ sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
 #pragma unroll
             for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
                 float w = e[c] * inv_pdf;
-                q[c][k] = (fabsf(w) < INFINITY) ? w : 0.f;         // res &= isfinite(res)
+                setk(q[c], k, (fabsf(w) < INFINITY) ? w : 0.f);         // res &= isfinite(res)
             }
             // bounding-sphere bookkeeping (sunsky.cpp:415-421)
             if (a.ox || a.dist) {
-                Vec3 rel = { px[k] - U.bs_center[0], py[k] - U.bs_center[1], pz[k] - U.bs_center[2] };
+                float pxk = getk(px, k), pyk = getk(py, k), pzk = getk(pz, k);
+                Vec3 rel = { pxk - U.bs_center[0], pyk - U.bs_center[1], pzk - U.bs_center[2] };
                 float radius = fmaxf(U.bs_radius, sqrtf(sqnorm3(rel)));
                 float dd = 2.f * radius;
-                dist[k] = dd;
-                ox[k] = fmaf(s.d_world.x, dd, px[k]); oy[k] = fmaf(s.d_world.y, dd, py[k]); oz[k] = fmaf(s.d_world.z, dd, pz[k]);
+                setk(dist, k, dd);
+                setk(ox, k, fmaf(s.d_world.x, dd, pxk)); setk(oy, k, fmaf(s.d_world.y, dd, pyk)); setk(oz, k, fmaf(s.d_world.z, dd, pzk));
             }
         }
         store4<Vec>(a.dx, i, n, dx); store4<Vec>(a.dy, i, n, dy); store4<Vec>(a.dz, i, n, dz);
@@ -210,7 +222,7 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
     const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < npix; i += stride) {
         float o[4][4];
-#pragma unroll
+#pragma unroll 1
         for (int k = 0; k < 4; ++k) {
             size_t pix = i + k < npix ? i + k : npix - 1;
             int py = (int) (pix / (size_t) width), px = (int) (pix - (size_t) py * width);
@@ -220,7 +232,7 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
             if (Spectral) eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, e);
             else eval_rgb<A>(U, sun_rad, wi, true, e);
 #pragma unroll
-            for (int c = 0; c < C; ++c) o[c][k] = e[c];
+            for (int c = 0; c < C; ++c) setk(o[c], k, e[c]);
         }
 #pragma unroll
         for (int c = 0; c < C; ++c) {

@@ -75,7 +75,7 @@ struct HotBlock {
 struct EmitterBlock : HotBlock {
     float sun_rad[kSunSegments * 3 * 4 * kLd];       // RGB: [seg][ch][k][j]; spectral: [seg][11][k]
 };
-static_assert(sizeof(HotBlock) % 16 == 0, "HotBlock is copied with 16-byte accesses");
+static_assert(sizeof(HotBlock) % 16 == 0, "HotBlock is copied with 16-byte accesses; sun_rad must start 16-byte aligned");
 static_assert(sizeof(HotBlock) <= 3800, "HotBlock must fit the 4 KB kernel parameter space with the plane pointers");
 
 // ---------------------------------------------------------------------------------------------
@@ -104,6 +104,9 @@ template <int A> SSK_HD RayTerms ray_terms(float cos_theta, float gamma) {
     return r;
 }
 
+/// render_sky behind a call: the cancellation fallback of FAST mode and the sun-disc lanes
+SSK_COLD float render_sky_cold(const HotBlock &P, int ch, RayTerms r);
+
 /// FAST ray terms -> the reference's (only the square root differs)
 SSK_HD RayTerms exact_terms(RayTerms r) { r.sqrt_cos_theta = safe_sqrt(r.cos_theta); return r; }
 
@@ -117,6 +120,8 @@ SSK_HD float render_sky(const HotBlock &P, int ch, const RayTerms &r) {
     float c2 = A2 + A3 * dexp(A4 * r.gamma) + A5 * r.cos_gamma_sqr + A6 * chi + A7 * r.sqrt_cos_theta;
     return c1 * c2 * P.sky_rad[ch];
 }
+
+SSK_COLD float render_sky_cold(const HotBlock &P, int ch, RayTerms r) { return render_sky(P, ch, r); }
 
 /// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
 /// lane-dependent channels); the radiance scale T[10] folds sky_scale and, in RGB mode, the CIE-Y
@@ -172,24 +177,41 @@ SSK_HD void powers6(float c, float *p) {
     p[0] = 1.f; p[1] = c; p[2] = c2; p[3] = c * c2; p[4] = c4; p[5] = c * c4;
 }
 
-/// render_sun, RGB branch (sunsky.cpp:597-611)
+/// render_sun, RGB branch (sunsky.cpp:597-611). The 24 coefficients of a (segment, channel) pair are
+/// contiguous and 16-byte aligned: six 128-bit loads.
 SSK_HD float render_sun_rgb(const float *sun_rad, int ch, const SunSeg &s, const float *xk, const float *cj) {
     const float *S = sun_rad + s.pos * (3 * 4 * kLd) + ch * (4 * kLd);
+    float c[4 * kLd];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+        float4 v = __ldg(reinterpret_cast<const float4 *>(S) + q);
+        c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+    }
+#else
+    for (int q = 0; q < 4 * kLd; ++q) c[q] = S[q];
+#endif
     float acc = 0.f;
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
         for (int j = 0; j < kLd; ++j)
-            acc += xk[k] * cj[j] * S[k * kLd + j];
+            acc += xk[k] * cj[j] * c[k * kLd + j];
     return acc;
 }
-/// render_sun, spectral branch (sunsky.cpp:590-596)
+/// render_sun, spectral branch (sunsky.cpp:590-596): one 128-bit load per (segment, wavelength bin)
 SSK_HD float render_sun_spec(const float *sun_rad, int ch, const SunSeg &s, const float *xk) {
     const float *S = sun_rad + s.pos * (kMaxChannels * 4) + ch * 4;
+#if defined(__CUDA_ARCH__)
+    float4 v = __ldg(reinterpret_cast<const float4 *>(S));
+    const float c[4] = { v.x, v.y, v.z, v.w };
+#else
+    const float c[4] = { S[0], S[1], S[2], S[3] };
+#endif
     float acc = 0.f;
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-        acc += xk[k] * S[k];
+        acc += xk[k] * c[k];
     return acc;
 }
 /// compute_sun_ld (sunsky.cpp:631-650)
@@ -219,7 +241,7 @@ template <int A> SSK_HD EvalGeom eval_geom(const HotBlock &U, const Vec3 &wi, bo
 
 /// The sun term of SunskyEmitter::eval, RGB, added to the scaled sky radiance `res` in fp64 as the
 /// reference does (`Array<float> * double` promotes, sunsky.cpp:321-323). Reference op order in both modes.
-SSK_HD void add_sun_rgb(const HotBlock &U, const float *sun_rad, const RayTerms &r, float res[3]) {
+SSK_COLD void add_sun_rgb(const HotBlock &U, const float *sun_rad, const RayTerms &r, float res[3]) {
     SunSeg s = sun_segment(r.cos_theta);
     float xk[4], cj[6];
     powers4(s.x, xk);
@@ -245,7 +267,7 @@ SSK_HD void eval_rgb(const HotBlock &U, const float *sun_rad, const Vec3 &wi, bo
             bool ok;
             out[c] = sky_channel_fast(T, g.r, ok);
             if (!ok)   // cancellation: this channel with the reference sequence
-                out[c] = (float) ((double) (U.sky_scale * render_sky(U, c, exact_terms(g.r))) *
+                out[c] = (float) ((double) (U.sky_scale * render_sky_cold(U, c, exact_terms(g.r))) *
                                   (1.0 / 106.7502593994140625));
         }
         return;
@@ -274,7 +296,7 @@ SSK_HD Bin wavelength_bin(float wav) {
 }
 
 /// Sun term of the spectral eval for one wavelength (sunsky.cpp:339-347), reference op order
-SSK_HD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *sun_rad, const SunSeg &s,
+SSK_COLD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *sun_rad, const SunSeg &s,
                            const float *xk, const float *cj, int lo, float f) {
     int hi = lo + 1;
     float sun_lo = render_sun_spec(sun_rad, lo, s, xk),
@@ -316,7 +338,7 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
             res = lerp(sl, sh, b.f);
             if (!(ok_l && ok_h)) {   // cancellation: this wavelength with the reference sequence
                 RayTerms re = exact_terms(g.r);
-                res = U.sky_scale * lerp(render_sky(S, b.lo, re), render_sky(S, b.lo + 1, re), b.f);
+                res = U.sky_scale * lerp(render_sky_cold(S, b.lo, re), render_sky_cold(S, b.lo + 1, re), b.f);
             }
         } else {
             res = U.sky_scale * lerp(render_sky(S, b.lo, rx), render_sky(S, b.lo + 1, rx), b.f);
@@ -329,7 +351,7 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
 // ---------------------------------------------------------------------------------------------
 /// tgmm_pdf (sunsky.cpp:732-763), reference op order, generic IEEE divisions. mu / sigma / weight and
 /// `volume` are per-emitter constants that the JIT folds on the host (m_gaussians[i] is a scalar read).
-SSK_HD float tgmm_sum_generic(const HotBlock &U, float phi, float theta) {
+SSK_COLD float tgmm_sum_generic(const HotBlock &U, float phi, float theta) {
     float pdf = 0.f;
 #pragma unroll 1
     for (int i = 0; i < U.n_pdf; ++i) {

@@ -40,11 +40,13 @@ def main():
     kw3 = dict(turbidity=6.0, albedo=0.5, sun_direction=common.sun_dir_from_elevation(50.2), **extra)
     es, er = ssk.SunskyEmitter(spectral=True, **kw), ssk.SunskyEmitter(spectral=False, **kw)
     ss, sr = ssk.SunskyEmitter(spectral=True, **kw3), ssk.SunskyEmitter(spectral=False, **kw3)
+    sky = ssk.SunskyEmitter(spectral=False, sun_scale=0.0, **kw3)
     runs = {
         "eval_spec": lambda: es.eval(wi, wav),
         "eval_rgb": lambda: er.eval(wi),
         "pdf": lambda: er.pdf_direction(wo),
         "sample_rgb": lambda: sr.sample_direction(u),
+        "sample_sky": lambda: sky.sample_direction(u),
         "sample_spec": lambda: ss.sample_direction(u, None, wav),
         "envmap": lambda: ssk.envmaps([er], 4096, 2048),
     }
