@@ -1,5 +1,6 @@
 // sm_100a kernels of the sunsky hot path. One kernel per Emitter entry point, each a single fused
-// pass: planar fp32 in, planar fp32 out, 128-bit loads/stores (4 consecutive rays per thread), a
+// pass: planar fp32 in, planar fp32 out, 128-bit loads/stores (4 consecutive rays per thread; the
+// many-plane sampling kernel moves one ray per thread to stay within 2 resident CTAs' registers), a
 // persistent grid sized to a multiple of the SM count.
 //
 // The per-emitter coefficient block (HotBlock, 3.4 KB) is a __grid_constant__ kernel parameter: every
@@ -15,7 +16,6 @@
 namespace ssk {
 
 constexpr int kThreads = 256;
-constexpr int kVec = 4;
 
 /// Copy the emitter block from global to shared memory (16-byte accesses) and, for FAST spectral
 /// kernels, build the bin-pair table of eval_spec. Ends with a barrier.
@@ -32,32 +32,45 @@ __device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const 
     __syncthreads();
 }
 
-template <bool Vec> __device__ __forceinline__ void load4(const float *p, size_t i, size_t n, float v[4]) {
-    if (Vec && i + 3 < n) {
-        float4 t = __ldcs(reinterpret_cast<const float4 *>(p + i));      // streamed once: evict first
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-    } else {
+/// R rays per thread: R = 4 moves 4 consecutive rays with one 128-bit access per plane (planes must be
+/// 16-byte aligned), R = 1 moves one ray with a 32-bit access (a warp still covers one full 128-byte line).
+/// Which one a kernel uses is a register-pressure trade: every plane costs R staging registers per thread.
+template <int R> __device__ __forceinline__ void loadr(const float *p, size_t i, size_t n, float v[4]) {
+    if (R == 4) {
+        if (i + 3 < n) {
+            float4 t = __ldcs(reinterpret_cast<const float4 *>(p + i));      // streamed once: evict first
+            v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+        } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) v[k] = (i + k < n) ? __ldg(p + i + k) : 0.f;
+            for (int k = 0; k < 4; ++k) v[k] = (i + k < n) ? __ldg(p + i + k) : 0.f;
+        }
+    } else {
+        v[0] = __ldcs(p + i);
     }
 }
-template <bool Vec> __device__ __forceinline__ void store4(float *p, size_t i, size_t n, const float v[4]) {
-    if (Vec && i + 3 < n) {
-        __stcs(reinterpret_cast<float4 *>(p + i), make_float4(v[0], v[1], v[2], v[3]));
-    } else {
+template <int R> __device__ __forceinline__ void storer(float *p, size_t i, size_t n, const float v[4]) {
+    if (R == 4) {
+        if (i + 3 < n) {
+            __stcs(reinterpret_cast<float4 *>(p + i), make_float4(v[0], v[1], v[2], v[3]));
+        } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) if (i + k < n) p[i + k] = v[k];
+            for (int k = 0; k < 4; ++k) if (i + k < n) p[i + k] = v[k];
+        }
+    } else {
+        __stcs(p + i, v[0]);
     }
 }
 
 /// Element k of a 4-vector held in registers, k not known at compile time (3 selects, no local memory).
-/// The per-ray body is deliberately NOT unrolled over the 4 rays of a thread: unrolled, the kernels grow to
+/// The per-ray body is deliberately NOT unrolled over the rays of a thread: unrolled, the kernels grow to
 /// 14-30 k instructions and stall on instruction fetch (ncu: `no_instructions` was the top stall reason).
-__device__ __forceinline__ float getk(const float v[4], int k) {
+template <int R> __device__ __forceinline__ float getk(const float v[4], int k) {
+    if (R == 1) return v[0];
     float a = k & 1 ? v[1] : v[0], b = k & 1 ? v[3] : v[2];
     return k & 2 ? b : a;
 }
-__device__ __forceinline__ void setk(float v[4], int k, float x) {
+template <int R> __device__ __forceinline__ void setk(float v[4], int k, float x) {
+    if (R == 1) { v[0] = x; return; }
     v[0] = k == 0 ? x : v[0]; v[1] = k == 1 ? x : v[1]; v[2] = k == 2 ? x : v[2]; v[3] = k == 3 ? x : v[3];
 }
 
@@ -68,28 +81,28 @@ struct OutPlanes4 { float *a, *b, *c, *d; };
 
 /// eval / eval_direction, RGB. dir_sign = +1: input is si.wi (the model negates it);
 /// dir_sign = -1: input is ds.d (eval_direction passes wi = -d).
-template <int A, bool Vec>
+template <int A, int R>
 __global__ void __launch_bounds__(kThreads)
 eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out,
                 size_t n, float dir_sign) {
     const float *sun_rad = blk->sun_rad;
-    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+    const size_t stride = (size_t) gridDim.x * blockDim.x * R;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
         float x[4], y[4], z[4], r[4], g[4], b[4];
-        load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
+        loadr<R>(in.x, i, n, x); loadr<R>(in.y, i, n, y); loadr<R>(in.z, i, n, z);
 #pragma unroll 1
-        for (int k = 0; k < 4; ++k) {
-            Vec3 wi = { dir_sign * getk(x, k), dir_sign * getk(y, k), dir_sign * getk(z, k) };
+        for (int k = 0; k < R; ++k) {
+            Vec3 wi = { dir_sign * getk<R>(x, k), dir_sign * getk<R>(y, k), dir_sign * getk<R>(z, k) };
             float o[3];
             eval_rgb<A>(U, sun_rad, wi, true, o);
-            setk(r, k, o[0]); setk(g, k, o[1]); setk(b, k, o[2]);
+            setk<R>(r, k, o[0]); setk<R>(g, k, o[1]); setk<R>(b, k, o[2]);
         }
-        store4<Vec>(out.x, i, n, r); store4<Vec>(out.y, i, n, g); store4<Vec>(out.z, i, n, b);
+        storer<R>(out.x, i, n, r); storer<R>(out.y, i, n, g); storer<R>(out.z, i, n, b);
     }
 }
 
 /// eval / eval_direction, spectral (4 wavelengths per ray)
-template <int A, bool Vec>
+template <int A, int R>
 __global__ void __launch_bounds__(kThreads)
 eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
                  OutPlanes4 out, size_t n, float dir_sign) {
@@ -97,36 +110,36 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
     __shared__ __align__(16) float2 pairs[A == kFast ? kFastCoefs * kChanPad : 1];
     stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
-    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+    const size_t stride = (size_t) gridDim.x * blockDim.x * R;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
         float x[4], y[4], z[4], w0[4], w1[4], w2[4], w3[4], o0[4], o1[4], o2[4], o3[4];
-        load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
-        load4<Vec>(wav.a, i, n, w0); load4<Vec>(wav.b, i, n, w1); load4<Vec>(wav.c, i, n, w2); load4<Vec>(wav.d, i, n, w3);
+        loadr<R>(in.x, i, n, x); loadr<R>(in.y, i, n, y); loadr<R>(in.z, i, n, z);
+        loadr<R>(wav.a, i, n, w0); loadr<R>(wav.b, i, n, w1); loadr<R>(wav.c, i, n, w2); loadr<R>(wav.d, i, n, w3);
 #pragma unroll 1
-        for (int k = 0; k < 4; ++k) {
-            Vec3 wi = { dir_sign * getk(x, k), dir_sign * getk(y, k), dir_sign * getk(z, k) };
-            float wl[4] = { getk(w0, k), getk(w1, k), getk(w2, k), getk(w3, k) }, o[4];
+        for (int k = 0; k < R; ++k) {
+            Vec3 wi = { dir_sign * getk<R>(x, k), dir_sign * getk<R>(y, k), dir_sign * getk<R>(z, k) };
+            float wl[4] = { getk<R>(w0, k), getk<R>(w1, k), getk<R>(w2, k), getk<R>(w3, k) }, o[4];
             eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
-            setk(o0, k, o[0]); setk(o1, k, o[1]); setk(o2, k, o[2]); setk(o3, k, o[3]);
+            setk<R>(o0, k, o[0]); setk<R>(o1, k, o[1]); setk<R>(o2, k, o[2]); setk<R>(o3, k, o[3]);
         }
-        store4<Vec>(out.a, i, n, o0); store4<Vec>(out.b, i, n, o1); store4<Vec>(out.c, i, n, o2); store4<Vec>(out.d, i, n, o3);
+        storer<R>(out.a, i, n, o0); storer<R>(out.b, i, n, o1); storer<R>(out.c, i, n, o2); storer<R>(out.d, i, n, o3);
     }
 }
 
 /// pdf_direction
-template <int A, bool Vec>
+template <int A, int R>
 __global__ void __launch_bounds__(kThreads)
 pdf_kernel(const __grid_constant__ HotBlock U, Planes3 in, float *__restrict__ pdf, size_t n) {
-    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+    const size_t stride = (size_t) gridDim.x * blockDim.x * R;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
         float x[4], y[4], z[4], o[4];
-        load4<Vec>(in.x, i, n, x); load4<Vec>(in.y, i, n, y); load4<Vec>(in.z, i, n, z);
+        loadr<R>(in.x, i, n, x); loadr<R>(in.y, i, n, y); loadr<R>(in.z, i, n, z);
 #pragma unroll 1
-        for (int k = 0; k < 4; ++k) {
-            Vec3 d = { getk(x, k), getk(y, k), getk(z, k) };
-            setk(o, k, pdf_direction<A>(U, d));
+        for (int k = 0; k < R; ++k) {
+            Vec3 d = { getk<R>(x, k), getk<R>(y, k), getk<R>(z, k) };
+            setk<R>(o, k, pdf_direction<A>(U, d));
         }
-        store4<Vec>(pdf, i, n, o);
+        storer<R>(pdf, i, n, o);
     }
 }
 
@@ -140,33 +153,33 @@ struct SampleArgs {
 };
 
 /// sample_direction, fused: select technique -> sample -> pdf -> eval -> weight (sunsky.cpp:399-441)
-template <int A, bool Vec, bool Spectral>
+template <int A, int R, bool Spectral>
 __global__ void __launch_bounds__(kThreads)
 sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
     __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kFastCoefs * kChanPad : 1];
     stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
-    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < n; i += stride) {
+    const size_t stride = (size_t) gridDim.x * blockDim.x * R;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
         float u0[4], u1[4], wl[4][4], dx[4], dy[4], dz[4], pdf[4], q[4][4];
         float px[4] = { 0, 0, 0, 0 }, py[4] = { 0, 0, 0, 0 }, pz[4] = { 0, 0, 0, 0 };
         float ox[4] = { 0, 0, 0, 0 }, oy[4] = { 0, 0, 0, 0 }, oz[4] = { 0, 0, 0, 0 }, dist[4] = { 0, 0, 0, 0 };
-        load4<Vec>(a.u0, i, n, u0); load4<Vec>(a.u1, i, n, u1);
+        loadr<R>(a.u0, i, n, u0); loadr<R>(a.u1, i, n, u1);
         if (Spectral) {
-            load4<Vec>(a.w0, i, n, wl[0]); load4<Vec>(a.w1, i, n, wl[1]);
-            load4<Vec>(a.w2, i, n, wl[2]); load4<Vec>(a.w3, i, n, wl[3]);
+            loadr<R>(a.w0, i, n, wl[0]); loadr<R>(a.w1, i, n, wl[1]);
+            loadr<R>(a.w2, i, n, wl[2]); loadr<R>(a.w3, i, n, wl[3]);
         }
-        if (a.px) { load4<Vec>(a.px, i, n, px); load4<Vec>(a.py, i, n, py); load4<Vec>(a.pz, i, n, pz); }
+        if (a.px) { loadr<R>(a.px, i, n, px); loadr<R>(a.py, i, n, py); loadr<R>(a.pz, i, n, pz); }
 #pragma unroll 1
-        for (int k = 0; k < 4; ++k) {
-            DirSample s = sample_dir<A>(U, S, getk(u0, k), getk(u1, k));
-            setk(dx, k, s.d_world.x); setk(dy, k, s.d_world.y); setk(dz, k, s.d_world.z); setk(pdf, k, s.pdf);
+        for (int k = 0; k < R; ++k) {
+            DirSample s = sample_dir<A>(U, S, getk<R>(u0, k), getk<R>(u1, k));
+            setk<R>(dx, k, s.d_world.x); setk<R>(dy, k, s.d_world.y); setk<R>(dz, k, s.d_world.z); setk<R>(pdf, k, s.pdf);
             // eval(si) with si.wi = -d (sunsky.cpp:430-438)
             Vec3 wi = { -s.d_world.x, -s.d_world.y, -s.d_world.z };
             float e[4];
             if (Spectral) {
-                float w4[4] = { getk(wl[0], k), getk(wl[1], k), getk(wl[2], k), getk(wl[3], k) };
+                float w4[4] = { getk<R>(wl[0], k), getk<R>(wl[1], k), getk<R>(wl[2], k), getk<R>(wl[3], k) };
                 eval_spec<A>(U, S, pairs, sun_rad, wi, w4, s.active, e);
             } else {
                 eval_rgb<A>(U, sun_rad, wi, s.active, e);
@@ -177,24 +190,24 @@ sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
 #pragma unroll
             for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
                 float w = e[c] * inv_pdf;
-                setk(q[c], k, (fabsf(w) < INFINITY) ? w : 0.f);         // res &= isfinite(res)
+                setk<R>(q[c], k, (fabsf(w) < INFINITY) ? w : 0.f);         // res &= isfinite(res)
             }
             // bounding-sphere bookkeeping (sunsky.cpp:415-421)
             if (a.ox || a.dist) {
-                float pxk = getk(px, k), pyk = getk(py, k), pzk = getk(pz, k);
+                float pxk = getk<R>(px, k), pyk = getk<R>(py, k), pzk = getk<R>(pz, k);
                 Vec3 rel = { pxk - U.bs_center[0], pyk - U.bs_center[1], pzk - U.bs_center[2] };
                 float radius = fmaxf(U.bs_radius, sqrtf(sqnorm3(rel)));
                 float dd = 2.f * radius;
-                setk(dist, k, dd);
-                setk(ox, k, fmaf(s.d_world.x, dd, pxk)); setk(oy, k, fmaf(s.d_world.y, dd, pyk)); setk(oz, k, fmaf(s.d_world.z, dd, pzk));
+                setk<R>(dist, k, dd);
+                setk<R>(ox, k, fmaf(s.d_world.x, dd, pxk)); setk<R>(oy, k, fmaf(s.d_world.y, dd, pyk)); setk<R>(oz, k, fmaf(s.d_world.z, dd, pzk));
             }
         }
-        store4<Vec>(a.dx, i, n, dx); store4<Vec>(a.dy, i, n, dy); store4<Vec>(a.dz, i, n, dz);
-        store4<Vec>(a.pdf, i, n, pdf);
-        store4<Vec>(a.q0, i, n, q[0]); store4<Vec>(a.q1, i, n, q[1]); store4<Vec>(a.q2, i, n, q[2]);
-        if (Spectral) store4<Vec>(a.q3, i, n, q[3]);
-        if (a.ox) { store4<Vec>(a.ox, i, n, ox); store4<Vec>(a.oy, i, n, oy); store4<Vec>(a.oz, i, n, oz); }
-        if (a.dist) store4<Vec>(a.dist, i, n, dist);
+        storer<R>(a.dx, i, n, dx); storer<R>(a.dy, i, n, dy); storer<R>(a.dz, i, n, dz);
+        storer<R>(a.pdf, i, n, pdf);
+        storer<R>(a.q0, i, n, q[0]); storer<R>(a.q1, i, n, q[1]); storer<R>(a.q2, i, n, q[2]);
+        if (Spectral) storer<R>(a.q3, i, n, q[3]);
+        if (a.ox) { storer<R>(a.ox, i, n, ox); storer<R>(a.oy, i, n, oy); storer<R>(a.oz, i, n, oz); }
+        if (a.dist) storer<R>(a.dist, i, n, dist);
     }
 }
 
@@ -219,8 +232,9 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
     const size_t npix = (size_t) width * height;
     const float wl[4] = { wav4.x, wav4.y, wav4.z, wav4.w };
     const bool vec = (width % 4) == 0 && (reinterpret_cast<uintptr_t>(out) & 15u) == 0;
-    const size_t stride = (size_t) gridDim.x * blockDim.x * kVec;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * kVec; i < npix; i += stride) {
+    constexpr int R = 4;
+    const size_t stride = (size_t) gridDim.x * blockDim.x * R;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < npix; i += stride) {
         float o[4][4];
 #pragma unroll 1
         for (int k = 0; k < 4; ++k) {
@@ -232,12 +246,12 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
             if (Spectral) eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, e);
             else eval_rgb<A>(U, sun_rad, wi, true, e);
 #pragma unroll
-            for (int c = 0; c < C; ++c) setk(o[c], k, e[c]);
+            for (int c = 0; c < C; ++c) setk<R>(o[c], k, e[c]);
         }
 #pragma unroll
         for (int c = 0; c < C; ++c) {
-            if (vec) store4<true>(out + (size_t) c * npix, i, npix, o[c]);
-            else store4<false>(out + (size_t) c * npix, i, npix, o[c]);
+            if (vec) storer<4>(out + (size_t) c * npix, i, npix, o[c]);
+            else for (int k = 0; k < 4; ++k) if (i + k < npix) out[(size_t) c * npix + i + k] = o[c][k];
         }
     }
 }
