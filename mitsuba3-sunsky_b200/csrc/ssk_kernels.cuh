@@ -82,7 +82,7 @@ struct OutPlanes4 { float *a, *b, *c, *d; };
 /// eval / eval_direction, RGB. dir_sign = +1: input is si.wi (the model negates it);
 /// dir_sign = -1: input is ds.d (eval_direction passes wi = -d).
 template <int A, int R>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, R == 1 ? 4 : 3)
 eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out,
                 size_t n, float dir_sign) {
     const float *sun_rad = blk->sun_rad;

@@ -253,12 +253,35 @@ SSK_COLD void add_sun_rgb(const HotBlock &U, const float *sun_rad, const RayTerm
     }
 }
 
+/// Sun-disc lane of SunskyEmitter::eval, RGB, reference sequence from the ray terms on (sunsky.cpp:317-323)
+SSK_COLD void eval_rgb_sun_cold(const HotBlock &U, const float *sun_rad, RayTerms r, float out[3]) {
+    float res[3];
+    for (int c = 0; c < 3; ++c) res[c] = U.sky_scale * render_sky(U, c, r);
+    add_sun_rgb(U, sun_rad, r, res);
+    for (int c = 0; c < 3; ++c) out[c] = (float) ((double) res[c] * (1.0 / 106.7502593994140625));
+}
+
+/// FAST mode, sun-disc lane: normalised sun term on top of the fast sky radiance `sky` (by value in and
+/// out: a pointer argument would push the caller's registers to local memory)
+SSK_COLD Vec3 add_sun_rgb_fast_cold(const HotBlock &U, const float *sun_rad, RayTerms r, Vec3 sky) {
+    float sun[3] = { 0.f, 0.f, 0.f }, out[3] = { sky.x, sky.y, sky.z };
+    add_sun_rgb(U, sun_rad, r, sun);
+    bool ok = true;
+    for (int c = 0; c < 3; ++c) {
+        float sn = (float) ((double) sun[c] * (1.0 / 106.7502593994140625)), sum = out[c] + sn;
+        ok = ok && fabsf(sum) >= kCancel * (fabsf(out[c]) + fabsf(sn));
+        out[c] = sum;
+    }
+    if (!ok) eval_rgb_sun_cold(U, sun_rad, exact_terms(r), out);
+    return { out[0], out[1], out[2] };
+}
+
 /// SunskyEmitter::eval, RGB (sunsky.cpp:303-323, 351)
 template <int A>
 SSK_HD void eval_rgb(const HotBlock &U, const float *sun_rad, const Vec3 &wi, bool active_in, float out[3]) {
     EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = 0.f; return; }
-    if (A == kFast && !g.hit_sun) {
+    if (A == kFast) {
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             float T[kFastCoefs];
@@ -270,9 +293,16 @@ SSK_HD void eval_rgb(const HotBlock &U, const float *sun_rad, const Vec3 &wi, bo
                 out[c] = (float) ((double) (U.sky_scale * render_sky_cold(U, c, exact_terms(g.r))) *
                                   (1.0 / 106.7502593994140625));
         }
+        // sun disc lanes (half of the lanes of sample_direction when the sun is on): the reference's sun
+        // term, normalised, on top of the fast sky. It usually outweighs the sky by 4 orders of magnitude,
+        // but the fitted sun radiance turns negative for a low sun in a turbid atmosphere and can cancel the
+        // sky: such lanes take the reference sequence for all three channels.
+        if (g.hit_sun) {
+            Vec3 v = add_sun_rgb_fast_cold(U, sun_rad, g.r, Vec3{ out[0], out[1], out[2] });
+            out[0] = v.x; out[1] = v.y; out[2] = v.z;
+        }
         return;
     }
-    if (A == kFast) g.r = exact_terms(g.r);     // sun disc lanes: reference sequence
     float res[3];
 #pragma unroll
     for (int c = 0; c < 3; ++c)
@@ -320,13 +350,12 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
         s = sun_segment(g.r.cos_theta);
         powers4(s.x, xk);
         powers6(cos_psi(U, g.r.gamma), cj);
-        if (A == kFast) rx = exact_terms(g.r);
     }
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
         Bin b = wavelength_bin(wav[w]);
         float res;
-        if (A == kFast && !g.hit_sun) {
+        if (A == kFast) {
             float Tl[kFastCoefs], Th[kFastCoefs];
 #pragma unroll
             for (int k = 0; k < kFastCoefs; ++k) {
@@ -342,7 +371,15 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
             }
         } else {
             res = U.sky_scale * lerp(render_sky(S, b.lo, rx), render_sky(S, b.lo + 1, rx), b.f);
-            if (g.hit_sun) res += sun_spec_term(U, S, sun_rad, s, xk, cj, b.lo, b.f);
+        }
+        if (g.hit_sun) {
+            float sun = sun_spec_term(U, S, sun_rad, s, xk, cj, b.lo, b.f), sum = res + sun;
+            if (A == kFast && !(fabsf(sum) >= kCancel * (fabsf(res) + fabsf(sun)))) {
+                // the fitted sun radiance can be negative (low sun, turbid) and cancel the sky: reference sequence
+                RayTerms re = exact_terms(g.r);
+                sum = U.sky_scale * lerp(render_sky_cold(S, b.lo, re), render_sky_cold(S, b.lo + 1, re), b.f) + sun;
+            }
+            res = sum;
         }
         out[w] = b.valid ? res : 0.f;
     }

@@ -304,3 +304,63 @@ def test_fast_mode_matches_golden(ssk, name):
     assert common.bit_equal(d, g["s_d"]), f"{name}: FAST sampled directions are not bit-identical"
     assert_close(pdf, g["s_pdf"], f"{name} fast ds.pdf", exact=False)
     assert_close(w, g["s_weight"], f"{name} fast weight", exact=False)
+
+
+# ---- environment maps and sweeps (BASELINE configs[3], configs[4]) ----------------------------------------
+
+@pytest.mark.parametrize("spectral", [False, True])
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+def test_envmap_equals_eval_of_its_pixel_directions(ssk, spectral, arith):
+    """ssk_envmap_device == eval(wi = -d) at the pixel-centre directions, bit for bit in either mode; the
+    directions follow phi = 2 pi (x + .5) / W, theta = pi (y + .5) / H; odd sizes take the scalar store path."""
+    import torch
+    name = "cfg2_spec" if spectral else "cfg1_rgb"
+    e = emitters.make(ssk, name, g=emitters.golden(name), arith=arith)
+    for (W, H) in ((256, 128), (37, 19)):
+        wl4 = [440.0, 520.0, 600.0, 680.0]
+        img = ssk.envmaps([e], W, H, wl4 if spectral else None)
+        assert img.shape == (1, 4 if spectral else 3, H, W)
+        d = ssk.envmap_directions(e, W, H)
+        xs = (torch.arange(W, device="cuda", dtype=torch.float64) + 0.5) * (2 * np.pi / W)
+        ys = (torch.arange(H, device="cuda", dtype=torch.float64) + 0.5) * (np.pi / H)
+        T, P = torch.meshgrid(ys, xs, indexing="ij")
+        want_d = torch.stack([torch.sin(T) * torch.cos(P), torch.sin(T) * torch.sin(P), torch.cos(T)]).reshape(3, -1)
+        assert float((d.double() - want_d).abs().max()) < 1e-6
+        wav = torch.tensor(wl4, device="cuda").float()[:, None].expand(4, W * H).contiguous() if spectral else None
+        ev = e.eval(-d, wav)
+        assert torch.equal(img[0].reshape(ev.shape[0], -1).view(torch.int32), ev.view(torch.int32))
+        assert float(img[0, :, H // 2 + 1:, :].abs().max()) == 0.0          # below the horizon
+
+
+def test_envmap_against_reference_on_a_strided_subset(ssk, ref):
+    """configs[3]-style map (RGB, low sun) against the reference library on every 61st pixel."""
+    import torch
+    sd = common.sun_dir_from_elevation(90.0 * 5 / 63.0)
+    r = ref.RefEmitter(spectral=False, flavour=1, turbidity=4.0, albedo=0.3, sun_direction=sd)
+    e = ssk.SunskyEmitter(spectral=False, sun_direction_normalized=True, turbidity=4.0, albedo=0.3,
+                          sun_direction=list(r.state().sun_dir_world))
+    W, H = 1024, 512
+    img = ssk.envmaps([e], W, H)[0].reshape(3, -1)
+    d = ssk.envmap_directions(e, W, H)
+    sel = torch.arange(0, W * H, 61, device="cuda")
+    want = r.eval(-d[:, sel].cpu().numpy())
+    assert_close(img[:, sel].cpu().numpy(), want, "envmap vs reference")
+
+
+@pytest.mark.parametrize("config", ["time_of_day", "animation"])
+def test_sweep_sharded_over_ranks_equals_single_rank(ssk, config):
+    """The frames two ranks render (blocked / round-robin split) reassemble to the single-rank sweep."""
+    import torch
+    from sunsky_b200 import sweep, sharding
+    frames = [0, 5, 63, 64, 130, 200, 255] if config == "time_of_day" else [0, 1, 50, 100, 127]
+    W, H = 128, 64
+    idx1, full = sweep.render_sweep(config, W, H, frames=frames)
+    assert idx1 == list(range(len(frames))) and full.shape[0] == len(frames)
+    got = torch.empty_like(full)
+    for rank in range(2):
+        idx, part = sweep.render_sweep(config, W, H, rank=rank, world_size=2, frames=frames, chunk=2)
+        got[idx] = part
+    assert torch.equal(got.view(torch.int32), full.view(torch.int32))
+    assert bool(torch.isfinite(full).all()) and float(full.max()) > 0
+    # eta = 0 and 90 degrees (frames 0 and 63 of the time-of-day sweep) are legal emitters
+    assert len(sharding.sweep_parameters(config)) in (256, 128)
