@@ -122,6 +122,27 @@ SSK_HD float render_sky(const HotBlock &P, int ch, const RayTerms &r) {
 }
 
 SSK_COLD float render_sky_cold(const HotBlock &P, int ch, RayTerms r) { return render_sky(P, ch, r); }
+/// render_sky for channels ch and ch + 1 at once (the two bins a wavelength falls between): the reference
+/// op order on float2, each element bit-identical to render_sky(). The one IEEE division stays per element.
+SSK_HD float2 render_sky_2(const HotBlock &P, int ch, const RayTerms &r) {
+    const float (*A)[kChanPad] = P.sky_params;
+    float2 A0 = f2(A[0][ch], A[0][ch + 1]), A1 = f2(A[1][ch], A[1][ch + 1]), A2 = f2(A[2][ch], A[2][ch + 1]),
+           A3 = f2(A[3][ch], A[3][ch + 1]), A4 = f2(A[4][ch], A[4][ch + 1]), A5 = f2(A[5][ch], A[5][ch + 1]),
+           A6 = f2(A[6][ch], A[6][ch + 1]), A7 = f2(A[7][ch], A[7][ch + 1]), A8 = f2(A[8][ch], A[8][ch + 1]);
+    // every product that feeds a sum goes through add2x (see there: ptxas would contract it otherwise)
+    float2 c1 = add2x(mul2(A0, dexp_2(mul2s(A1, r.inv_denom_c1))), splat2(1.f));
+    // 1 + A8 * A8 - 2 * A8 * cos_gamma: ((1 + A8 A8) - ((2 A8) cos_gamma))
+    float2 arg = add2x(neg2(mul2s(mul2s(A8, 2.f), r.cos_gamma)), add2x(mul2(A8, A8), splat2(1.f)));
+    float2 pw = dpow15_2(arg);
+    float2 chi = f2(fdiv(r.one_plus_cg2, pw.x), fdiv(r.one_plus_cg2, pw.y));
+    // A2 + A3 exp(A4 gamma) + A5 cos^2 + A6 chi + A7 sqrt(cos_theta), summed left to right
+    float2 c2 = add2x(mul2(A3, dexp_2(mul2s(A4, r.gamma))), A2);
+    c2 = add2x(mul2s(A5, r.cos_gamma_sqr), c2);
+    c2 = add2x(mul2(A6, chi), c2);
+    c2 = add2x(mul2s(A7, r.sqrt_cos_theta), c2);
+    return mul2(mul2(c1, c2), f2(P.sky_rad[ch], P.sky_rad[ch + 1]));
+}
+
 
 /// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
 /// lane-dependent channels); the radiance scale T[10] folds sky_scale and, in RGB mode, the CIE-Y
@@ -149,6 +170,23 @@ SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool
     g_fast_calls++; g_fast_fallbacks += !ok;
 #endif
     return c1 * c2 * T[10];
+}
+
+/// sky_channel_fast on a pair of channels (the two neighbouring bins of a wavelength, two RGB channels):
+/// the same op sequence on float2, so each element equals the scalar function's result bit for bit.
+/// T[k] = { coefficient k of channel a, of channel b }. ok = neither element cancelled.
+SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, bool &ok) {
+    float2 c1 = add2s(mul2(T[0], dexp_2(mul2s(T[1], r.inv_denom_c1))), 1.f);
+    float2 t = sub2(T[8], mul2s(T[9], r.cos_gamma));
+    float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
+    float2 chi = mul2s(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
+    float2 a = mul2s(T[4], r.gamma);
+    float2 p3 = mul2(T[3], f2(hw_ex2(a.x), hw_ex2(a.y))), p5 = mul2s(T[5], r.cos_gamma_sqr), p6 = mul2(T[6], chi),
+           p7 = mul2s(T[7], r.sqrt_cos_theta);
+    float2 c2 = add2(add2(add2(T[2], p3), add2(p5, p6)), p7);
+    float2 s2 = add2(add2(add2(abs2(T[2]), abs2(p3)), add2(abs2(p5), abs2(p6))), abs2(p7));
+    ok = fabsf(c2.x) >= kCancel * s2.x && fabsf(c2.y) >= kCancel * s2.y;
+    return mul2(mul2(c1, c2), T[10]);
 }
 
 /// compute_cos_psi (sunsky.h:384-392); `1.0 - ...` is evaluated in fp64 by the reference, which
@@ -356,21 +394,19 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
         Bin b = wavelength_bin(wav[w]);
         float res;
         if (A == kFast) {
-            float Tl[kFastCoefs], Th[kFastCoefs];
+            float2 T[kFastCoefs];
 #pragma unroll
-            for (int k = 0; k < kFastCoefs; ++k) {
-                float2 p = pairs[k * kChanPad + b.lo];
-                Tl[k] = p.x; Th[k] = p.y;
-            }
-            bool ok_l, ok_h;
-            float sl = sky_channel_fast(Tl, g.r, ok_l), sh = sky_channel_fast(Th, g.r, ok_h);
-            res = lerp(sl, sh, b.f);
-            if (!(ok_l && ok_h)) {   // cancellation: this wavelength with the reference sequence
+            for (int k = 0; k < kFastCoefs; ++k) T[k] = pairs[k * kChanPad + b.lo];
+            bool ok;
+            float2 sk = sky_channel_fast_2(T, g.r, ok);
+            res = lerp(sk.x, sk.y, b.f);
+            if (!ok) {   // cancellation: this wavelength with the reference sequence
                 RayTerms re = exact_terms(g.r);
                 res = U.sky_scale * lerp(render_sky_cold(S, b.lo, re), render_sky_cold(S, b.lo + 1, re), b.f);
             }
         } else {
-            res = U.sky_scale * lerp(render_sky(S, b.lo, rx), render_sky(S, b.lo + 1, rx), b.f);
+            float2 sk = render_sky_2(S, b.lo, rx);
+            res = U.sky_scale * lerp(sk.x, sk.y, b.f);
         }
         if (g.hit_sun) {
             float sun = sun_spec_term(U, S, sun_rad, s, xk, cj, b.lo, b.f), sum = res + sun;
@@ -406,9 +442,21 @@ SSK_COLD float tgmm_sum_generic(const HotBlock &U, float phi, float theta) {
 SSK_HD float tgmm_sum_exact(const HotBlock &U, float phi, float theta) {
     float pdf = 0.f;
     bool tiny = false;
+    // two components per pass on float2 (same per-element op sequence), accumulated in component order
 #pragma unroll
-    for (int i = 0; i < kGauss; ++i) {
-        if (i < U.n_pdf) {
+    for (int i = 0; i < kGauss; i += 2) {
+        if (i + 1 < U.n_pdf) {
+            float2 sx = fdiv_by_2(sub2(splat2(phi), f2(U.p_mu_phi[i], U.p_mu_phi[i + 1])),
+                                  f2(U.p_sigma_phi[i], U.p_sigma_phi[i + 1]), f2(U.p_rsigma_phi[i], U.p_rsigma_phi[i + 1])),
+                   sy = fdiv_by_2(sub2(splat2(theta), f2(U.p_mu_theta[i], U.p_mu_theta[i + 1])),
+                                  f2(U.p_sigma_theta[i], U.p_sigma_theta[i + 1]), f2(U.p_rsigma_theta[i], U.p_rsigma_theta[i + 1]));
+            float2 g = mul2s(dexp_2(mul2s(fma2(sy, sy, mul2(sx, sx)), -.5f)), SSK_INV_TWO_PI);
+            float2 num = mul2(f2(U.p_weight[i], U.p_weight[i + 1]), g);
+            tiny = tiny || fdiv_by_tiny(num.x) || fdiv_by_tiny(num.y);
+            float2 q = fdiv_by_2(num, f2(U.p_volume[i], U.p_volume[i + 1]), f2(U.p_rvolume[i], U.p_rvolume[i + 1]));
+            pdf += q.x;
+            pdf += q.y;
+        } else if (i < U.n_pdf) {
             float sx = fdiv_by(phi - U.p_mu_phi[i], U.p_sigma_phi[i], U.p_rsigma_phi[i]),
                   sy = fdiv_by(theta - U.p_mu_theta[i], U.p_sigma_theta[i], U.p_rsigma_theta[i]);
             float g = SSK_INV_TWO_PI * dexp(-.5f * fmaf(sy, sy, sx * sx));
@@ -421,18 +469,24 @@ SSK_HD float tgmm_sum_exact(const HotBlock &U, float phi, float theta) {
     return pdf;
 }
 
-/// FAST: 8 instructions per component, one MUFU. phi - mu is the reference's own rounding (the Gaussian
-/// argument cancels there); k = sqrt(log2(e) / 2) / sigma, wv = weight / (2 pi volume).
+/// FAST: 4.5 instructions per component, one MUFU. phi - mu is the reference's own rounding (the Gaussian
+/// argument cancels there); k = sqrt(log2(e) / 2) / sigma, wv = weight / (2 pi volume). Two components per
+/// pass on float2, even and odd components in separate accumulators.
 SSK_HD float tgmm_sum_fast(const HotBlock &U, float phi, float theta) {
-    float pdf = 0.f;
+    float2 acc = f2(0.f, 0.f);
 #pragma unroll
-    for (int i = 0; i < kGauss; ++i) {
-        if (i < U.n_pdf) {
+    for (int i = 0; i < kGauss; i += 2) {
+        if (i + 1 < U.n_pdf) {
+            float2 sx = mul2(sub2(splat2(phi), f2(U.p_mu_phi[i], U.p_mu_phi[i + 1])), f2(U.p_k_phi[i], U.p_k_phi[i + 1])),
+                   sy = mul2(sub2(splat2(theta), f2(U.p_mu_theta[i], U.p_mu_theta[i + 1])), f2(U.p_k_theta[i], U.p_k_theta[i + 1]));
+            float2 e = fma2(sy, sy, mul2(sx, sx));
+            acc = fma2(f2(U.p_wv[i], U.p_wv[i + 1]), f2(hw_ex2(-e.x), hw_ex2(-e.y)), acc);
+        } else if (i < U.n_pdf) {
             float sx = (phi - U.p_mu_phi[i]) * U.p_k_phi[i], sy = (theta - U.p_mu_theta[i]) * U.p_k_theta[i];
-            pdf = fmaf(U.p_wv[i], hw_ex2(-fmaf(sy, sy, sx * sx)), pdf);
+            acc.x = fmaf(U.p_wv[i], hw_ex2(-fmaf(sy, sy, sx * sx)), acc.x);
         }
     }
-    return pdf;
+    return acc.x + acc.y;
 }
 
 template <int A> SSK_HD float tgmm_pdf(const HotBlock &U, float phi, float theta, bool active) {
