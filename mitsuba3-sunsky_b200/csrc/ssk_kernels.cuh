@@ -18,13 +18,13 @@ namespace ssk {
 constexpr int kThreads = 256;
 
 /// Copy the emitter block from global to shared memory (16-byte accesses) and, for FAST spectral
-/// kernels, build the bin-pair table of eval_spec. Ends with a barrier.
+/// kernels, build the bin-pair table of eval_spec (build_pair_table's layout). Ends with a barrier.
 __device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const EmitterBlock *src) {
     const uint4 *s = reinterpret_cast<const uint4 *>(src);
     uint4 *d = reinterpret_cast<uint4 *>(dst);
     for (int i = threadIdx.x; i < (int) (sizeof(HotBlock) / 16); i += blockDim.x) d[i] = __ldg(s + i);
     if (pairs)
-        for (int i = threadIdx.x; i < kFastCoefs * kChanPad; i += blockDim.x) {
+        for (int i = threadIdx.x; i < kPairTable; i += blockDim.x) {
             int c = i % kChanPad;
             const float *row = &src->sky_fast[0][0] + (i - c);
             pairs[i] = make_float2(__ldg(row + c), c + 1 < kChanPad ? __ldg(row + c + 1) : 0.f);
@@ -103,11 +103,11 @@ eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restri
 
 /// eval / eval_direction, spectral (4 wavelengths per ray)
 template <int A, int R>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? 4 : 1)
 eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
                  OutPlanes4 out, size_t n, float dir_sign) {
     __shared__ __align__(16) HotBlock S;
-    __shared__ __align__(16) float2 pairs[A == kFast ? kFastCoefs * kChanPad : 1];
+    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
     stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
@@ -157,7 +157,7 @@ template <int A, int R, bool Spectral>
 __global__ void __launch_bounds__(kThreads)
 sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
-    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kFastCoefs * kChanPad : 1];
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
     stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(kThreads)
 envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, float4 wav4,
               float *__restrict__ out, int width, int height) {
     __shared__ __align__(16) HotBlock S;
-    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kFastCoefs * kChanPad : 1];
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
     if (Spectral) stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     constexpr int C = Spectral ? 4 : 3;

@@ -176,7 +176,8 @@ SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool
 /// the same op sequence on float2, so each element equals the scalar function's result bit for bit.
 /// T[k] = { coefficient k of channel a, of channel b }. ok = neither element cancelled.
 SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, bool &ok) {
-    float2 c1 = add2s(mul2(T[0], dexp_2(mul2s(T[1], r.inv_denom_c1))), 1.f);
+    bool ok_e;
+    float2 c1 = add2s(mul2(T[0], fexp_2(mul2s(T[1], r.inv_denom_c1), ok_e)), 1.f);
     float2 t = sub2(T[8], mul2s(T[9], r.cos_gamma));
     float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
     float2 chi = mul2s(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
@@ -185,7 +186,7 @@ SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, 
            p7 = mul2s(T[7], r.sqrt_cos_theta);
     float2 c2 = add2(add2(add2(T[2], p3), add2(p5, p6)), p7);
     float2 s2 = add2(add2(add2(abs2(T[2]), abs2(p3)), add2(abs2(p5), abs2(p6))), abs2(p7));
-    ok = fabsf(c2.x) >= kCancel * s2.x && fabsf(c2.y) >= kCancel * s2.y;
+    ok = ok_e && fabsf(c2.x) >= kCancel * s2.x && fabsf(c2.y) >= kCancel * s2.y;
     return mul2(mul2(c1, c2), T[10]);
 }
 
@@ -364,7 +365,7 @@ SSK_HD Bin wavelength_bin(float wav) {
 }
 
 /// Sun term of the spectral eval for one wavelength (sunsky.cpp:339-347), reference op order
-SSK_COLD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *sun_rad, const SunSeg &s,
+SSK_HD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *sun_rad, const SunSeg &s,
                            const float *xk, const float *cj, int lo, float f) {
     int hi = lo + 1;
     float sun_lo = render_sun_spec(sun_rad, lo, s, xk),
@@ -374,51 +375,96 @@ SSK_COLD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *
     return U.sun_scale * sun * ld * U.area_ratio;
 }
 
-/// SunskyEmitter::eval, spectral, for the 4 wavelengths of one ray (sunsky.cpp:325-351).
-/// FAST mode reads `pairs`: pairs[k * kChanPad + c] = { sky_fast[k][c], sky_fast[k][c + 1] }, so the
-/// coefficients of a wavelength's two neighbouring bins arrive in one 64-bit shared-memory load each.
+/// Layout of the FAST spectral coefficient table in shared memory: pairs[k * kChanPad + bin] =
+/// { sky_fast[k][bin], sky_fast[k][bin + 1] }, the coefficient k of the two dataset bins a wavelength falls
+/// between, in one 64-bit load. For a given k the 11 bins span 88 bytes, so whatever bins the lanes of a warp
+/// ask for, the load is a single conflict-free wavefront (a row-per-bin layout read with 128-bit loads was
+/// measured at 2.2x the ideal wavefront count and became the bottleneck: profiles/r1_summary.md).
+constexpr int kPairTable = kFastCoefs * kChanPad;
+SSK_HD void build_pair_table(const HotBlock &B, float2 *pairs) {
+    for (int k = 0; k < kFastCoefs; ++k)
+        for (int c = 0; c < kChanPad; ++c)
+            pairs[k * kChanPad + c] = f2(B.sky_fast[k][c], c + 1 < kChanPad ? B.sky_fast[k][c + 1] : 0.f);
+}
+
+/// Sky radiance of the 4 wavelengths with the reference sequence (FAST mode's fallback for cancelling lanes)
+SSK_COLD float4 sky_spec_exact_cold(const HotBlock &U, const HotBlock &S, RayTerms r, float4 wav) {
+    const float wl[4] = { wav.x, wav.y, wav.z, wav.w };
+    float o[4];
+    RayTerms re = exact_terms(r);
+    for (int w = 0; w < 4; ++w) {
+        Bin b = wavelength_bin(wl[w]);
+        float2 sk = render_sky_2(S, b.lo, re);
+        o[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
+    }
+    return make_float4(o[0], o[1], o[2], o[3]);
+}
+
+/// Sun-disc lanes of the spectral eval: the sun term of every wavelength on top of `sky` (sunsky.cpp:339-347),
+/// reference op order. `fast`: guard against the sun cancelling the sky (the fitted sun radiance can be
+/// negative for a low sun in a turbid atmosphere); such lanes redo the sky with the reference sequence.
+SSK_COLD float4 add_sun_spec_cold(const HotBlock &U, const HotBlock &S, const float *sun_rad, RayTerms r, float4 wav,
+                                  float4 sky, bool fast) {
+    const float wl[4] = { wav.x, wav.y, wav.z, wav.w };
+    float res[4] = { sky.x, sky.y, sky.z, sky.w }, sun[4];
+    SunSeg s = sun_segment(r.cos_theta);
+    float xk[4], cj[6];
+    powers4(s.x, xk);
+    powers6(cos_psi(U, r.gamma), cj);
+    bool ok = true;
+    for (int w = 0; w < 4; ++w) {
+        Bin b = wavelength_bin(wl[w]);
+        sun[w] = sun_spec_term(U, S, sun_rad, s, xk, cj, b.lo, b.f);
+        float sum = res[w] + sun[w];
+        ok = ok && fabsf(sum) >= kCancel * (fabsf(res[w]) + fabsf(sun[w]));
+        res[w] = sum;
+    }
+    if (fast && !ok) {
+        float4 e = sky_spec_exact_cold(U, S, r, wav);
+        res[0] = e.x + sun[0]; res[1] = e.y + sun[1]; res[2] = e.z + sun[2]; res[3] = e.w + sun[3];
+    }
+    return make_float4(res[0], res[1], res[2], res[3]);
+}
+
+/// SunskyEmitter::eval, spectral, for the 4 wavelengths of one ray (sunsky.cpp:325-351). The two bins of a
+/// wavelength are evaluated as one float2 pair. FAST mode reads `pairs` (build_pair_table); lanes where a
+/// channel cancels redo all four wavelengths with the reference sequence, sun-disc lanes add the sun term,
+/// both behind one call per ray.
 template <int A>
 SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs, const float *sun_rad,
                       const Vec3 &wi, const float wav[4], bool active_in, float out[4]) {
     EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = out[3] = 0.f; return; }
-    SunSeg s = { 0, 0.f }; float xk[4], cj[6];
-    RayTerms rx = g.r;
-    if (g.hit_sun) {
-        s = sun_segment(g.r.cos_theta);
-        powers4(s.x, xk);
-        powers6(cos_psi(U, g.r.gamma), cj);
-    }
+    bool ok = true, valid[4];
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
         Bin b = wavelength_bin(wav[w]);
-        float res;
+        valid[w] = b.valid;
         if (A == kFast) {
             float2 T[kFastCoefs];
 #pragma unroll
             for (int k = 0; k < kFastCoefs; ++k) T[k] = pairs[k * kChanPad + b.lo];
-            bool ok;
-            float2 sk = sky_channel_fast_2(T, g.r, ok);
-            res = lerp(sk.x, sk.y, b.f);
-            if (!ok) {   // cancellation: this wavelength with the reference sequence
-                RayTerms re = exact_terms(g.r);
-                res = U.sky_scale * lerp(render_sky_cold(S, b.lo, re), render_sky_cold(S, b.lo + 1, re), b.f);
-            }
+            bool ok_w;
+            float2 sk = sky_channel_fast_2(T, g.r, ok_w);
+            ok = ok && ok_w;
+            out[w] = lerp(sk.x, sk.y, b.f);
         } else {
-            float2 sk = render_sky_2(S, b.lo, rx);
-            res = U.sky_scale * lerp(sk.x, sk.y, b.f);
+            float2 sk = render_sky_2(S, b.lo, g.r);
+            out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
         }
-        if (g.hit_sun) {
-            float sun = sun_spec_term(U, S, sun_rad, s, xk, cj, b.lo, b.f), sum = res + sun;
-            if (A == kFast && !(fabsf(sum) >= kCancel * (fabsf(res) + fabsf(sun)))) {
-                // the fitted sun radiance can be negative (low sun, turbid) and cancel the sky: reference sequence
-                RayTerms re = exact_terms(g.r);
-                sum = U.sky_scale * lerp(render_sky_cold(S, b.lo, re), render_sky_cold(S, b.lo + 1, re), b.f) + sun;
-            }
-            res = sum;
-        }
-        out[w] = b.valid ? res : 0.f;
     }
+    const float4 wav4 = make_float4(wav[0], wav[1], wav[2], wav[3]);
+    if (A == kFast && !ok) {
+        float4 e = sky_spec_exact_cold(U, S, g.r, wav4);
+        out[0] = e.x; out[1] = e.y; out[2] = e.z; out[3] = e.w;
+    }
+    if (g.hit_sun) {
+        float4 e = add_sun_spec_cold(U, S, sun_rad, A == kFast ? exact_terms(g.r) : g.r, wav4,
+                                     make_float4(out[0], out[1], out[2], out[3]), A == kFast);
+        out[0] = e.x; out[1] = e.y; out[2] = e.z; out[3] = e.w;
+    }
+#pragma unroll
+    for (int w = 0; w < 4; ++w) out[w] = valid[w] ? out[w] : 0.f;
 }
 
 // ---------------------------------------------------------------------------------------------

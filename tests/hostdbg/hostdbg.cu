@@ -6,10 +6,8 @@ namespace ssk { long long g_fast_calls = 0, g_fast_fallbacks = 0; }
 using namespace ssk;
 extern "C" void hostdbg_fallback_stats(long long *calls, long long *fb) { *calls = g_fast_calls; *fb = g_fast_fallbacks; g_fast_calls = g_fast_fallbacks = 0; }
 static const float2 *E_pairs(const HostEmitter &E) {
-    static thread_local float2 pairs[kFastCoefs * kChanPad];
-    for (int k = 0; k < kFastCoefs; ++k)
-        for (int c = 0; c < kChanPad; ++c)
-            pairs[k * kChanPad + c] = make_float2(E.block.sky_fast[k][c], c + 1 < kChanPad ? E.block.sky_fast[k][c + 1] : 0.f);
+    static thread_local float2 pairs[kPairTable];
+    build_pair_table(E.block, pairs);
     return pairs;
 }
 extern "C" {
