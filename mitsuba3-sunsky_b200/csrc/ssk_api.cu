@@ -53,6 +53,7 @@ constexpr int kSampleRays = 1;
 /// selects the 128-bit variant when the planes are 16-byte aligned
 bool force_scalar() { static const bool v = !(getenv("SSK_RAYS_PER_THREAD") && getenv("SSK_RAYS_PER_THREAD")[0] == '4'); return v; }
 bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+bool aligned8(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 7u) == 0; }
 
 /// Persistent grid: enough CTAs to fill every SM at the kernel's occupancy, never more than the work needs.
 template <typename K> int occupancy_grid(const ssk_ctx *ctx, K kernel, size_t n_items, int *grid_out, int rays_per_thread = 4) {
@@ -122,6 +123,22 @@ int launch_eval(const ssk_ctx *ctx, const float *const in[3], const float *const
         w4 = { wav[0], wav[1], wav[2], wav[3] };
     }
     int rc;
+    // RGB: two rays per thread on packed f32x2 arithmetic (planes 8-byte aligned); SSK_RAYS_PER_THREAD=1 or 4
+    // selects the older one-ray / 128-bit kernels
+    bool pair = !spectral && !getenv("SSK_RAYS_PER_THREAD") && aligned8(in[0]) && aligned8(in[1]) && aligned8(in[2]) &&
+                aligned8(out[0]) && aligned8(out[1]) && aligned8(out[2]);
+    if (pair) {
+        int grid = 1;
+        OutPlanes3 o3 = { out[0], out[1], out[2] };
+        if (fast(ctx)) {
+            if (int rc2 = occupancy_grid(ctx, eval_rgb_pair_kernel<kFast>, n, &grid, 2)) return rc2;
+            eval_rgb_pair_kernel<kFast><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, o3, n, dir_sign);
+        } else {
+            if (int rc2 = occupancy_grid(ctx, eval_rgb_pair_kernel<kExact>, n, &grid, 2)) return rc2;
+            eval_rgb_pair_kernel<kExact><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, o3, n, dir_sign);
+        }
+        rc = SSK_OK;
+    } else
     if (fast(ctx)) rc = vec ? launch_eval_t<kFast, 4>(ctx, spectral, i3, w4, out, n, dir_sign, s)
                             : launch_eval_t<kFast, 1>(ctx, spectral, i3, w4, out, n, dir_sign, s);
     else rc = vec ? launch_eval_t<kExact, 4>(ctx, spectral, i3, w4, out, n, dir_sign, s)

@@ -101,6 +101,35 @@ eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restri
     }
 }
 
+/// eval / eval_direction, RGB, two consecutive rays per thread as float2 pairs (64-bit plane accesses, planes
+/// 8-byte aligned): every FP32 instruction of the model works on both rays (FFMA2 / FMUL2 / FADD2).
+template <int A>
+__global__ void __launch_bounds__(kThreads, 3)
+eval_rgb_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out,
+                     size_t n, float dir_sign) {
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x * 2;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+        const bool two = i + 1 < n;
+        float2 x, y, z;
+        if (two) {
+            x = __ldcs(reinterpret_cast<const float2 *>(in.x + i)); y = __ldcs(reinterpret_cast<const float2 *>(in.y + i));
+            z = __ldcs(reinterpret_cast<const float2 *>(in.z + i));
+        } else {
+            x = f2(in.x[i], 0.f); y = f2(in.y[i], 0.f); z = f2(in.z[i], 1.f);
+        }
+        Vec3p wi = { mul2s(x, dir_sign), mul2s(y, dir_sign), mul2s(z, dir_sign) };
+        float2 o[3];
+        eval_rgb_p<A>(U, sun_rad, wi, true, two, o);
+        if (two) {
+            __stcs(reinterpret_cast<float2 *>(out.x + i), o[0]); __stcs(reinterpret_cast<float2 *>(out.y + i), o[1]);
+            __stcs(reinterpret_cast<float2 *>(out.z + i), o[2]);
+        } else {
+            out.x[i] = o[0].x; out.y[i] = o[1].x; out.z[i] = o[2].x;
+        }
+    }
+}
+
 /// eval / eval_direction, spectral (4 wavelengths per ray)
 template <int A, int R>
 __global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? 4 : 1)
@@ -236,6 +265,21 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < npix; i += stride) {
         float o[4][4];
+        if (!Spectral) {
+            // RGB: two pixels at a time on the packed two-ray path (the same functions as eval_rgb_pair_kernel)
+#pragma unroll 1
+            for (int k = 0; k < 4; k += 2) {
+                size_t p0 = i + k < npix ? i + k : npix - 1, p1 = i + k + 1 < npix ? i + k + 1 : npix - 1;
+                int y0 = (int) (p0 / (size_t) width), x0 = (int) (p0 - (size_t) y0 * width);
+                int y1 = (int) (p1 / (size_t) width), x1 = (int) (p1 - (size_t) y1 * width);
+                Vec3 d0 = envmap_dir(x0, y0, width, height), d1 = envmap_dir(x1, y1, width, height);
+                Vec3p wi = { f2(-d0.x, -d1.x), f2(-d0.y, -d1.y), f2(-d0.z, -d1.z) };
+                float2 e[3];
+                eval_rgb_p<A>(U, sun_rad, wi, true, true, e);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { setk<R>(o[c], k, e[c].x); setk<R>(o[c], k + 1, e[c].y); }
+            }
+        } else
 #pragma unroll 1
         for (int k = 0; k < 4; ++k) {
             size_t pix = i + k < npix ? i + k : npix - 1;

@@ -156,15 +156,20 @@ SSK_HD float2 render_sky_2(const HotBlock &P, int ch, const RayTerms &r) {
 ///    carries its absolute-value twin (every variable is >= 0, so |T x| = |T| x) and `ok` is cleared when
 ///    |c2| falls below kCancel of it; the caller then evaluates this channel with the reference sequence.
 constexpr float kCancel = 0.125f;
+/// All three variants (scalar, bin pair, ray pair) run ONE explicit op sequence, so they agree bit for bit:
+///   c1 = 1 + T0 fexp(T1 / (cos(theta) + .01))      product and sum rounded separately (it cancels to ~0.1)
+///   t  = T8 - T9 cos(gamma)                        two roundings, as the reference (it cancels towards the sun)
+///   c2 = fma chain T2 + T3 2^(T4 gamma) + T5 cos^2(gamma) + T6 chi + T7 sqrt(cos(theta)), s2 its |.| twin
 SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool &ok) {
-    float c1 = 1.f + T[0] * dexp(T[1] * r.inv_denom_c1);
+    bool ok_e;
+    float c1 = T[0] * fexp(T[1] * r.inv_denom_c1, ok_e) + 1.f;
     float t = T[8] - T[9] * r.cos_gamma;
     float rs = hw_rsqrt(t);
-    float chi = r.one_plus_cg2 * (rs * rs * rs);
-    float p3 = T[3] * hw_ex2(T[4] * r.gamma), p5 = T[5] * r.cos_gamma_sqr, p6 = T[6] * chi, p7 = T[7] * r.sqrt_cos_theta;
-    float c2 = (T[2] + p3) + (p5 + p6) + p7;
-    float s2 = (fabsf(T[2]) + fabsf(p3)) + (fabsf(p5) + fabsf(p6)) + fabsf(p7);
-    ok = fabsf(c2) >= kCancel * s2;
+    float chi = (rs * rs * rs) * r.one_plus_cg2;
+    float ex = hw_ex2(T[4] * r.gamma);
+    float c2 = fmaf(r.sqrt_cos_theta, T[7], fmaf(chi, T[6], fmaf(r.cos_gamma_sqr, T[5], fmaf(ex, T[3], T[2]))));
+    float s2 = fmaf(r.sqrt_cos_theta, fabsf(T[7]), fmaf(chi, fabsf(T[6]), fmaf(r.cos_gamma_sqr, fabsf(T[5]), fmaf(ex, fabsf(T[3]), fabsf(T[2])))));
+    ok = ok_e && fabsf(c2) >= kCancel * s2;
 #if defined(SSK_COUNT_FALLBACK) && !defined(__CUDA_ARCH__)
     extern long long g_fast_calls, g_fast_fallbacks;
     g_fast_calls++; g_fast_fallbacks += !ok;
@@ -177,15 +182,14 @@ SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool
 /// T[k] = { coefficient k of channel a, of channel b }. ok = neither element cancelled.
 SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, bool &ok) {
     bool ok_e;
-    float2 c1 = add2s(mul2(T[0], fexp_2(mul2s(T[1], r.inv_denom_c1), ok_e)), 1.f);
-    float2 t = sub2(T[8], mul2s(T[9], r.cos_gamma));
+    float2 c1 = add2x(mul2(T[0], fexp_2(mul2s(T[1], r.inv_denom_c1), ok_e)), splat2(1.f));
+    float2 t = subp2(T[8], mul2s(T[9], r.cos_gamma));
     float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
     float2 chi = mul2s(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
     float2 a = mul2s(T[4], r.gamma);
-    float2 p3 = mul2(T[3], f2(hw_ex2(a.x), hw_ex2(a.y))), p5 = mul2s(T[5], r.cos_gamma_sqr), p6 = mul2(T[6], chi),
-           p7 = mul2s(T[7], r.sqrt_cos_theta);
-    float2 c2 = add2(add2(add2(T[2], p3), add2(p5, p6)), p7);
-    float2 s2 = add2(add2(add2(abs2(T[2]), abs2(p3)), add2(abs2(p5), abs2(p6))), abs2(p7));
+    float2 ex = f2(hw_ex2(a.x), hw_ex2(a.y));
+    float2 c2 = fma2(splat2(r.sqrt_cos_theta), T[7], fma2(chi, T[6], fma2(splat2(r.cos_gamma_sqr), T[5], fma2(ex, T[3], T[2]))));
+    float2 s2 = fma2(splat2(r.sqrt_cos_theta), abs2(T[7]), fma2(chi, abs2(T[6]), fma2(splat2(r.cos_gamma_sqr), abs2(T[5]), fma2(ex, abs2(T[3]), abs2(T[2])))));
     ok = ok_e && fabsf(c2.x) >= kCancel * s2.x && fabsf(c2.y) >= kCancel * s2.y;
     return mul2(mul2(c1, c2), T[10]);
 }
@@ -350,6 +354,122 @@ SSK_HD void eval_rgb(const HotBlock &U, const float *sun_rad, const Vec3 &wi, bo
 #pragma unroll
     for (int c = 0; c < 3; ++c)
         out[c] = (float) ((double) res[c] * (1.0 / 106.7502593994140625));
+}
+
+// ---- two rays per thread (RGB): the same sequences on float2, one element per ray ----------------------
+struct RayTermsP { float2 cos_theta, gamma, cos_gamma, cos_gamma_sqr, inv_denom_c1, one_plus_cg2, sqrt_cos_theta; };
+SSK_HD RayTerms lane_terms(const RayTermsP &r, int e) {
+    return e == 0 ? RayTerms{ r.cos_theta.x, r.gamma.x, r.cos_gamma.x, r.cos_gamma_sqr.x, r.inv_denom_c1.x, r.one_plus_cg2.x, r.sqrt_cos_theta.x }
+                  : RayTerms{ r.cos_theta.y, r.gamma.y, r.cos_gamma.y, r.cos_gamma_sqr.y, r.inv_denom_c1.y, r.one_plus_cg2.y, r.sqrt_cos_theta.y };
+}
+template <int A> SSK_HD RayTermsP ray_terms_p(float2 cos_theta, float2 gamma) {
+    RayTermsP r;
+    r.cos_theta = cos_theta; r.gamma = gamma;
+    r.cos_gamma = dcos_2(gamma);
+    r.cos_gamma_sqr = mul2(r.cos_gamma, r.cos_gamma);
+    float2 den = add2s(cos_theta, 0.01f);
+    r.inv_denom_c1 = f2(fdiv(1.f, den.x), fdiv(1.f, den.y));
+    r.one_plus_cg2 = add2x(r.cos_gamma_sqr, splat2(1.f));
+    r.sqrt_cos_theta = A == kFast ? f2(hw_sqrt(fmaxf(cos_theta.x, 0.f)), hw_sqrt(fmaxf(cos_theta.y, 0.f))) : safe_sqrt2(cos_theta);
+    return r;
+}
+SSK_HD Vec3p xform_p(const float *m, const Vec3p &v) {
+    return { fma2(splat2(m[2]), v.z, fma2(splat2(m[1]), v.y, mul2s(v.x, m[0]))),
+             fma2(splat2(m[5]), v.z, fma2(splat2(m[4]), v.y, mul2s(v.x, m[3]))),
+             fma2(splat2(m[8]), v.z, fma2(splat2(m[7]), v.y, mul2s(v.x, m[6]))) };
+}
+/// render_sky for one channel and two rays, reference op order (see render_sky)
+SSK_HD float2 render_sky_p(const HotBlock &P, int ch, const RayTermsP &r) {
+    float A0 = P.sky_params[0][ch], A1 = P.sky_params[1][ch], A2 = P.sky_params[2][ch],
+          A3 = P.sky_params[3][ch], A4 = P.sky_params[4][ch], A5 = P.sky_params[5][ch],
+          A6 = P.sky_params[6][ch], A7 = P.sky_params[7][ch], A8 = P.sky_params[8][ch];
+    float2 c1 = add2x(mul2s(dexp_2(mul2s(r.inv_denom_c1, A1)), A0), splat2(1.f));
+    const float k1 = 1.f + A8 * A8, k2 = 2.f * A8;          // the same for every lane: uniform scalars
+    float2 chi = fdiv2(r.one_plus_cg2, dpow15_2(subp2(splat2(k1), mul2s(r.cos_gamma, k2))));
+    float2 c2 = add2x(mul2s(dexp_2(mul2s(r.gamma, A4)), A3), splat2(A2));
+    c2 = add2x(mul2s(r.cos_gamma_sqr, A5), c2);
+    c2 = add2x(mul2s(chi, A6), c2);
+    c2 = add2x(mul2s(r.sqrt_cos_theta, A7), c2);
+    return mul2s(mul2(c1, c2), P.sky_rad[ch]);
+}
+/// sky_channel_fast for one channel and two rays (see sky_channel_fast_2 for what is approximated)
+SSK_HD float2 sky_channel_fast_p(const float T[kFastCoefs], const RayTermsP &r, bool &ok0, bool &ok1) {
+    bool ok_e;
+    float2 c1 = add2x(mul2s(fexp_2(mul2s(r.inv_denom_c1, T[1]), ok_e), T[0]), splat2(1.f));
+    float2 t = subp2(splat2(T[8]), mul2s(r.cos_gamma, T[9]));
+    float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
+    float2 chi = mul2(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
+    float2 a = mul2s(r.gamma, T[4]);
+    float2 ex = f2(hw_ex2(a.x), hw_ex2(a.y));
+    float2 c2 = fma2(r.sqrt_cos_theta, splat2(T[7]), fma2(chi, splat2(T[6]), fma2(r.cos_gamma_sqr, splat2(T[5]), fma2(ex, splat2(T[3]), splat2(T[2])))));
+    float2 s2 = fma2(r.sqrt_cos_theta, splat2(fabsf(T[7])), fma2(chi, splat2(fabsf(T[6])), fma2(r.cos_gamma_sqr, splat2(fabsf(T[5])), fma2(ex, splat2(fabsf(T[3])), splat2(fabsf(T[2]))))));
+    ok0 = ok_e && fabsf(c2.x) >= kCancel * s2.x;
+    ok1 = ok_e && fabsf(c2.y) >= kCancel * s2.y;
+    return mul2s(mul2(c1, c2), T[10]);
+}
+struct EvalGeomP { RayTermsP r; bool active0, active1, hit0, hit1; };
+template <int A> SSK_HD EvalGeomP eval_geom_p(const HotBlock &U, const Vec3p &wi, bool act0, bool act1) {
+    Vec3p neg = { neg2(wi.x), neg2(wi.y), neg2(wi.z) };
+    Vec3p wo = xform_p(U.to_local, neg);
+    Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
+    float2 cos_theta = wo.z, gamma = unit_angle_p(n, wo), dn = dot3_p(n, wo);
+    EvalGeomP g;
+    g.active0 = act0 && cos_theta.x >= 0.f; g.active1 = act1 && cos_theta.y >= 0.f;
+    g.hit0 = g.active0 && dn.x >= U.cos_cutoff; g.hit1 = g.active1 && dn.y >= U.cos_cutoff;
+    g.r = ray_terms_p<A>(cos_theta, gamma);
+    return g;
+}
+/// One element of the EXACT pair path, after the sky channels: sun term and fp64 normalisation (sunsky.cpp:317-323)
+SSK_COLD Vec3 finish_rgb_sun_cold(const HotBlock &U, const float *sun_rad, RayTerms r, Vec3 res) {
+    float v[3] = { res.x, res.y, res.z };
+    add_sun_rgb(U, sun_rad, r, v);
+    return { v[0], v[1], v[2] };
+}
+SSK_COLD float sky_rgb_exact_cold(const HotBlock &U, int c, RayTerms r) {
+    return (float) ((double) (U.sky_scale * render_sky(U, c, exact_terms(r))) * (1.0 / 106.7502593994140625));
+}
+/// SunskyEmitter::eval, RGB, two rays (see eval_rgb)
+template <int A>
+SSK_HD void eval_rgb_p(const HotBlock &U, const float *sun_rad, const Vec3p &wi, bool act0, bool act1, float2 out[3]) {
+    EvalGeomP g = eval_geom_p<A>(U, wi, act0, act1);
+    if (!g.active0 && !g.active1) { out[0] = out[1] = out[2] = f2(0.f, 0.f); return; }
+    if (A == kFast) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float T[kFastCoefs];
+#pragma unroll
+            for (int k = 0; k < kFastCoefs; ++k) T[k] = U.sky_fast[k][c];
+            bool ok0, ok1;
+            out[c] = sky_channel_fast_p(T, g.r, ok0, ok1);
+            if (!ok0 && g.active0) out[c].x = sky_rgb_exact_cold(U, c, lane_terms(g.r, 0));
+            if (!ok1 && g.active1) out[c].y = sky_rgb_exact_cold(U, c, lane_terms(g.r, 1));
+        }
+        if (g.hit0) {
+            Vec3 v = add_sun_rgb_fast_cold(U, sun_rad, lane_terms(g.r, 0), Vec3{ out[0].x, out[1].x, out[2].x });
+            out[0].x = v.x; out[1].x = v.y; out[2].x = v.z;
+        }
+        if (g.hit1) {
+            Vec3 v = add_sun_rgb_fast_cold(U, sun_rad, lane_terms(g.r, 1), Vec3{ out[0].y, out[1].y, out[2].y });
+            out[0].y = v.x; out[1].y = v.y; out[2].y = v.z;
+        }
+    } else {
+        float2 res[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) res[c] = mul2s(render_sky_p(U, c, g.r), U.sky_scale);
+        if (g.hit0) {
+            Vec3 v = finish_rgb_sun_cold(U, sun_rad, lane_terms(g.r, 0), Vec3{ res[0].x, res[1].x, res[2].x });
+            res[0].x = v.x; res[1].x = v.y; res[2].x = v.z;
+        }
+        if (g.hit1) {
+            Vec3 v = finish_rgb_sun_cold(U, sun_rad, lane_terms(g.r, 1), Vec3{ res[0].y, res[1].y, res[2].y });
+            res[0].y = v.x; res[1].y = v.y; res[2].y = v.z;
+        }
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            out[c] = f2((float) ((double) res[c].x * (1.0 / 106.7502593994140625)), (float) ((double) res[c].y * (1.0 / 106.7502593994140625)));
+    }
+    if (!g.active0) { out[0].x = 0.f; out[1].x = 0.f; out[2].x = 0.f; }
+    if (!g.active1) { out[0].y = 0.f; out[1].y = 0.f; out[2].y = 0.f; }
 }
 
 /// Spectral bin lookup of one wavelength (sunsky.cpp:326-338)

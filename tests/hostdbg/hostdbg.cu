@@ -28,6 +28,13 @@ void hostdbg_eval(void *h, size_t n, const float *wi, const float *wav, float *o
             float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }, o[4];
             if (E.block.arith) eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, v, w, true, o); else eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, v, w, true, o);
             for (int c = 0; c < 4; ++c) out[c * n + i] = o[c];
+        } else if (getenv("HOSTDBG_PAIR")) {       // the two-rays-per-thread path of eval_rgb_pair_kernel
+            if (i & 1) continue;
+            bool two = i + 1 < n;
+            Vec3p w = { f2(wi[i], two ? wi[i + 1] : 0.f), f2(wi[n + i], two ? wi[n + i + 1] : 0.f), f2(wi[2 * n + i], two ? wi[2 * n + i + 1] : 1.f) };
+            float2 o[3];
+            if (E.block.arith) eval_rgb_p<1>(E.block, E.block.sun_rad, w, true, two, o); else eval_rgb_p<0>(E.block, E.block.sun_rad, w, true, two, o);
+            for (int c = 0; c < 3; ++c) { out[c * n + i] = o[c].x; if (two) out[c * n + i + 1] = o[c].y; }
         } else {
             float o[3];
             if (E.block.arith) eval_rgb<1>(E.block, E.block.sun_rad, v, true, o); else eval_rgb<0>(E.block, E.block.sun_rad, v, true, o);
