@@ -164,6 +164,17 @@ int launch_pdf(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf
     bool vec = !force_scalar() && aligned16(d[0]) && aligned16(d[1]) && aligned16(d[2]) && aligned16(pdf);
     Planes3 i3 = { d[0], d[1], d[2] };
     int rc;
+    if (!getenv("SSK_RAYS_PER_THREAD") && aligned8(d[0]) && aligned8(d[1]) && aligned8(d[2]) && aligned8(pdf)) {
+        int grid = 1;
+        if (fast(ctx)) {
+            if (int rc2 = occupancy_grid(ctx, pdf_pair_kernel<kFast>, n, &grid, 2)) return rc2;
+            pdf_pair_kernel<kFast><<<grid, kThreads, 0, s>>>(hot(ctx), i3, pdf, n);
+        } else {
+            if (int rc2 = occupancy_grid(ctx, pdf_pair_kernel<kExact>, n, &grid, 2)) return rc2;
+            pdf_pair_kernel<kExact><<<grid, kThreads, 0, s>>>(hot(ctx), i3, pdf, n);
+        }
+        rc = SSK_OK;
+    } else
     if (fast(ctx)) rc = vec ? launch_pdf_t<kFast, 4>(ctx, i3, pdf, n, s) : launch_pdf_t<kFast, 1>(ctx, i3, pdf, n, s);
     else rc = vec ? launch_pdf_t<kExact, 4>(ctx, i3, pdf, n, s) : launch_pdf_t<kExact, 1>(ctx, i3, pdf, n, s);
     if (rc) return rc;
@@ -181,9 +192,26 @@ int launch_sample_t(const ssk_ctx *ctx, const SampleArgs &a, size_t n, cudaStrea
 }
 /// sample_direction moves 9 to 21 planes: one ray per thread (32-bit accesses, full 128-byte lines per warp)
 /// keeps the staging registers low enough for 2-3 resident CTAs per SM
+template <int A, bool Spectral>
+int launch_sample_pair_t(const ssk_ctx *ctx, const SampleArgs &a, size_t n, cudaStream_t s) {
+    int grid = 1;
+    if (int rc = occupancy_grid(ctx, sample_pair_kernel<A, Spectral>, n, &grid, 2)) return rc;
+    sample_pair_kernel<A, Spectral><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    return SSK_OK;
+}
+/// every non-null plane of the argument block 8-byte aligned: the two-samples-per-thread kernel can be used
+bool sample_planes_aligned8(const SampleArgs &a) {
+    const void *ps[] = { a.u0, a.u1, a.px, a.py, a.pz, a.w0, a.w1, a.w2, a.w3, a.dx, a.dy, a.dz, a.pdf,
+                         a.q0, a.q1, a.q2, a.q3, a.ox, a.oy, a.oz, a.dist };
+    uintptr_t acc = 0;
+    for (const void *q : ps) acc |= reinterpret_cast<uintptr_t>(q);
+    return (acc & 7u) == 0;
+}
 template <int A>
 int launch_sample_a(const ssk_ctx *ctx, bool spectral, bool vec, const SampleArgs &a, size_t n, cudaStream_t s) {
     (void) vec;
+    if (!getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a))
+        return spectral ? launch_sample_pair_t<A, true>(ctx, a, n, s) : launch_sample_pair_t<A, false>(ctx, a, n, s);
     if (spectral) return launch_sample_t<A, kSampleRays, true>(ctx, a, n, s);
     return launch_sample_t<A, kSampleRays, false>(ctx, a, n, s);
 }

@@ -17,6 +17,21 @@ namespace ssk {
 
 constexpr int kThreads = 256;
 
+// Resident CTAs per SM each kernel family is compiled for (the register cap of __launch_bounds__); overridable
+// for tuning builds (-DSSK_..._MINB=n).
+#ifndef SSK_SAMPLE_MINB
+#define SSK_SAMPLE_MINB 4      /* resident CTAs per SM the sampling kernels are compiled for (register cap); */
+#endif                         /* measured on B200, sky-only RGB: 2 -> 30.5, 3 -> 33.5, 4 -> 35.3 Gsamples/s */
+#ifndef SSK_SAMPLE_MINB_SPEC
+#define SSK_SAMPLE_MINB_SPEC 3
+#endif
+#ifndef SSK_RGBP_MINB
+#define SSK_RGBP_MINB 3
+#endif
+#ifndef SSK_SPECX_MINB
+#define SSK_SPECX_MINB 1
+#endif
+
 /// Copy the emitter block from global to shared memory (16-byte accesses) and, for FAST spectral
 /// kernels, build the bin-pair table of eval_spec (build_pair_table's layout). Ends with a barrier.
 __device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const EmitterBlock *src) {
@@ -104,7 +119,7 @@ eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restri
 /// eval / eval_direction, RGB, two consecutive rays per thread as float2 pairs (64-bit plane accesses, planes
 /// 8-byte aligned): every FP32 instruction of the model works on both rays (FFMA2 / FMUL2 / FADD2).
 template <int A>
-__global__ void __launch_bounds__(kThreads, 3)
+__global__ void __launch_bounds__(kThreads, SSK_RGBP_MINB)
 eval_rgb_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, OutPlanes3 out,
                      size_t n, float dir_sign) {
     const float *sun_rad = blk->sun_rad;
@@ -132,7 +147,7 @@ eval_rgb_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
 
 /// eval / eval_direction, spectral (4 wavelengths per ray)
 template <int A, int R>
-__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? 4 : 1)
+__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? 4 : SSK_SPECX_MINB)
 eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
                  OutPlanes4 out, size_t n, float dir_sign) {
     __shared__ __align__(16) HotBlock S;
@@ -237,6 +252,78 @@ sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
         if (Spectral) storer<R>(a.q3, i, n, q[3]);
         if (a.ox) { storer<R>(a.ox, i, n, ox); storer<R>(a.oy, i, n, oy); storer<R>(a.oz, i, n, oz); }
         if (a.dist) storer<R>(a.dist, i, n, dist);
+    }
+}
+
+// ---- two rays per thread (float2 pairs, 64-bit plane accesses; planes 8-byte aligned) -------------------
+__device__ __forceinline__ float2 ld2(const float *p, size_t i, bool two, float pad) {
+    return two ? __ldcs(reinterpret_cast<const float2 *>(p + i)) : make_float2(__ldcs(p + i), pad);
+}
+__device__ __forceinline__ void st2(float *p, size_t i, bool two, float2 v) {
+    if (two) __stcs(reinterpret_cast<float2 *>(p + i), v); else __stcs(p + i, v.x);
+}
+
+/// pdf_direction, two directions per thread
+template <int A>
+__global__ void __launch_bounds__(kThreads, 4)
+pdf_pair_kernel(const __grid_constant__ HotBlock U, Planes3 in, float *__restrict__ pdf, size_t n) {
+    const size_t stride = (size_t) gridDim.x * blockDim.x * 2;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+        const bool two = i + 1 < n;
+        Vec3p d = { ld2(in.x, i, two, 0.f), ld2(in.y, i, two, 0.f), ld2(in.z, i, two, 1.f) };
+        st2(pdf, i, two, pdf_direction_p<A>(U, d, true, two));
+    }
+}
+
+/// sample_direction, two samples per thread (see sample_kernel)
+template <int A, bool Spectral>
+__global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
+sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
+    stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x * 2;
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+        const bool two = i + 1 < n;
+        DirSampleP s = sample_dir_p<A>(U, S, ld2(a.u0, i, two, 0.5f), ld2(a.u1, i, two, 0.5f));
+        st2(a.dx, i, two, s.d_world.x); st2(a.dy, i, two, s.d_world.y); st2(a.dz, i, two, s.d_world.z);
+        st2(a.pdf, i, two, s.pdf);
+        // eval(si) with si.wi = -d (sunsky.cpp:430-438)
+        float2 e[4];
+        if (Spectral) {
+            float2 w0 = ld2(a.w0, i, two, 0.f), w1 = ld2(a.w1, i, two, 0.f), w2 = ld2(a.w2, i, two, 0.f), w3 = ld2(a.w3, i, two, 0.f);
+            float ea[4], eb[4];
+            const float wa[4] = { w0.x, w1.x, w2.x, w3.x }, wb[4] = { w0.y, w1.y, w2.y, w3.y };
+            eval_spec<A>(U, S, pairs, sun_rad, Vec3{ -s.d_world.x.x, -s.d_world.y.x, -s.d_world.z.x }, wa, s.active0, ea);
+            eval_spec<A>(U, S, pairs, sun_rad, Vec3{ -s.d_world.x.y, -s.d_world.y.y, -s.d_world.z.y }, wb, s.active1 && two, eb);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) e[c] = f2(ea[c], eb[c]);
+        } else {
+            Vec3p wi = { neg2(s.d_world.x), neg2(s.d_world.y), neg2(s.d_world.z) };
+            eval_rgb_p<A>(U, sun_rad, wi, s.active0, s.active1 && two, e);
+        }
+        // Spectrum / Float -> eval * rcp(pdf) (drjit/array_router.h:225-228); res &= isfinite(res)
+        const float2 inv_pdf = A == kFast ? f2(hw_rcp(s.pdf.x), hw_rcp(s.pdf.y)) : f2(fdiv(1.f, s.pdf.x), fdiv(1.f, s.pdf.y));
+#pragma unroll
+        for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
+            float2 w = mul2(e[c], inv_pdf);
+            w = f2((fabsf(w.x) < INFINITY) ? w.x : 0.f, (fabsf(w.y) < INFINITY) ? w.y : 0.f);
+            st2(c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3, i, two, w);
+        }
+        // bounding-sphere bookkeeping (sunsky.cpp:415-421)
+        if (a.ox || a.dist) {
+            float2 px = f2(0.f, 0.f), py = px, pz = px;
+            if (a.px) { px = ld2(a.px, i, two, 0.f); py = ld2(a.py, i, two, 0.f); pz = ld2(a.pz, i, two, 0.f); }
+            Vec3p rel = { add2s(px, -U.bs_center[0]), add2s(py, -U.bs_center[1]), add2s(pz, -U.bs_center[2]) };
+            float2 nr = sqrt2(sqnorm3_p(rel));
+            float2 dd = mul2s(f2(fmaxf(U.bs_radius, nr.x), fmaxf(U.bs_radius, nr.y)), 2.f);
+            if (a.dist) st2(a.dist, i, two, dd);
+            if (a.ox) {
+                st2(a.ox, i, two, fma2(s.d_world.x, dd, px)); st2(a.oy, i, two, fma2(s.d_world.y, dd, py));
+                st2(a.oz, i, two, fma2(s.d_world.z, dd, pz));
+            }
+        }
     }
 }
 

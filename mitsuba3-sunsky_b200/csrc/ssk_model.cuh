@@ -683,6 +683,74 @@ template <int A> SSK_HD float pdf_direction(const HotBlock &U, const Vec3 &d_wor
     return combined_pdf<A>(U, xform(U.to_local, d_world), true, true);
 }
 
+// ---- two rays per thread: pdf --------------------------------------------------------------------------
+/// tgmm_sum_exact for two rays: per element the same ops and the same accumulation order
+SSK_HD float2 tgmm_sum_exact_p(const HotBlock &U, float2 phi, float2 theta) {
+    float2 pdf = f2(0.f, 0.f);
+    bool tiny0 = false, tiny1 = false;
+#pragma unroll
+    for (int i = 0; i < kGauss; ++i) {
+        if (i < U.n_pdf) {
+            float2 sx = fdiv_by_2(add2s(phi, -U.p_mu_phi[i]), splat2(U.p_sigma_phi[i]), splat2(U.p_rsigma_phi[i])),
+                   sy = fdiv_by_2(add2s(theta, -U.p_mu_theta[i]), splat2(U.p_sigma_theta[i]), splat2(U.p_rsigma_theta[i]));
+            float2 g = mul2s(dexp_2(mul2s(fma2(sy, sy, mul2(sx, sx)), -.5f)), SSK_INV_TWO_PI);
+            float2 num = mul2s(g, U.p_weight[i]);
+            tiny0 = tiny0 || fdiv_by_tiny(num.x); tiny1 = tiny1 || fdiv_by_tiny(num.y);
+            pdf = add2(pdf, fdiv_by_2(num, splat2(U.p_volume[i]), splat2(U.p_rvolume[i])));
+        }
+    }
+    if (tiny0 && !(pdf.x >= 9.313225746154785e-10f)) pdf.x = tgmm_sum_generic(U, phi.x, theta.x);
+    if (tiny1 && !(pdf.y >= 9.313225746154785e-10f)) pdf.y = tgmm_sum_generic(U, phi.y, theta.y);
+    return pdf;
+}
+/// tgmm_sum_fast for two rays: even and odd components in separate accumulators, as the scalar version
+SSK_HD float2 tgmm_sum_fast_p(const HotBlock &U, float2 phi, float2 theta) {
+    float2 acc_e = f2(0.f, 0.f), acc_o = f2(0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < kGauss; ++i) {
+        if (i < U.n_pdf) {
+            float2 sx = mul2s(add2s(phi, -U.p_mu_phi[i]), U.p_k_phi[i]), sy = mul2s(add2s(theta, -U.p_mu_theta[i]), U.p_k_theta[i]);
+            float2 e = fma2(sy, sy, mul2(sx, sx));
+            float2 ex = f2(hw_ex2(-e.x), hw_ex2(-e.y));
+            if (i & 1) acc_o = fma2(splat2(U.p_wv[i]), ex, acc_o);
+            else acc_e = fma2(splat2(U.p_wv[i]), ex, acc_e);
+        }
+    }
+    return add2(acc_e, acc_o);
+}
+template <int A> SSK_HD float2 tgmm_pdf_p(const HotBlock &U, float2 phi, float2 theta, bool act0, bool act1) {
+    phi = add2s(phi, -U.sun_phi_shift);
+    float2 up = add2s(phi, SSK_TWO_PI);
+    phi = sel2(phi.x < 0.f, phi.y < 0.f, up, phi);
+    float2 dn = add2s(phi, -SSK_TWO_PI);
+    phi = sel2(phi.x > SSK_TWO_PI, phi.y > SSK_TWO_PI, dn, phi);
+    act0 = act0 && theta.x >= 0.f && theta.x <= SSK_HALF_PI;
+    act1 = act1 && theta.y >= 0.f && theta.y <= SSK_HALF_PI;
+    if (!act0 && !act1) return f2(0.f, 0.f);
+    float2 r;
+    if (A == kFast) r = tgmm_sum_fast_p(U, phi, theta);
+    else if (U.pdf_generic) r = f2(tgmm_sum_generic(U, phi.x, theta.x), tgmm_sum_generic(U, phi.y, theta.y));
+    else r = tgmm_sum_exact_p(U, phi, theta);
+    return f2(act0 ? r.x : 0.f, act1 ? r.y : 0.f);
+}
+/// combined_pdf for two rays
+template <int A> SSK_HD float2 combined_pdf_p(const HotBlock &U, const Vec3p &d, bool cs0, bool cs1, bool act0, bool act1) {
+    float2 sin_theta = safe_sqrt2(fma2(d.x, d.x, mul2(d.y, d.y)));
+    act0 = act0 && d.z.x >= 0.f && sin_theta.x != 0.f;
+    act1 = act1 && d.z.y >= 0.f && sin_theta.y != 0.f;
+    sin_theta = f2(fmaxf(sin_theta.x, SSK_EPSILON), fmaxf(sin_theta.y, SSK_EPSILON));
+    float2 phi = datan2_2(d.y, d.x), theta = unit_angle_z_p(d);
+    float2 t = tgmm_pdf_p<A>(U, phi, theta, act0, act1);
+    float2 sky_pdf = A == kFast ? mul2(t, f2(hw_rcp(sin_theta.x), hw_rcp(sin_theta.y))) : fdiv2(t, sin_theta);
+    Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
+    float2 dn = dot3_p(n, d);
+    float2 sun_pdf = f2((!cs0 || dn.x >= U.cos_cutoff) ? U.sun_pdf_const : 0.f, (!cs1 || dn.y >= U.cos_cutoff) ? U.sun_pdf_const : 0.f);
+    return lerp2(sun_pdf, sky_pdf, splat2(U.sky_w));
+}
+template <int A> SSK_HD float2 pdf_direction_p(const HotBlock &U, const Vec3p &d_world, bool act0, bool act1) {
+    return combined_pdf_p<A>(U, xform_p(U.to_local, d_world), true, true, act0, act1);
+}
+
 /// DiscreteDistribution::sample_reuse, JIT flavour (distr_1d.h:116-134,172-182; drjit/util.h:136-181)
 SSK_HD int tgmm_pick(const HotBlock &U, const HotBlock &S, float u, float &reuse) {
     float s = u * U.cdf_sum;
@@ -747,6 +815,72 @@ template <int A> SSK_HD DirSample sample_dir(const HotBlock &U, const HotBlock &
     r.active = dir.z >= 0.f;
     r.d_world = xform(U.to_world, dir);
     r.pdf = combined_pdf<A>(U, dir, pick_sky, r.active);
+    return r;
+}
+
+// ---- two samples per thread: sample_direction ------------------------------------------------------------
+SSK_HD Vec3p sphdir_p(float2 theta, float2 phi) {
+    float2 st, ct, sp, cp;
+    dsincos_2(theta, st, ct);
+    dsincos_2(phi, sp, cp);
+    return { mul2(cp, st), mul2(sp, st), ct };
+}
+/// sample_sky for two samples (see sample_sky)
+SSK_HD Vec3p sample_sky_p(const HotBlock &U, const HotBlock &S, float2 u0, float2 u1) {
+    float t0, t1;
+    int i0 = tgmm_pick(U, S, u0.x, t0), i1 = tgmm_pick(U, S, u0.y, t1);
+    float2 sx = lerp2(f2(S.g_cdf_a_phi[i0], S.g_cdf_a_phi[i1]), f2(S.g_cdf_b_phi[i0], S.g_cdf_b_phi[i1]), f2(t0, t1)),
+           sy = lerp2(f2(S.g_cdf_a_theta[i0], S.g_cdf_a_theta[i1]), f2(S.g_cdf_b_theta[i0], S.g_cdf_b_theta[i1]), u1);
+    sx = f2(fmaxf(fminf(sx.x, SSK_ONE_MINUS_EPSILON), SSK_EPSILON), fmaxf(fminf(sx.y, SSK_ONE_MINUS_EPSILON), SSK_EPSILON));
+    sy = f2(fmaxf(fminf(sy.x, SSK_ONE_MINUS_EPSILON), SSK_EPSILON), fmaxf(fminf(sy.y, SSK_ONE_MINUS_EPSILON), SSK_EPSILON));
+    float2 ex = mul2s(derfinv_2(add2x(mul2s(sx, 2.f), splat2(-1.f))), SSK_SQRT_TWO),
+           ey = mul2s(derfinv_2(add2x(mul2s(sy, 2.f), splat2(-1.f))), SSK_SQRT_TWO);
+    float2 phi = add2x(mul2(ex, f2(S.g_sigma_phi[i0], S.g_sigma_phi[i1])), f2(S.g_mu_phi[i0], S.g_mu_phi[i1])),
+           theta = add2x(mul2(ey, f2(S.g_sigma_theta[i0], S.g_sigma_theta[i1])), f2(S.g_mu_theta[i0], S.g_mu_theta[i1]));
+    phi = add2s(phi, U.sun_phi_shift);
+    theta = f2(fminf(theta.x, SSK_HALF_PI - SSK_EPSILON), fminf(theta.y, SSK_HALF_PI - SSK_EPSILON));
+    return sphdir_p(theta, phi);
+}
+/// sample_sun for two samples (see sample_sun)
+SSK_HD Vec3p sample_sun_p(const HotBlock &P, float2 u0, float2 u1) {
+    float2 x = fma2(splat2(2.f), u0, splat2(-1.f)), y = fma2(splat2(2.f), u1, splat2(-1.f));
+    bool z0 = x.x == 0.f && y.x == 0.f, z1 = x.y == 0.f && y.y == 0.f;
+    bool q0 = fabsf(x.x) < fabsf(y.x), q1 = fabsf(x.y) < fabsf(y.y);
+    float2 r = sel2(q0, q1, y, x), rp = sel2(q0, q1, x, y);
+    float2 phi = fdiv2(mul2(splat2(0.25f * SSK_PI), rp), r);
+    float2 alt = add2(splat2(SSK_HALF_PI), neg2(phi));
+    phi = sel2(q0, q1, alt, phi);
+    phi = sel2(z0, z1, f2(0.f, 0.f), phi);
+    float2 s, c;
+    dsincos_2(phi, s, c);
+    float2 px = mul2(r, c), py = mul2(r, s);
+    float2 pn = fma2(py, py, mul2(px, px));
+    float2 z = add2x(mul2s(add2(splat2(1.f), neg2(pn)), P.one_minus_cos_cutoff), splat2(P.cos_cutoff));
+    float2 k = safe_sqrt2(mul2s(subp2(splat2(2.f), mul2s(pn, P.one_minus_cos_cutoff)), P.one_minus_cos_cutoff));
+    px = mul2(px, k); py = mul2(py, k);
+    return { fma2(splat2(P.sun_n[0]), z, fma2(splat2(P.sun_t[0]), py, mul2s(px, P.sun_s[0]))),
+             fma2(splat2(P.sun_n[1]), z, fma2(splat2(P.sun_t[1]), py, mul2s(px, P.sun_s[1]))),
+             fma2(splat2(P.sun_n[2]), z, fma2(splat2(P.sun_t[2]), py, mul2s(px, P.sun_s[2]))) };
+}
+/// Direction part of sample_direction for two samples (see sample_dir)
+struct DirSampleP { Vec3p d_world; float2 pdf; bool active0, active1; };
+template <int A> SSK_HD DirSampleP sample_dir_p(const HotBlock &U, const HotBlock &S, float2 u0, float2 u1) {
+    bool sky0 = u0.x < U.sky_w, sky1 = u0.y < U.sky_w;
+    Vec3p dir = { f2(0.f, 0.f), f2(0.f, 0.f), f2(0.f, 0.f) };
+    if (sky0 || sky1) {
+        float2 v = f2(sky0 ? fdiv_by_safe(u0.x, U.sky_w, U.r_sky_w) : 0.5f, sky1 ? fdiv_by_safe(u0.y, U.sky_w, U.r_sky_w) : 0.5f);
+        dir = sample_sky_p(U, S, v, u1);
+    }
+    if (!sky0 || !sky1) {
+        float2 v = f2(sky0 ? 0.5f : fdiv_by_safe(u0.x - U.sky_w, U.one_minus_sky_w, U.r_one_minus_sky_w),
+                      sky1 ? 0.5f : fdiv_by_safe(u0.y - U.sky_w, U.one_minus_sky_w, U.r_one_minus_sky_w));
+        Vec3p ds = sample_sun_p(U, v, u1);
+        dir = { sel2(sky0, sky1, dir.x, ds.x), sel2(sky0, sky1, dir.y, ds.y), sel2(sky0, sky1, dir.z, ds.z) };
+    }
+    DirSampleP r;
+    r.active0 = dir.z.x >= 0.f; r.active1 = dir.z.y >= 0.f;
+    r.d_world = xform_p(U.to_world, dir);
+    r.pdf = combined_pdf_p<A>(U, dir, sky0, sky1, r.active0, r.active1);
     return r;
 }
 

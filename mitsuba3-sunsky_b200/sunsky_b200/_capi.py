@@ -5,7 +5,7 @@ import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(_PKG)                      # mitsuba3-sunsky_b200/
-LIB_PATH = os.path.join(ROOT, "libsunsky_b200.so")
+LIB_PATH = os.environ.get("SSK_LIB") or os.path.join(ROOT, "libsunsky_b200.so")   # SSK_LIB: tuning builds only
 DATASET_DIR = os.path.join(ROOT, "data", "resources", "sunsky", "datasets")
 
 SSK_OK, SSK_ERR_INVALID, SSK_ERR_IO, SSK_ERR_CUDA, SSK_ERR_UNSUPPORTED = 0, -1, -2, -3, -4

@@ -44,11 +44,47 @@ void hostdbg_eval(void *h, size_t n, const float *wi, const float *wav, float *o
 }
 void hostdbg_pdf(void *h, size_t n, const float *d, float *pdf) {
     HostEmitter &E = *(HostEmitter *) h;
+    if (getenv("HOSTDBG_PAIR")) {
+        for (size_t i = 0; i < n; i += 2) {
+            bool two = i + 1 < n;
+            Vec3p v = { f2(d[i], two ? d[i + 1] : 0.f), f2(d[n + i], two ? d[n + i + 1] : 0.f), f2(d[2 * n + i], two ? d[2 * n + i + 1] : 1.f) };
+            float2 r = E.block.arith ? pdf_direction_p<1>(E.block, v, true, two) : pdf_direction_p<0>(E.block, v, true, two);
+            pdf[i] = r.x; if (two) pdf[i + 1] = r.y;
+        }
+        return;
+    }
     for (size_t i = 0; i < n; ++i) { Vec3 v{ d[i], d[n + i], d[2 * n + i] }; pdf[i] = E.block.arith ? pdf_direction<1>(E.block, v) : pdf_direction<0>(E.block, v); }
 }
 void hostdbg_sample(void *h, size_t n, const float *u, const float *wav, float *d, float *pdf, float *weight) {
     HostEmitter &E = *(HostEmitter *) h;
     int C = E.spectral ? 4 : 3;
+    if (getenv("HOSTDBG_PAIR")) {
+        for (size_t i = 0; i < n; i += 2) {
+            bool two = i + 1 < n;
+            float2 a = f2(u[i], two ? u[i + 1] : .5f), b = f2(u[n + i], two ? u[n + i + 1] : .5f);
+            DirSampleP s = E.block.arith ? sample_dir_p<1>(E.block, E.block, a, b) : sample_dir_p<0>(E.block, E.block, a, b);
+            float2 e[4];
+            if (E.spectral) {
+                float ea[4], eb[4] = { 0, 0, 0, 0 };
+                size_t j = two ? i + 1 : i;
+                float wa[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }, wb[4] = { wav[j], wav[n + j], wav[2 * n + j], wav[3 * n + j] };
+                Vec3 va = { -s.d_world.x.x, -s.d_world.y.x, -s.d_world.z.x }, vb = { -s.d_world.x.y, -s.d_world.y.y, -s.d_world.z.y };
+                if (E.block.arith) { eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, va, wa, s.active0, ea); eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, vb, wb, s.active1, eb); }
+                else { eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, va, wa, s.active0, ea); eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, vb, wb, s.active1, eb); }
+                for (int c = 0; c < 4; ++c) e[c] = f2(ea[c], eb[c]);
+            } else {
+                Vec3p wi = { neg2(s.d_world.x), neg2(s.d_world.y), neg2(s.d_world.z) };
+                if (E.block.arith) eval_rgb_p<1>(E.block, E.block.sun_rad, wi, s.active0, s.active1, e); else eval_rgb_p<0>(E.block, E.block.sun_rad, wi, s.active0, s.active1, e);
+            }
+            for (int k = 0; k < (two ? 2 : 1); ++k) {
+                size_t o = i + k;
+                d[o] = k ? s.d_world.x.y : s.d_world.x.x; d[n + o] = k ? s.d_world.y.y : s.d_world.y.x; d[2 * n + o] = k ? s.d_world.z.y : s.d_world.z.x;
+                float pv = k ? s.pdf.y : s.pdf.x; pdf[o] = pv;
+                for (int c = 0; c < C; ++c) { float w = (k ? e[c].y : e[c].x) * (1.f / pv); weight[c * n + o] = (fabsf(w) < INFINITY) ? w : 0.f; }
+            }
+        }
+        return;
+    }
     for (size_t i = 0; i < n; ++i) {
         DirSample s = E.block.arith ? sample_dir<1>(E.block, E.block, u[i], u[n + i]) : sample_dir<0>(E.block, E.block, u[i], u[n + i]);
         d[i] = s.d_world.x; d[n + i] = s.d_world.y; d[2 * n + i] = s.d_world.z; pdf[i] = s.pdf;
