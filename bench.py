@@ -30,8 +30,8 @@ FLOPS = dict(eval_spectral=1013, eval_rgb=426, pdf=761, sample_rgb=1776)      # 
 BYTES = dict(eval_spectral=44, eval_rgb=24, pdf=16, sample_rgb=36)
 METRIC = "sky+sun radiance Gevals/s (spectral eval, 16M directions)"
 # dram__bytes_read.sum + dram__bytes_write.sum of one eval_spec_kernel launch on 2^24 rays (ncu --set full,
-# profiles/r1_ncu_summary.md); the algorithmic figure is 44 B x 2^24 = 738 MB (part of the output is still in L2)
-NCU_TRAFFIC = {"fast": 698.3e6, "exact": 701.3e6}
+# profiles/r1_summary.md); the algorithmic figure is 44 B x 2^24 = 738 MB (part of the output is still in L2)
+NCU_TRAFFIC = {"fast": 699.0e6, "exact": 701.3e6}
 
 
 def peaks():

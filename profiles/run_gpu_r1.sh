@@ -11,6 +11,9 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "sm
 python bench.py --impl reference --steps 5 --warmup 1 > $O/bench_reference.json 2> $O/bench_reference.err; echo "ref rc=$?"
 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench rc=$?"
 python bench.py --arith exact --no-extra --steps 100 > $O/bench_exact.json 2> $O/bench_exact.err; echo "bench exact rc=$?"
+# launch list of the bench command itself (its kernel share of the step is what must agree with the live timing)
+ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_bench.csv \
+    python bench.py --steps 20 --warmup 3 --no-extra > $O/ncu_launches_bench.log 2>&1; echo "bench launch list rc=$?"
 K="eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,sample_spec,envmap"
 for A in fast exact; do
 python profiles/prof_driver.py --kernels $K --reps 3 --arith $A > $O/prof_plain_$A.log 2>&1 &&
