@@ -143,6 +143,25 @@ int ssk_sample_direction_device(const ssk_ctx *ctx, const float *const u[2], con
                                 const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
                                 float *const weight[4], float *const p[3], float *dist, void *stream);
 
+/* sample_wavelengths(si, sample) (src/emitters/sunsky.cpp:463-480).
+ *   spectral: wavelengths[k] = ContinuousDistribution::sample_pdf(sample_shifted<4>(sample)[k]) over the emitter's
+ *   mean sun+sky spectrum on [360, 720] nm (include/mitsuba/core/distr_1d.h:468-502, core/math.h:408-431), and
+ *   weight = eval(si with those wavelengths) / pdf. sample: one float per ray. wavelengths[4], weight[4]: outputs.
+ *   RGB: the reference returns Wavelength(0) and eval(si); sample and wavelengths are ignored (may be NULL),
+ *   weight[3] = eval. */
+int ssk_sample_wavelengths_device(const ssk_ctx *ctx, const float *const wi[3], const float *sample, size_t n,
+                                  float *const wavelengths[4], float *const weight[4], void *stream);
+
+/* sample_ray(time, wavelength_sample, sample2, sample3) (src/emitters/sunsky.cpp:354-397), fused: origin offset
+ * on the bounding-sphere disc (sample2), technique selection + TGMM / sun-cone direction (sample3), pdf including
+ * the disc, wavelengths + eval, weight = eval / (pdf_wavelength * pdf) (non-finite -> 0).
+ *   wl_sample: wavelength sample per ray (spectral; NULL for RGB). s2[2], s3[2]: the two Point2f samples.
+ *   o[3], d[3]: ray origin and direction (d points from the sky into the scene). wavelengths[4]: ray.wavelengths
+ *   (spectral; NULL for RGB). weight[C]: returned spectrum. ray.time = time is reconstructed by the caller. */
+int ssk_sample_ray_device(const ssk_ctx *ctx, const float *wl_sample, const float *const s2[2], const float *const s3[2],
+                          size_t n, float *const o[3], float *const d[3], float *const wavelengths[4],
+                          float *const weight[4], void *stream);
+
 /* Equirectangular environment maps (BASELINE configs 4 and 5): one map per context, direction
  * generated from the pixel centre, no direction buffer is read. Pixel (x, y) looks along
  *   phi = 2*pi*(x + 0.5)/width, theta = pi*(y + 0.5)/height, d = (sin(theta)cos(phi), sin(theta)sin(phi), cos(theta))
@@ -160,6 +179,11 @@ int ssk_pdf_direction_host(const ssk_ctx *ctx, const float *const d[3], size_t n
 int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
                               const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
                               float *const weight[4], float *const p[3], float *dist);
+int ssk_sample_wavelengths_host(const ssk_ctx *ctx, const float *const wi[3], const float *sample, size_t n,
+                                float *const wavelengths[4], float *const weight[4]);
+int ssk_sample_ray_host(const ssk_ctx *ctx, const float *wl_sample, const float *const s2[2], const float *const s3[2],
+                        size_t n, float *const o[3], float *const d[3], float *const wavelengths[4],
+                        float *const weight[4]);
 
 /* Test hook: out[i] = a[i] / b[i] computed with the reciprocal-based division the kernels use for
  * per-emitter constant divisors (device pointers); the tests compare it with IEEE division. */

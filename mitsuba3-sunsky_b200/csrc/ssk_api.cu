@@ -259,6 +259,73 @@ int launch_sample(const ssk_ctx *ctx, const float *const u[2], const float *cons
     return SSK_OK;
 }
 
+/// sample_wavelengths: spectral -> wavelength importance sampling + eval / pdf; RGB -> eval (sunsky.cpp:463-480)
+int launch_sample_wavelengths(const ssk_ctx *ctx, const float *const wi[3], const float *sample, size_t n,
+                              float *const wav[4], float *const weight[4], cudaStream_t s) {
+    if (int rc = need_device(ctx)) return rc;
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    if (!spectral) return launch_eval(ctx, wi, nullptr, n, weight, 1.f, s);      // Wavelength(0), eval(si)
+    if (!wi || !wi[0] || !wi[1] || !wi[2] || !sample) return fail(SSK_ERR_INVALID, "null direction / sample planes");
+    if (!wav || !weight) return fail(SSK_ERR_INVALID, "null output planes");
+    for (int c = 0; c < 4; ++c) if (!wav[c] || !weight[c]) return fail(SSK_ERR_INVALID, "null output plane");
+    if (n == 0) return SSK_OK;
+    Planes3 i3 = { wi[0], wi[1], wi[2] };
+    OutPlanes4 w4 = { wav[0], wav[1], wav[2], wav[3] }, q4 = { weight[0], weight[1], weight[2], weight[3] };
+    int grid = 1;
+    if (fast(ctx)) {
+        if (int rc = occupancy_grid(ctx, sample_wavelengths_kernel<kFast>, n, &grid, 1)) return rc;
+        sample_wavelengths_kernel<kFast><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, sample, w4, q4, n);
+    } else {
+        if (int rc = occupancy_grid(ctx, sample_wavelengths_kernel<kExact>, n, &grid, 1)) return rc;
+        sample_wavelengths_kernel<kExact><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, sample, w4, q4, n);
+    }
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+template <int A, bool Spectral>
+int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStream_t s) {
+    int grid = 1;
+    if (int rc = occupancy_grid(ctx, sample_ray_kernel<A, Spectral>, n, &grid, 1)) return rc;
+    sample_ray_kernel<A, Spectral><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    return SSK_OK;
+}
+/// sample_ray (sunsky.cpp:354-397); `time` passes through the reference untouched and is not an argument
+int launch_sample_ray(const ssk_ctx *ctx, const float *wl_sample, const float *const s2[2], const float *const s3[2],
+                      size_t n, float *const o[3], float *const d[3], float *const wav[4], float *const weight[4],
+                      cudaStream_t s) {
+    if (int rc = need_device(ctx)) return rc;
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    const int C = spectral ? 4 : 3;
+    if (!s2 || !s2[0] || !s2[1] || !s3 || !s3[0] || !s3[1]) return fail(SSK_ERR_INVALID, "null sample planes");
+    if (!o || !o[0] || !o[1] || !o[2] || !d || !d[0] || !d[1] || !d[2] || !weight)
+        return fail(SSK_ERR_INVALID, "null output planes");
+    RayArgs a = {};
+    a.s2x = s2[0]; a.s2y = s2[1]; a.s3x = s3[0]; a.s3y = s3[1];
+    a.ox = o[0]; a.oy = o[1]; a.oz = o[2]; a.dx = d[0]; a.dy = d[1]; a.dz = d[2];
+    if (spectral) {
+        if (!wl_sample) return fail(SSK_ERR_INVALID, "spectral mode needs the wavelength sample plane");
+        if (!wav || !wav[0] || !wav[1] || !wav[2] || !wav[3])
+            return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength output planes");
+        a.wl_sample = wl_sample; a.w0 = wav[0]; a.w1 = wav[1]; a.w2 = wav[2]; a.w3 = wav[3];
+    }
+    float *q[4] = { nullptr, nullptr, nullptr, nullptr };
+    for (int c = 0; c < C; ++c) {
+        if (!weight[c]) return fail(SSK_ERR_INVALID, "null weight plane");
+        q[c] = weight[c];
+    }
+    a.q0 = q[0]; a.q1 = q[1]; a.q2 = q[2]; a.q3 = q[3];
+    if (n == 0) return SSK_OK;
+    int rc;
+    if (fast(ctx)) rc = spectral ? launch_sample_ray_t<kFast, true>(ctx, a, n, s) : launch_sample_ray_t<kFast, false>(ctx, a, n, s);
+    else rc = spectral ? launch_sample_ray_t<kExact, true>(ctx, a, n, s) : launch_sample_ray_t<kExact, false>(ctx, a, n, s);
+    if (rc) return rc;
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
 // ---- host entry points: chunked H2D -> kernel -> D2H over 3 streams with pinned staging ---------
 int ensure_staging(const ssk_ctx *ctx, int planes) {
     Staging &st = ctx->st;
@@ -442,6 +509,7 @@ int ssk_set_scene(ssk_ctx *ctx, const float *bmin, const float *bmax) {
     }
     for (int i = 0; i < 3; ++i) E.block.bs_center[i] = E.bs_center[i];
     E.block.bs_radius = E.bs_radius;
+    set_ray_pdf_scale(E.block);
     return upload_block(ctx);
 }
 
@@ -645,6 +713,51 @@ int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const
         float *od = want_dist ? dout[o++] : nullptr;
         return launch_sample(ctx, din, has_p ? dp : nullptr, spectral ? dw : nullptr, m, dout, dout[3], wq,
                              want_p ? op : nullptr, od, s);
+    });
+}
+
+int ssk_sample_wavelengths_device(const ssk_ctx *ctx, const float *const wi[3], const float *sample, size_t n,
+                                  float *const wav[4], float *const weight[4], void *stream) {
+    return launch_sample_wavelengths(ctx, wi, sample, n, wav, weight, (cudaStream_t) stream);
+}
+int ssk_sample_ray_device(const ssk_ctx *ctx, const float *wl_sample, const float *const s2[2], const float *const s3[2],
+                          size_t n, float *const o[3], float *const d[3], float *const wav[4], float *const weight[4],
+                          void *stream) {
+    return launch_sample_ray(ctx, wl_sample, s2, s3, n, o, d, wav, weight, (cudaStream_t) stream);
+}
+int ssk_sample_wavelengths_host(const ssk_ctx *ctx, const float *const wi[3], const float *sample, size_t n,
+                                float *const wav[4], float *const weight[4]) {
+    if (!ctx || !wi || !weight) return fail(SSK_ERR_INVALID, "null argument");
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    if (!spectral) return ssk_eval_host(ctx, wi, nullptr, n, weight);
+    if (!sample || !wav) return fail(SSK_ERR_INVALID, "spectral mode needs the sample plane and 4 wavelength output planes");
+    const float *in[4] = { wi[0], wi[1], wi[2], sample };
+    float *out[8] = { wav[0], wav[1], wav[2], wav[3], weight[0], weight[1], weight[2], weight[3] };
+    for (int k = 0; k < 4; ++k) if (!in[k]) return fail(SSK_ERR_INVALID, "null input plane");
+    for (int k = 0; k < 8; ++k) if (!out[k]) return fail(SSK_ERR_INVALID, "null output plane");
+    return host_pipeline(ctx, in, 4, out, 8, n, [&](const float **din, float **dout, size_t m, cudaStream_t s) {
+        return launch_sample_wavelengths(ctx, din, din[3], m, dout, dout + 4, s);
+    });
+}
+int ssk_sample_ray_host(const ssk_ctx *ctx, const float *wl_sample, const float *const s2[2], const float *const s3[2],
+                        size_t n, float *const o[3], float *const d[3], float *const wav[4], float *const weight[4]) {
+    if (!ctx || !s2 || !s3 || !o || !d || !weight) return fail(SSK_ERR_INVALID, "null argument");
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    const int C = spectral ? 4 : 3;
+    if (spectral && (!wl_sample || !wav)) return fail(SSK_ERR_INVALID, "spectral mode needs the wavelength sample and output planes");
+    const float *in[5]; int n_in = 0;
+    in[n_in++] = s2[0]; in[n_in++] = s2[1]; in[n_in++] = s3[0]; in[n_in++] = s3[1];
+    if (spectral) in[n_in++] = wl_sample;
+    float *out[14]; int n_out = 0;
+    for (int k = 0; k < 3; ++k) out[n_out++] = o[k];
+    for (int k = 0; k < 3; ++k) out[n_out++] = d[k];
+    if (spectral) for (int k = 0; k < 4; ++k) out[n_out++] = wav[k];
+    for (int k = 0; k < C; ++k) out[n_out++] = weight[k];
+    for (int k = 0; k < n_in; ++k) if (!in[k]) return fail(SSK_ERR_INVALID, "null input plane");
+    for (int k = 0; k < n_out; ++k) if (!out[k]) return fail(SSK_ERR_INVALID, "null output plane");
+    return host_pipeline(ctx, in, n_in, out, n_out, n, [&](const float **din, float **dout, size_t m, cudaStream_t s) {
+        return launch_sample_ray(ctx, spectral ? din[4] : nullptr, din, din + 2, m, dout, dout + 3,
+                                 spectral ? dout + 6 : nullptr, dout + (spectral ? 10 : 6), s);
     });
 }
 

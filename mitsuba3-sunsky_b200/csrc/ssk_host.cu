@@ -185,7 +185,18 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     estimate_sky_sun_ratio(E);
     B.sky_w = E.sky_w; B.r_sky_w = 1.f / E.sky_w;
     B.one_minus_sky_w = 1.f - E.sky_w; B.r_one_minus_sky_w = 1.f / B.one_minus_sky_w;
+    for (int i = 0; i < 10; ++i) { B.wl_pdf[i] = E.spectral_pdf[i]; B.wl_cdf[i] = E.spectral_cdf[i]; }
+    B.wl_integral = E.spectral_integral; B.wl_norm = E.spectral_norm;
+    B.wl_interval = (float) ((720.0 - 360.0) / 9.0); B.wl_inv_interval = 1.f / B.wl_interval;
+    B.wl_valid_lo = E.spectral_valid[0]; B.wl_valid_hi = E.spectral_valid[1];
+    // dr::binary_search trip count: log2i(end - start) + 1 when start < end (drjit/util.h:138-139)
+    B.wl_iters = 0;
+    for (uint32_t w = (uint32_t) (B.wl_valid_hi - B.wl_valid_lo); w; w >>= 1) ++B.wl_iters;
+    set_ray_pdf_scale(B);
 }
+
+/// pdf of the origin offset in sample_ray (sunsky.cpp:381): InvPi * rcp(square(radius)), fp32
+void set_ray_pdf_scale(HotBlock &B) { B.ray_pdf_scale = SSK_INV_PI * (1.f / (B.bs_radius * B.bs_radius)); }
 
 /// estimate_sky_sun_ratio, array branch (sunsky.cpp:772-886): 200x200 Gauss-Legendre quadrature of the
 /// sky over the hemisphere and of the sun over its cone, luminance ratio, and (spectral) the
@@ -288,18 +299,27 @@ void estimate_sky_sun_ratio(HostEmitter &E) {
             all_zero &= E.spectral_pdf[i] == 0.f;
         }
         if (all_zero) for (int i = 0; i < 10; ++i) E.spectral_pdf[i] += 1.f;
+        // compute_cdf_scalar (distr_1d.h:540-590): fp64 running trapezoid sum, cast to fp32 per entry;
+        // m_valid = first / last interval with positive mass; m_integral = cdf[valid.y]
         double interval = (720.0 - 360.0) / 9.0, integral = 0.0;
+        int lo = -1, hi = -1;
         for (int i = 0; i < 9; ++i) {
             double y0 = E.spectral_pdf[i], y1 = E.spectral_pdf[i + 1];
-            integral += 0.5 * interval * (y0 + y1);
+            double value = 0.5 * interval * (y0 + y1);
+            integral += value;
             E.spectral_cdf[i] = (float) integral;
+            if (value > 0.0) { if (lo < 0) lo = i; hi = i; }
         }
         E.spectral_cdf[9] = 0.f;
-        E.spectral_integral = (float) integral;
-        E.spectral_norm = (float) (1.0 / integral);
+        if (lo < 0) { lo = 0; hi = 8; }               // unreachable: the reference throws "no probability mass"
+        E.spectral_valid[0] = lo; E.spectral_valid[1] = hi;
+        E.spectral_integral = E.spectral_cdf[hi];
+        E.spectral_norm = 1.f / E.spectral_integral;  // dr::rcp(m_integral) in fp32
     } else {
         memset(E.spectral_pdf, 0, sizeof(E.spectral_pdf));
         memset(E.spectral_cdf, 0, sizeof(E.spectral_cdf));
+        E.spectral_valid[0] = E.spectral_valid[1] = 0;
+        E.spectral_integral = E.spectral_norm = 0.f;
     }
 }
 

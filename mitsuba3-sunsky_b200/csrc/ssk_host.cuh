@@ -271,6 +271,7 @@ struct HostEmitter {
     Vec3 sun_dir_world = { 0, 0, 1 };
     float half_aperture = 0;
     float spectral_pdf[10], spectral_cdf[10], spectral_integral = 0, spectral_norm = 0;
+    int spectral_valid[2] = { 0, 0 };
     float area_ratio = 1;
     bool sun_below_horizon = false;
     bool active_record = false;
@@ -280,5 +281,6 @@ struct HostEmitter {
 void validate_params(const ssk_params &p, bool spectral);
 void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor);
 void estimate_sky_sun_ratio(HostEmitter &E);
+void set_ray_pdf_scale(HotBlock &B);
 
 } // namespace ssk

@@ -327,6 +327,65 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
     }
 }
 
+// ---- sample_wavelengths / sample_ray -------------------------------------------------------------------
+/// sample_wavelengths, spectral (sunsky.cpp:463-473): one ray per thread; 4 planes in (wi, sample), 8 planes out
+template <int A>
+__global__ void __launch_bounds__(kThreads, 3)
+sample_wavelengths_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in,
+                          const float *__restrict__ sample, OutPlanes4 wav, OutPlanes4 weight, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
+    stage_block(&S, A == kFast ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Vec3 wi = { __ldcs(in.x + i), __ldcs(in.y + i), __ldcs(in.z + i) };
+        float w[4], q[4];
+        sample_wavelengths_spec<A>(U, S, pairs, sun_rad, wi, __ldcs(sample + i), true, w, q);
+        __stcs(wav.a + i, w[0]); __stcs(wav.b + i, w[1]); __stcs(wav.c + i, w[2]); __stcs(wav.d + i, w[3]);
+        __stcs(weight.a + i, q[0]); __stcs(weight.b + i, q[1]); __stcs(weight.c + i, q[2]); __stcs(weight.d + i, q[3]);
+    }
+}
+
+struct RayArgs {
+    const float *wl_sample;             // wavelength sample (spectral only)
+    const float *s2x, *s2y, *s3x, *s3y; // sample2 (origin disc), sample3 (direction)
+    float *ox, *oy, *oz, *dx, *dy, *dz; // ray origin and direction
+    float *w0, *w1, *w2, *w3;           // sampled wavelengths (spectral only)
+    float *q0, *q1, *q2, *q3;           // weight planes
+};
+
+/// sample_ray, fused (sunsky.cpp:354-397): origin disc -> technique -> direction -> pdf -> wavelengths -> eval -> weight
+template <int A, bool Spectral>
+__global__ void __launch_bounds__(kThreads, 3)
+sample_ray_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, RayArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
+    stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        RaySample r = sample_ray_geom<A>(U, S, __ldcs(a.s2x + i), __ldcs(a.s2y + i), __ldcs(a.s3x + i), __ldcs(a.s3y + i));
+        __stcs(a.ox + i, r.origin.x); __stcs(a.oy + i, r.origin.y); __stcs(a.oz + i, r.origin.z);
+        __stcs(a.dx + i, r.d_world.x); __stcs(a.dy + i, r.d_world.y); __stcs(a.dz + i, r.d_world.z);
+        float e[4];
+        if (Spectral) {
+            float w[4];
+            sample_wavelengths_spec<A>(U, S, pairs, sun_rad, r.d_world, __ldcs(a.wl_sample + i), r.active, w, e);
+            __stcs(a.w0 + i, w[0]); __stcs(a.w1 + i, w[1]); __stcs(a.w2 + i, w[2]); __stcs(a.w3 + i, w[3]);
+        } else {
+            eval_rgb<A>(U, sun_rad, r.d_world, r.active, e);
+        }
+        // weight /= pdf (Spectrum / Float -> weight * rcp(pdf)); weight &= isfinite(weight)
+        const float inv_pdf = A == kFast ? hw_rcp(r.pdf) : fdiv(1.f, r.pdf);
+#pragma unroll
+        for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
+            float w = e[c] * inv_pdf;
+            __stcs((c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3) + i, (fabsf(w) < INFINITY) ? w : 0.f);
+        }
+    }
+}
+
 /// Direction of equirectangular pixel (x, y): phi = 2*pi*(x+.5)/W, theta = pi*(y+.5)/H
 SSK_HD Vec3 envmap_dir(int x, int y, int width, int height) {
     float phi = fdiv(SSK_TWO_PI * ((float) x + 0.5f), (float) width),

@@ -69,6 +69,14 @@ struct HotBlock {
     int32_t spectral;
     int32_t arith;
     int32_t pad_[4];
+    // --- wavelength importance sampling: ContinuousDistribution over [360, 720] nm, 10 nodes
+    //     (sunsky.cpp:869-881, distr_1d.h:286-593); RGB emitters leave it zeroed
+    float wl_pdf[10], wl_cdf[10];                    // unnormalised node densities, cumulative trapezoid sums (9 used)
+    float wl_integral, wl_norm;                      // cdf[valid.y], 1 / that
+    float wl_interval, wl_inv_interval;              // 40 nm, 1 / 40
+    int32_t wl_valid_lo, wl_valid_hi, wl_iters;      // m_valid and the binary search trip count
+    float ray_pdf_scale;                             // InvPi * rcp(radius^2) of sample_ray (sunsky.cpp:381)
+    int32_t pad2_[4];
 };
 
 /// HotBlock followed by the sun radiance table, which only lanes inside the sun disc read (from L2).
@@ -815,6 +823,93 @@ template <int A> SSK_HD DirSample sample_dir(const HotBlock &U, const HotBlock &
     r.active = dir.z >= 0.f;
     r.d_world = xform(U.to_world, dir);
     r.pdf = combined_pdf<A>(U, dir, pick_sky, r.active);
+    return r;
+}
+
+// ---- sample_wavelengths / sample_ray (sunsky.cpp:463-480, 354-397) ---------------------------------------
+/// ContinuousDistribution::sample_pdf (distr_1d.h:468-502) over the emitter's 10-node wavelength density.
+/// U: constant-bank copy (uniform scalars), S: copy with lane-indexed tables (shared memory on the device).
+SSK_HD void wavelength_sample_pdf(const HotBlock &U, const HotBlock &S, float sample, float &wav, float &pdf) {
+    sample *= U.wl_integral;
+    uint32_t start = (uint32_t) U.wl_valid_lo, end = (uint32_t) U.wl_valid_hi;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {                 // at most log2i(8) + 1 iterations (drjit/util.h:136-181)
+        if (it < U.wl_iters) {
+            uint32_t middle = (start + end) >> 1;
+            bool cond = S.wl_cdf[middle] < sample;
+            uint32_t nstart = middle + 1 < end ? middle + 1 : end;
+            start = cond ? nstart : start;
+            end = cond ? end : middle;
+        }
+    }
+    const uint32_t index = start;
+    float y0 = S.wl_pdf[index], y1 = S.wl_pdf[index + 1], c0 = index > 0 ? S.wl_cdf[index - 1] : 0.f;
+    sample = (sample - c0) * U.wl_inv_interval;
+    float t_linear = (y0 - safe_sqrt(fmaf(y0, y0, 2.f * sample * (y1 - y0)))) * fdiv(1.f, y0 - y1),
+          t_const = sample * fdiv(1.f, y0),
+          t = y0 == y1 ? t_const : t_linear;
+    wav = fmaf((float) index + t, U.wl_interval, 360.f);
+    pdf = fmaf(t, y1 - y0, y0) * U.wl_norm;
+}
+
+/// sample_wavelengths, spectral (sunsky.cpp:466-473): math::sample_shifted<Wavelength> (core/math.h:408-415),
+/// the density above per wavelength, weight = eval / pdf (Spectrum / Wavelength: element-wise division)
+template <int A>
+SSK_HD void sample_wavelengths_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs, const float *sun_rad,
+                                    const Vec3 &wi, float sample, bool active, float wav[4], float weight[4]) {
+    float pdf[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        float v = sample + 0.25f * (float) k;
+        if (v > 1.f) v -= 1.f;
+        wavelength_sample_pdf(U, S, v, wav[k], pdf[k]);
+    }
+    float e[4];
+    eval_spec<A>(U, S, pairs, sun_rad, wi, wav, active, e);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) weight[k] = A == kFast ? e[k] * hw_rcp(pdf[k]) : fdiv(e[k], pdf[k]);
+}
+
+/// warp::square_to_uniform_disk_concentric (warp.h:54-90)
+SSK_HD void disk_concentric(float u0, float u1, float &px, float &py) {
+    float x = fmaf(2.f, u0, -1.f), y = fmaf(2.f, u1, -1.f);
+    bool is_zero = x == 0.f && y == 0.f, q13 = fabsf(x) < fabsf(y);
+    float r = q13 ? y : x, rp = q13 ? x : y;
+    float phi = fdiv(0.25f * SSK_PI * rp, r);
+    if (q13) phi = SSK_HALF_PI - phi;
+    if (is_zero) phi = 0.f;
+    float s, c;
+    dsincos(phi, s, c);
+    px = r * c; py = r * s;
+}
+
+/// coordinate_system (core/vector.h:116-136), the s and t of Frame3f(n)
+SSK_HD void coordinate_system_dev(const Vec3 &n, Vec3 &s, Vec3 &t) {
+    float sign = copysignf(1.f, n.z), a = -fdiv(1.f, sign + n.z), b = n.x * n.y * a;   // dr::sign = copysign(1, v)
+    s = { mulsign(sqr(n.x) * a, n.z) + 1.f, mulsign(b, n.z), mulsign_neg(n.x, n.z) };
+    t = { b, fmaf(n.y, n.y * a, sign), -n.y };
+}
+
+/// Geometry part of sample_ray (sunsky.cpp:360-383, 390-392): direction, pdf (incl. the origin disc), origin
+struct RaySample { Vec3 d_world, origin; float pdf; bool active; };
+template <int A> SSK_HD RaySample sample_ray_geom(const HotBlock &U, const HotBlock &S, float s2x, float s2y, float s3x, float s3y) {
+    float ox, oy;
+    disk_concentric(s2x, s2y, ox, oy);
+    bool pick_sky = s3x < U.sky_w;
+    Vec3 d = pick_sky ? sample_sky(U, S, fdiv_by_safe(s3x, U.sky_w, U.r_sky_w), s3y)
+                      : sample_sun(U, fdiv_by_safe(s3x - U.sky_w, U.one_minus_sky_w, U.r_one_minus_sky_w), s3y);
+    RaySample r;
+    r.d_world = xform(U.to_world, Vec3{ -d.x, -d.y, -d.z });
+    r.active = d.z >= 0.f;
+    r.pdf = combined_pdf<A>(U, d, pick_sky, r.active) * U.ray_pdf_scale;
+    r.active = r.active && r.pdf > 0.f;
+    Vec3 fs, ft;
+    coordinate_system_dev(r.d_world, fs, ft);
+    // Frame3f(d_world).to_world((ox, oy, 0)) (frame.h:39-41), then center + (offset - d_world) * radius
+    Vec3 perp = { fmaf(r.d_world.x, 0.f, fmaf(ft.x, oy, fs.x * ox)), fmaf(r.d_world.y, 0.f, fmaf(ft.y, oy, fs.y * ox)),
+                  fmaf(r.d_world.z, 0.f, fmaf(ft.z, oy, fs.z * ox)) };
+    r.origin = { U.bs_center[0] + (perp.x - r.d_world.x) * U.bs_radius, U.bs_center[1] + (perp.y - r.d_world.y) * U.bs_radius,
+                 U.bs_center[2] + (perp.z - r.d_world.z) * U.bs_radius };
     return r;
 }
 

@@ -298,6 +298,81 @@ class SunskyEmitter:
         return (d, pdf, wgt, op, dist) if want_p else (d, pdf, wgt)
 
 
+    def sample_wavelengths(self, wi, sample=None):
+        """Emitter.sample_wavelengths(si, sample) (sunsky.cpp:463-480). wi: (3, n); sample: (n,) in [0, 1).
+        Spectral: returns (wavelengths (4, n), weight (4, n) = eval / pdf). RGB: (None, eval (3, n))."""
+        if not self.spectral:
+            return None, self.eval(wi)
+        if sample is None:
+            raise ValueError("spectral mode needs the wavelength sample of shape (n,)")
+        if _is_torch(wi):
+            import torch
+            d_pp, wi = _pp_t(wi, 3, "wi")
+            n = wi.shape[1]
+            sample = sample.contiguous()
+            if sample.dtype != torch.float32 or sample.numel() != n:
+                raise ValueError("sample: expected float32 tensor of n elements")
+            wav = torch.empty((4, n), dtype=torch.float32, device=wi.device)
+            wgt = torch.empty((4, n), dtype=torch.float32, device=wi.device)
+            w_pp, _ = _pp_t(wav, 4, "wavelengths"); q_pp, _ = _pp_t(wgt, 4, "weight")
+            _check(self._L.ssk_sample_wavelengths_device(self._ctx, d_pp, C.cast(sample.data_ptr(), _capi.FP), n,
+                                                         w_pp, q_pp, self._stream()))
+            return wav, wgt
+        planes = _planes_np(wi, 3, "wi")
+        n = planes[0].size
+        sample = np.ascontiguousarray(sample, dtype=np.float32).reshape(-1)
+        if sample.size != n:
+            raise ValueError(f"sample: expected {n} elements, got {sample.size}")
+        wav = np.empty((4, n), np.float32); wgt = np.empty((4, n), np.float32)
+        _check(self._L.ssk_sample_wavelengths_host(self._ctx, _pp(planes), sample.ctypes.data_as(_capi.FP), n,
+                                                   _pp([wav[c] for c in range(4)]), _pp([wgt[c] for c in range(4)])))
+        return wav, wgt
+
+    def sample_ray(self, wavelength_sample, sample2, sample3):
+        """Emitter.sample_ray(time, wavelength_sample, sample2, sample3) (sunsky.cpp:354-397).
+        wavelength_sample: (n,) (ignored for RGB, may be None); sample2, sample3: (2, n).
+        Returns (o (3, n), d (3, n), wavelengths (4, n) or None, weight (C, n))."""
+        Cn = self.channels
+        if _is_torch(sample2):
+            import torch
+            a_pp, sample2 = _pp_t(sample2, 2, "sample2")
+            b_pp, sample3 = _pp_t(sample3, 2, "sample3")
+            n = sample2.shape[1]
+            dev = sample2.device
+            wl_p = w_pp = wav = None
+            if self.spectral:
+                if wavelength_sample is None:
+                    raise ValueError("spectral mode needs wavelength_sample of shape (n,)")
+                wavelength_sample = wavelength_sample.contiguous()
+                if wavelength_sample.dtype != torch.float32 or wavelength_sample.numel() != n:
+                    raise ValueError("wavelength_sample: expected float32 tensor of n elements")
+                wl_p = C.cast(wavelength_sample.data_ptr(), _capi.FP)
+                wav = torch.empty((4, n), dtype=torch.float32, device=dev)
+                w_pp, _ = _pp_t(wav, 4, "wavelengths")
+            o = torch.empty((3, n), dtype=torch.float32, device=dev)
+            d = torch.empty((3, n), dtype=torch.float32, device=dev)
+            wgt = torch.empty((Cn, n), dtype=torch.float32, device=dev)
+            o_pp, _ = _pp_t(o, 3, "o"); d_pp, _ = _pp_t(d, 3, "d"); q_pp, _ = _pp_t(wgt, Cn, "weight")
+            _check(self._L.ssk_sample_ray_device(self._ctx, wl_p, a_pp, b_pp, n, o_pp, d_pp, w_pp, q_pp, self._stream()))
+            return o, d, wav, wgt
+        a = _planes_np(sample2, 2, "sample2"); b = _planes_np(sample3, 2, "sample3")
+        n = a[0].size
+        wl_p = w_pp = wav = None
+        if self.spectral:
+            if wavelength_sample is None:
+                raise ValueError("spectral mode needs wavelength_sample of shape (n,)")
+            wl = np.ascontiguousarray(wavelength_sample, dtype=np.float32).reshape(-1)
+            if wl.size != n:
+                raise ValueError(f"wavelength_sample: expected {n} elements, got {wl.size}")
+            wl_p = wl.ctypes.data_as(_capi.FP)
+            wav = np.empty((4, n), np.float32)
+            w_pp = _pp([wav[c] for c in range(4)])
+        o = np.empty((3, n), np.float32); d = np.empty((3, n), np.float32); wgt = np.empty((Cn, n), np.float32)
+        _check(self._L.ssk_sample_ray_host(self._ctx, wl_p, _pp(a), _pp(b), n, _pp([o[i] for i in range(3)]),
+                                           _pp([d[i] for i in range(3)]), w_pp, _pp([wgt[c] for c in range(Cn)])))
+        return o, d, wav, wgt
+
+
 def envmaps(emitters, width, height, wavelengths4=None, out=None):
     """Equirectangular radiance maps, one per emitter (all on one device, same mode), written by one
     kernel launch straight into a torch CUDA tensor of shape (n_maps, C, height, width)."""

@@ -49,6 +49,9 @@ def main():
         "sample_sky": lambda: sky.sample_direction(u),
         "sample_spec": lambda: ss.sample_direction(u, None, wav),
         "envmap": lambda: ssk.envmaps([er], 4096, 2048),
+        "wavelengths": lambda: es.sample_wavelengths(wi, u2),
+        "ray_rgb": lambda: sr.sample_ray(None, u, u),
+        "ray_spec": lambda: ss.sample_ray(u1, u, u),
     }
     for name in args.kernels.split(","):
         fn = runs[name]

@@ -91,6 +91,22 @@ def parity_inputs(sun_dir_world, spectral, seed=1234, n_rand=2048):
     return dict(wo=wo, wav=wav, u=u)
 
 
+SCENE_BBOX = ([-1.0, -2.0, -3.0], [4.0, 3.0, 2.0])     # set_scene box of the sample_ray parity cases
+
+
+def ray_inputs(n, seed):
+    """Extra deterministic inputs of sample_wavelengths / sample_ray: the wavelength sample and sample2
+    (sample3 reuses `u` of parity_inputs). Includes the edges 0, 1, the shift wrap points and the disc centre."""
+    rng = np.random.default_rng(seed + 977)
+    wl = rng.random(n, dtype=np.float32)
+    # not 0.25 / 0.5 / 0.75 / 1.0 themselves: a shifted sample of exactly 1 maps to 720 nm, where the reference
+    # gathers one past the end of its coefficient table (SURVEY.md appendix C4; the oracle's arrays bounds-check)
+    wl[:8] = np.array([0.0, 0.9999, 0.2499, 0.5001, 0.7501, 0.999, 1e-7, 0.2501], dtype=np.float32)
+    s2 = rng.random((2, n), dtype=np.float32)
+    s2[:, :5] = np.array([[0.5, 0.5], [0.0, 0.0], [1.0, 0.5], [0.5, 1.0], [0.25, 0.75]], dtype=np.float32).T
+    return dict(wl_sample=wl, s2=s2)
+
+
 def rel_err(a, b, floor=0.0):
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
     return np.abs(a - b) / np.maximum(np.abs(b), floor if floor > 0 else np.finfo(np.float64).tiny)

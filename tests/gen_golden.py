@@ -45,6 +45,16 @@ def main():
         d, pdf, w, p, dist = e.sample_direction(u, None, wav, want_p=True)
         out.update(s_d=d, s_pdf=pdf, s_weight=w, s_p=p, s_dist=dist)
         out["s_pdf_requery"] = e.pdf_direction(d)
+        # sample_wavelengths(si.wi = -wo) and sample_ray (after set_scene with a non-trivial bounding sphere)
+        seed = sum(map(ord, name))
+        ri = common.ray_inputs(wo.shape[1], seed)
+        out.update(wl_sample=ri["wl_sample"], s2=ri["s2"])
+        sw_wav, sw_weight = e.sample_wavelengths(-wo, ri["wl_sample"])
+        out.update(sw_wav=sw_wav, sw_weight=sw_weight)
+        e.set_scene(*common.SCENE_BBOX)
+        r_o, r_d, r_wav, r_w = e.sample_ray(ri["wl_sample"], ri["s2"], u)
+        out.update(ray_o=r_o, ray_d=r_d, ray_wav=r_wav, ray_weight=r_w)
+        out["state_bsphere"] = np.array(list(e.state().bsphere_center) + [e.state().bsphere_radius], dtype=np.float32)
         es = R.RefEmitter(spectral=spectral, flavour=0, **kw)
         out["eval_scalar"] = es.eval(-wo, wav)
         out.update(state_dict(s))

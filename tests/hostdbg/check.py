@@ -50,5 +50,16 @@ for name, (spectral, kw) in common.CONFIGS.items():
         same = (a.view(np.uint32) == b.view(np.uint32)) | (np.isnan(a) & np.isnan(b)) | ((a == 0) & (b == 0))
         return int((~same).sum())
     print(f"{name:18s} eval mism {mm(out, g['eval'])}  pdf mism {mm(pdf, g['pdf'])}  d mism {mm(d, g['s_d'])}  spdf mism {mm(sp, g['s_pdf'])} weight mism {mm(sw, g['s_weight'])}   maxrel eval {common.max_rel_err(out, g['eval'])} pdf {common.max_rel_err(pdf, g['pdf'])}")
+    wl = np.ascontiguousarray(g['wl_sample']); s2 = np.ascontiguousarray(g['s2'])
+    if spectral:
+        ww = np.empty((4, n), np.float32); wq = np.empty((4, n), np.float32)
+        H.hostdbg_sample_wavelengths(C.c_void_p(h), C.c_size_t(n), fp(wi), fp(wl), fp(ww), fp(wq))
+        print(f"{'':18s} sample_wavelengths: wav mism {mm(ww, g['sw_wav'])} weight mism {mm(wq, g['sw_weight'])} maxrel {common.max_rel_err(wq, g['sw_weight'])}")
+    H.hostdbg_set_bsphere(C.c_void_p(h), fp(np.ascontiguousarray(g['state_bsphere'])))
+    ro = np.empty((3, n), np.float32); rd = np.empty((3, n), np.float32); rw = np.zeros((4, n), np.float32); rq = np.empty((Cn, n), np.float32)
+    H.hostdbg_sample_ray(C.c_void_p(h), C.c_size_t(n), fp(wl), fp(s2), fp(u), fp(ro), fp(rd), fp(rw), fp(rq))
+    print(f"{'':18s} sample_ray: o mism {mm(ro, g['ray_o'])} d mism {mm(rd, g['ray_d'])} wav mism {mm(rw, g['ray_wav'])} weight mism {mm(rq, g['ray_weight'])} maxrel {common.max_rel_err(rq, g['ray_weight'])}")
+    if only:
+        np.savez('/tmp/hostdbg_ray_%s.npz' % name, ro=ro, rd=rd, rw=rw, rq=rq)
     if only:
         np.savez('/tmp/hostdbg_%s.npz' % name, out=out, pdf=pdf, d=d, sp=sp, sw=sw)

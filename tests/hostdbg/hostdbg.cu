@@ -95,6 +95,41 @@ void hostdbg_sample(void *h, size_t n, const float *u, const float *wav, float *
         for (int c = 0; c < C; ++c) { float w = e[c] * (1.f / s.pdf); weight[c * n + i] = (fabsf(w) < INFINITY) ? w : 0.f; }
     }
 }
+void hostdbg_set_bsphere(void *h, const float *c4) {
+    HostEmitter &E = *(HostEmitter *) h;
+    for (int i = 0; i < 3; ++i) E.bs_center[i] = E.block.bs_center[i] = c4[i];
+    E.bs_radius = E.block.bs_radius = c4[3];
+    set_ray_pdf_scale(E.block);
+}
+void hostdbg_sample_wavelengths(void *h, size_t n, const float *wi, const float *sample, float *wav, float *weight) {
+    HostEmitter &E = *(HostEmitter *) h;
+    for (size_t i = 0; i < n; ++i) {
+        Vec3 v = { wi[i], wi[n + i], wi[2 * n + i] };
+        float w[4], q[4];
+        if (E.block.arith) sample_wavelengths_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, v, sample[i], true, w, q);
+        else sample_wavelengths_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, v, sample[i], true, w, q);
+        for (int c = 0; c < 4; ++c) { wav[c * n + i] = w[c]; weight[c * n + i] = q[c]; }
+    }
+}
+void hostdbg_sample_ray(void *h, size_t n, const float *wl, const float *s2, const float *s3, float *o, float *d, float *wav, float *weight) {
+    HostEmitter &E = *(HostEmitter *) h;
+    int C = E.spectral ? 4 : 3;
+    for (size_t i = 0; i < n; ++i) {
+        RaySample r = E.block.arith ? sample_ray_geom<1>(E.block, E.block, s2[i], s2[n + i], s3[i], s3[n + i])
+                                    : sample_ray_geom<0>(E.block, E.block, s2[i], s2[n + i], s3[i], s3[n + i]);
+        o[i] = r.origin.x; o[n + i] = r.origin.y; o[2 * n + i] = r.origin.z;
+        d[i] = r.d_world.x; d[n + i] = r.d_world.y; d[2 * n + i] = r.d_world.z;
+        float e[4] = { 0, 0, 0, 0 }, w[4] = { 0, 0, 0, 0 };
+        if (E.spectral) {
+            if (E.block.arith) sample_wavelengths_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, r.d_world, wl[i], r.active, w, e);
+            else sample_wavelengths_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, r.d_world, wl[i], r.active, w, e);
+            for (int c = 0; c < 4; ++c) wav[c * n + i] = w[c];
+        } else {
+            if (E.block.arith) eval_rgb<1>(E.block, E.block.sun_rad, r.d_world, r.active, e); else eval_rgb<0>(E.block, E.block.sun_rad, r.d_world, r.active, e);
+        }
+        for (int c = 0; c < C; ++c) { float q = e[c] * (1.f / r.pdf); weight[c * n + i] = (fabsf(q) < INFINITY) ? q : 0.f; }
+    }
+}
 void hostdbg_math(int op, size_t n, const float *a, const float *b, float *o) {
     for (size_t i = 0; i < n; ++i) {
         float x = a[i];

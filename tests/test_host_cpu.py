@@ -49,6 +49,17 @@ def test_state_matches_reference_bitwise(ssk, name):
         assert common.bit_equal(mine[:k], ref[:k]), f"{name}: {f} differs (max abs {np.abs(mine[:k] - ref[:k]).max()})"
 
 
+@pytest.mark.parametrize("name", [n for n, (sp, _) in common.CONFIGS.items() if sp])
+def test_wavelength_distribution_matches_reference_bitwise(ssk, name):
+    """m_spectral_distr (sunsky.cpp:869-881): node densities, cumulative trapezoid sums, integral, normalisation."""
+    g = emitters.golden(name)
+    s = emitters.make(ssk, name, device=-1, g=g).state()
+    assert common.bit_equal(np.array(s.spectral_pdf[:10], np.float32), g["state_spectral_pdf"][:10])
+    assert common.bit_equal(np.array(s.spectral_cdf[:9], np.float32), g["state_spectral_cdf"][:9])
+    assert common.bit_equal(np.float32(s.spectral_integral), g["state_spectral_integral"])
+    assert common.bit_equal(np.float32(s.spectral_normalization), g["state_spectral_normalization"])
+
+
 def test_state_against_live_reference(ssk, ref):
     """Same check against the reference library itself on configurations that are not in the fixtures."""
     rng = np.random.default_rng(5)
@@ -192,3 +203,8 @@ def test_golden_reproducible_from_reference(ref):
         assert common.bit_equal(r.pdf_direction(g["wo"]), g["pdf"])
         d, pdf, w = r.sample_direction(g["u"], None, wav)
         assert common.bit_equal(d, g["s_d"]) and common.bit_equal(pdf, g["s_pdf"]) and common.bit_equal(w, g["s_weight"])
+        sw_wav, sw_w = r.sample_wavelengths(-g["wo"], g["wl_sample"])
+        assert common.bit_equal(sw_w, g["sw_weight"]) and (not spectral or common.bit_equal(sw_wav, g["sw_wav"]))
+        r.set_scene(*common.SCENE_BBOX)
+        ro, rd, rwav, rw = r.sample_ray(g["wl_sample"], g["s2"], g["u"])
+        assert common.bit_equal(ro, g["ray_o"]) and common.bit_equal(rd, g["ray_d"]) and common.bit_equal(rw, g["ray_weight"])

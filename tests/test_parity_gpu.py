@@ -306,6 +306,82 @@ def test_fast_mode_matches_golden(ssk, name):
     assert_close(w, g["s_weight"], f"{name} fast weight", exact=False)
 
 
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+@pytest.mark.parametrize("name", list(common.CONFIGS))
+def test_sample_wavelengths_matches_golden(ssk, name, arith):
+    """sample_wavelengths(si.wi = -wo, sample): wavelengths bit-identical in both modes, weight = eval / pdf."""
+    g = emitters.golden(name)
+    e = emitters.make(ssk, name, g=g, arith=arith)
+    wav, w = e.sample_wavelengths(-g["wo"], g["wl_sample"])
+    if e.spectral:
+        assert common.bit_equal(wav, g["sw_wav"]), f"{name}: sampled wavelengths are not bit-identical"
+        assert (wav >= 360).all() and (wav <= 720).all()
+        assert_close(w, g["sw_weight"], f"{name} sample_wavelengths weight", exact=arith == "exact")
+    else:
+        assert wav is None
+        assert_close(w, g["eval"], f"{name} sample_wavelengths (RGB) = eval", exact=arith == "exact")
+
+
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+@pytest.mark.parametrize("name", list(common.CONFIGS))
+def test_sample_ray_matches_golden(ssk, name, arith):
+    """sample_ray after set_scene: origin, direction and wavelengths bit-identical in both modes."""
+    g = emitters.golden(name)
+    e = emitters.make(ssk, name, g=g, arith=arith)
+    e.set_scene(*common.SCENE_BBOX)
+    st = e.state()
+    assert common.bit_equal(np.array(list(st.bsphere_center) + [st.bsphere_radius], np.float32), g["state_bsphere"])
+    o, d, wav, w = e.sample_ray(g["wl_sample"], g["s2"], g["u"])
+    assert np.abs(d - g["ray_d"]).max() <= DTOL and common.bit_equal(d, g["ray_d"]), f"{name}: ray.d"
+    assert common.bit_equal(o, g["ray_o"]), f"{name}: ray.o max abs err {np.abs(o - g['ray_o']).max():.3e}"
+    if e.spectral:
+        assert common.bit_equal(wav, g["ray_wav"]), f"{name}: ray.wavelengths"
+    else:
+        assert wav is None
+    assert_close(w, g["ray_weight"], f"{name} sample_ray weight", exact=arith == "exact")
+    # the ray starts on the bounding sphere's far side disc: |o - c - (-d) r| <= r, and points into the scene
+    c = g["state_bsphere"][:3, None]; r = g["state_bsphere"][3]
+    assert (np.linalg.norm(o - c + d * r, axis=0) <= r * (1 + 1e-5)).all()
+
+
+def test_sample_ray_and_wavelengths_device_path_equals_host_path(ssk):
+    import torch
+    for name in ("cfg2_spec", "cfg3_rgb_sunsky"):
+        g = emitters.golden(name)
+        e = emitters.make(ssk, name, g=g)
+        e.set_scene(*common.SCENE_BBOX)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+        o, d, wav, w = e.sample_ray(g["wl_sample"], g["s2"], g["u"])
+        to, td, twav, tw = e.sample_ray(t(g["wl_sample"]), t(g["s2"]), t(g["u"]))
+        assert common.bit_equal(o, to.cpu().numpy()) and common.bit_equal(d, td.cpu().numpy())
+        assert common.bit_equal(w, tw.cpu().numpy())
+        hw, hq = e.sample_wavelengths(-g["wo"], g["wl_sample"])
+        dw, dq = e.sample_wavelengths(t(-g["wo"]), t(g["wl_sample"]))
+        assert common.bit_equal(hq, dq.cpu().numpy())
+        if e.spectral:
+            assert common.bit_equal(wav, twav.cpu().numpy()) and common.bit_equal(hw, dw.cpu().numpy())
+
+
+def test_sample_wavelengths_density_integrates_to_one(ssk):
+    """Size-independent property: E[1 / pdf] over uniform samples = 360 nm, i.e. mean(weight / eval) = 360 where
+    eval > 0; and the histogram of the sampled wavelengths follows the emitter's node density."""
+    e = emitters.make(ssk, "cfg2_spec", g=emitters.golden("cfg2_spec"))
+    rng = np.random.default_rng(5)
+    n = 1 << 18
+    wo = common.hemisphere_dirs(n, rng)
+    s = rng.random(n, dtype=np.float32)
+    wav, w = e.sample_wavelengths(-wo, s)
+    ev = e.eval(-wo, wav)
+    ok = ev > 0
+    inv_pdf = (w[ok].astype(np.float64) / ev[ok])
+    assert abs(inv_pdf.mean() - 360.0) / 360.0 < 5e-3
+    st = e.state()
+    pdf_nodes = np.array(st.spectral_pdf[:10], dtype=np.float64)
+    hist, _ = np.histogram(wav[0], bins=9, range=(360, 720))
+    want = 0.5 * (pdf_nodes[:-1] + pdf_nodes[1:]); want = want / want.sum() * n
+    assert np.abs(hist - want).max() < 6 * np.sqrt(want.max())
+
+
 # ---- environment maps and sweeps (BASELINE configs[3], configs[4]) ----------------------------------------
 
 @pytest.mark.parametrize("spectral", [False, True])
