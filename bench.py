@@ -407,4 +407,12 @@ def main():
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    # stdout carries exactly one JSON line: native libraries that write to fd 1 (NCCL prints its version banner
+    # there) are diverted to stderr for the whole run, and the line goes out through the saved descriptor.
+    sys.stdout.flush()
+    _saved = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(_saved, "w")
+    rc = main()
+    sys.stdout.flush()
+    sys.exit(rc)
