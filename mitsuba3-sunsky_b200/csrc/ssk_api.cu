@@ -75,6 +75,62 @@ int upload_block(ssk_ctx *ctx) {
     return SSK_OK;
 }
 
+// ---- device execution of the setup quadrature ---------------------------------------------------------------
+struct SetupScratch {       // one per device, shared by every context on it (setup calls serialise on `mu`)
+    float *d_gl = nullptr, *d_buf = nullptr, *d_partial = nullptr, *h_partial = nullptr;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+};
+constexpr int kMaxDevices = 64;
+SetupScratch g_setup[kMaxDevices];
+constexpr int kMaxChains = 2 * kMaxChannels * kQuadChunks;
+
+int ensure_setup_scratch(SetupScratch &sc) {
+    if (sc.d_gl) return SSK_OK;
+    SSK_CUDA(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
+    SSK_CUDA(cudaMalloc(&sc.d_gl, 2 * kQuadN * sizeof(float)));
+    SSK_CUDA(cudaMalloc(&sc.d_buf, (size_t) kMaxChains * kQuadChunk * sizeof(float)));
+    SSK_CUDA(cudaMalloc(&sc.d_partial, kMaxChains * sizeof(float)));
+    SSK_CUDA(cudaMallocHost(&sc.h_partial, kMaxChains * sizeof(float)));
+    SSK_CUDA(cudaMemcpy(sc.d_gl, gauss_legendre_200().data(), 2 * kQuadN * sizeof(float), cudaMemcpyHostToDevice));
+    return SSK_OK;
+}
+
+/// QuadratureFn of a context with a device: preliminary block up, 80 000 nodes evaluated, chain sums, 66 floats back
+int quadrature_device(ssk_ctx *ctx, const HostEmitter &E, float sky_rad[11], float sun_rad[11]) {
+    if (ctx->device >= kMaxDevices) return fail(SSK_ERR_UNSUPPORTED, "device ordinal too large");
+    SetupScratch &sc = g_setup[ctx->device];
+    std::lock_guard<std::mutex> lock(sc.mu);
+    SSK_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ensure_setup_scratch(sc)) return rc;
+    const int C = E.n_channels, nchains = 2 * C * kQuadChunks;
+    SSK_CUDA(cudaMemcpyAsync(ctx->d_block, &E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, sc.stream));
+    setup_quadrature_kernel<<<(2 * kQuadNodes + kThreads - 1) / kThreads, kThreads, 0, sc.stream>>>(
+        E.block, ctx->d_block, sc.d_gl, sc.d_buf, C);
+    setup_sum_kernel<<<1, 96, 0, sc.stream>>>(sc.d_buf, sc.d_partial, nchains);
+    g_launches += 2;
+    SSK_CUDA(cudaGetLastError());
+    SSK_CUDA(cudaMemcpyAsync(sc.h_partial, sc.d_partial, nchains * sizeof(float), cudaMemcpyDeviceToHost, sc.stream));
+    SSK_CUDA(cudaStreamSynchronize(sc.stream));
+    for (int which = 0; which < 2; ++which) {
+        const float J = which == 0 ? quad_sky_jacobian() : quad_sun_jacobian(E.block);
+        for (int c = 0; c < C; ++c) {
+            float total = 0.f;                       // llvm_block_sum: partials added in chunk order
+            for (int k = 0; k < kQuadChunks; ++k) total = total + sc.h_partial[(which * C + c) * kQuadChunks + k];
+            (which == 0 ? sky_rad : sun_rad)[c] = total * J;
+        }
+    }
+    return SSK_OK;
+}
+
+/// build_emitter with the quadrature on the context's device (host execution for device-less contexts)
+void build_on(ssk_ctx *ctx, const ssk_params &p, bool from_constructor) {
+    if (ctx->device < 0 || getenv("SSK_HOST_SETUP")) { build_emitter(ctx->E, p, from_constructor); return; }
+    build_emitter(ctx->E, p, from_constructor, [ctx](const HostEmitter &E, float *sky, float *sun) {
+        if (quadrature_device(ctx, E, sky, sun)) throw std::runtime_error("setup quadrature: " + g_err);
+    });
+}
+
 int need_device(const ssk_ctx *ctx) {
     if (!ctx) return fail(SSK_ERR_INVALID, "null context");
     if (ctx->device < 0 || !ctx->d_block)
@@ -460,19 +516,21 @@ int ssk_create(const ssk_params *p, const char *dataset_dir, int device, int mod
         ctx->device = device;
         ctx->E.spectral = mode == SSK_MODE_SPECTRAL;
         ctx->E.n_channels = ctx->E.spectral ? 11 : 3;
-        ctx->E.data = load_datasets(dataset_dir, ctx->E.spectral);
-        build_emitter(ctx->E, *p, true);
+        ctx->E.data = datasets_for(dataset_dir, ctx->E.spectral);
         if (device >= 0) {
             int count = 0;
             cudaError_t e = cudaGetDeviceCount(&count);
-            if (e != cudaSuccess || device >= count)
+            if (e != cudaSuccess || device >= count) {
+                validate_params(*p, ctx->E.spectral);          // property errors win over the missing device
                 return fail(SSK_ERR_CUDA, std::string("CUDA device ") + std::to_string(device) + " is not available: " +
                                               (e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range"));
+            }
             SSK_CUDA(cudaSetDevice(device));
             SSK_CUDA(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
-            return upload_block(ctx);
+            SSK_CUDA(cudaMalloc(&ctx->d_block, sizeof(EmitterBlock)));
         }
-        return SSK_OK;
+        build_on(ctx, *p, true);
+        return upload_block(ctx);
     });
     if (rc) { ssk_destroy(ctx); return rc; }
     *out = ctx;
@@ -483,8 +541,8 @@ int ssk_update(ssk_ctx *ctx, const ssk_params *p) {
     if (!ctx || !p) return fail(SSK_ERR_INVALID, "null argument");
     return guarded([&]() -> int {
         HostEmitter backup = ctx->E;
-        try { build_emitter(ctx->E, *p, false); }
-        catch (...) { ctx->E = backup; throw; }
+        try { build_on(ctx, *p, false); }
+        catch (...) { ctx->E = backup; upload_block(ctx); throw; }
         return upload_block(ctx);
     });
 }
@@ -539,7 +597,7 @@ int ssk_get_state(const ssk_ctx *ctx, ssk_state *s) {
     memcpy(s->sky_radiance, E.sky_radiance, sizeof(float) * E.n_channels);
     s->n_sun_radiance = (int32_t) E.sun_radiance.size();
     memcpy(s->sun_radiance, E.sun_radiance.data(), sizeof(float) * E.sun_radiance.size());
-    if (E.spectral) memcpy(s->sun_ld, E.data.sun_ld.data(), sizeof(float) * 66);
+    if (E.spectral) memcpy(s->sun_ld, E.data->sun_ld.data(), sizeof(float) * 66);
     memcpy(s->gaussians, E.gaussians, sizeof(E.gaussians));
     memcpy(s->pmf, E.pmf, sizeof(E.pmf)); memcpy(s->cdf, E.cdf, sizeof(E.cdf));
     s->cdf_sum = E.cdf_sum; s->cdf_normalization = E.cdf_norm; s->sky_sampling_w = E.sky_w;

@@ -1,6 +1,8 @@
 // Host setup of a sunsky emitter: see ssk_host.cuh. Compiled by nvcc with -fmad=false and the host
 // compiler's contraction off, so the fp32 op order below is the one that executes.
 #include "ssk_host.cuh"
+#include <map>
+#include <mutex>
 #include <cstring>
 
 namespace ssk {
@@ -46,7 +48,7 @@ static bool invert3(const float *m, float *inv) {
 
 /// The constructor (from_constructor = true, sunsky.cpp:162-218) or parameters_changed()
 /// (false, sunsky.cpp:242-285) applied to `p`.
-void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
+void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor, const QuadratureFn &quad) {
     validate_params(p, E.spectral);
     if (!from_constructor && (p.use_record != 0) != E.active_record)
         throw std::invalid_argument("an emitter keeps the sun parametrisation (direction or date/location) it was created with");
@@ -113,8 +115,8 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     B.bs_radius = E.bs_radius;
 
     // --- sky coefficients and mean radiance (sunsky.cpp:185-186 / 270-271)
-    radiance_params(E.data.sky_params, albedo, C, p.turbidity, eta, E.sky_params);
-    radiance_params(E.data.sky_rad, albedo, C, p.turbidity, eta, E.sky_radiance);
+    radiance_params(E.data->sky_params, albedo, C, p.turbidity, eta, E.sky_params);
+    radiance_params(E.data->sky_rad, albedo, C, p.turbidity, eta, E.sky_radiance);
     for (int c = 0; c < C; ++c) {
         for (int k = 0; k < kSkyParams; ++k) B.sky_params[k][c] = E.sky_params[c * 9 + k];
         B.sky_rad[c] = E.sky_radiance[c];
@@ -130,17 +132,17 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     }
     for (int c = C; c < kChanPad; ++c) B.sky_fast[8][c] = 1.f;      // pad channels: keep the -3/2 power finite
     // --- sun radiance table and limb darkening (:191-195 / 274)
-    E.sun_radiance.resize(E.data.sun_rad.size() / 10);
-    sun_params(E.data.sun_rad, p.turbidity, E.sun_radiance.data());
+    E.sun_radiance.resize(E.data->sun_rad.size() / 10);
+    sun_params(E.data->sun_rad, p.turbidity, E.sun_radiance.data());
     memset(B.sun_rad, 0, sizeof(B.sun_rad));
     memcpy(B.sun_rad, E.sun_radiance.data(), E.sun_radiance.size() * sizeof(float));
     if (E.spectral)
         for (int c = 0; c < 11; ++c)
-            for (int j = 0; j < kLd; ++j) B.sun_ld[j][c] = E.data.sun_ld[c * kLd + j];
+            for (int j = 0; j < kLd; ++j) B.sun_ld[j][c] = E.data->sun_ld[c * kLd + j];
 
     // --- TGMM mixture, CDF (JIT DiscreteDistribution: fp32 inclusive prefix sum, 1/sum), and the
     //     per-component constants the JIT folds at trace time (sunsky.cpp:201-204, 668-675, 742-755)
-    tgmm_distribution(E.data.tgmm, p.turbidity, eta, E.gaussians);
+    tgmm_distribution(E.data->tgmm, p.turbidity, eta, E.gaussians);
     float acc = 0.f;
     bool any_pos = false;
     for (int i = 0; i < kGauss; ++i) {
@@ -182,7 +184,7 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
         B.p_wv[k] = (float) ((double) E.pmf[i] * 0.15915494309189533577 / (double) volume);
     }
     // --- sky / sun sampling weight and wavelength distribution (:207-209 / 282-284)
-    estimate_sky_sun_ratio(E);
+    estimate_sky_sun_ratio(E, quad);
     B.sky_w = E.sky_w; B.r_sky_w = 1.f / E.sky_w;
     B.one_minus_sky_w = 1.f - E.sky_w; B.r_one_minus_sky_w = 1.f / B.one_minus_sky_w;
     for (int i = 0; i < 10; ++i) { B.wl_pdf[i] = E.spectral_pdf[i]; B.wl_cdf[i] = E.spectral_cdf[i]; }
@@ -198,74 +200,57 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor) {
 /// pdf of the origin offset in sample_ray (sunsky.cpp:381): InvPi * rcp(square(radius)), fp32
 void set_ray_pdf_scale(HotBlock &B) { B.ray_pdf_scale = SSK_INV_PI * (1.f / (B.bs_radius * B.bs_radius)); }
 
-/// estimate_sky_sun_ratio, array branch (sunsky.cpp:772-886): 200x200 Gauss-Legendre quadrature of the
-/// sky over the hemisphere and of the sun over its cone, luminance ratio, and (spectral) the
-/// per-bin mean radiance that drives wavelength sampling.
-void estimate_sky_sun_ratio(HostEmitter &E) {
-    const EmitterBlock &B = E.block;
-    const int C = E.n_channels;
-    static std::vector<float> gx, gw;
-    if (gx.empty()) gauss_legendre(200, gx, gw);
-    const int N = 200;
-    std::vector<float> buf((size_t) C * N * N);
-    float sky_rad[11], sun_rad[11];
-    Vec3 n = { B.sun_n[0], B.sun_n[1], B.sun_n[2] };
+std::shared_ptr<const Datasets> datasets_for(const std::string &dir, bool spectral) {
+    static std::mutex mu;
+    static std::map<std::pair<std::string, bool>, std::shared_ptr<const Datasets>> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    auto key = std::make_pair(dir, spectral);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    auto d = std::make_shared<const Datasets>(load_datasets(dir, spectral));
+    cache[key] = d;
+    return d;
+}
 
-    {   // sky over the hemisphere: [-1,1]^2 -> [0,2pi] x [0,1]
-        const float J = 0.5f * SSK_PI;
-        for (int iy = 0; iy < N; ++iy) {
-            float cos_theta = 0.5f * (gx[iy] + 1.f);
-            float sin_theta = safe_sqrt(1.f - cos_theta * cos_theta);
+const std::vector<float> &gauss_legendre_200() {
+    static const std::vector<float> g = [] {
+        std::vector<float> x, w, r;
+        gauss_legendre(kQuadN, x, w);
+        r = x; r.insert(r.end(), w.begin(), w.end());
+        return r;
+    }();
+    return g;
+}
+
+/// Host execution of the two 200 x 200 quadratures (contexts without a device; the device path is
+/// setup_quadrature_kernel + setup_sum_kernel in ssk_kernels.cuh, same per-node functions, same sum order)
+void quadrature_host(const HostEmitter &E, float sky_rad[11], float sun_rad[11]) {
+    const EmitterBlock &B = E.block;
+    const int C = E.n_channels, N = kQuadN;
+    const std::vector<float> &g = gauss_legendre_200();
+    const float *gx = g.data(), *gw = g.data() + N;
+    std::vector<float> buf((size_t) C * N * N);
+    float v[kMaxChannels];
+    for (int which = 0; which < 2; ++which) {
+        for (int iy = 0; iy < N; ++iy)
             for (int ix = 0; ix < N; ++ix) {
-                float phi = SSK_PI * (gx[ix] + 1.f), sp, cp;
-                dsincos(phi, sp, cp);
-                Vec3 wo = { sin_theta * cp, sin_theta * sp, cos_theta };
-                RayTerms r = ray_terms<kExact>(cos_theta, unit_angle(n, wo));
-                for (int c = 0; c < C; ++c)
-                    buf[(size_t) c * N * N + iy * N + ix] = render_sky(B, c, r) * gw[ix] * gw[iy];
+                if (which == 0) quad_sky_node(B, C, gx[ix], gx[iy], gw[ix], gw[iy], v);
+                else quad_sun_node(B, B.sun_rad, C, gx[ix], gx[iy], gw[ix], gw[iy], v);
+                for (int c = 0; c < C; ++c) buf[(size_t) c * N * N + iy * N + ix] = v[c];
             }
-        }
-        for (int c = 0; c < C; ++c) sky_rad[c] = llvm_block_sum(&buf[(size_t) c * N * N], N * N) * J;
+        const float J = which == 0 ? quad_sky_jacobian() : quad_sun_jacobian(B);
+        for (int c = 0; c < C; ++c)
+            (which == 0 ? sky_rad : sun_rad)[c] = llvm_block_sum(&buf[(size_t) c * N * N], N * N) * J;
     }
-    {   // sun over its cone: [-1,1]^2 -> [0,2pi] x [cos(half aperture), 1]
-        const float cutoff = B.cos_cutoff;
-        const float J = 0.5f * SSK_PI * (1.f - cutoff);
-        for (int iy = 0; iy < N; ++iy) {
-            float cos_gamma = 0.5f * ((1.f - cutoff) * gx[iy] + (1.f + cutoff));
-            float sin_gamma = safe_sqrt(1.f - cos_gamma * cos_gamma);
-            for (int ix = 0; ix < N; ++ix) {
-                float phi = SSK_PI * (gx[ix] + 1.f), sp, cp;
-                dsincos(phi, sp, cp);
-                Vec3 v = { sin_gamma * cp, sin_gamma * sp, cos_gamma };
-                float gamma = unit_angle_z(v);
-                Vec3 wo = { fmaf(B.sun_n[0], v.z, fmaf(B.sun_t[0], v.y, B.sun_s[0] * v.x)),
-                            fmaf(B.sun_n[1], v.z, fmaf(B.sun_t[1], v.y, B.sun_s[1] * v.x)),
-                            fmaf(B.sun_n[2], v.z, fmaf(B.sun_t[2], v.y, B.sun_s[2] * v.x)) };
-                float cos_theta = wo.z;
-                bool active = cos_theta >= 0.f;
-                float xk[4], cj[6];
-                SunSeg s = { 0, 0.f };
-                if (active) {
-                    s = sun_segment(cos_theta);
-                    powers4(s.x, xk);
-                    powers6(cos_psi(B, gamma), cj);
-                }
-                for (int c = 0; c < C; ++c) {
-                    float v0 = 0.f;
-                    if (active) {
-                        if (E.spectral) {
-                            v0 = render_sun_spec(B.sun_rad, c, s, xk) * gw[ix] * gw[iy];
-                            v0 *= sun_ld(B, c, c, 0.f, cj);
-                        } else {
-                            v0 = render_sun_rgb(B.sun_rad, c, s, xk, cj) * gw[ix] * gw[iy];
-                        }
-                    }
-                    buf[(size_t) c * N * N + iy * N + ix] = v0;
-                }
-            }
-        }
-        for (int c = 0; c < C; ++c) sun_rad[c] = llvm_block_sum(&buf[(size_t) c * N * N], N * N) * J;
-    }
+}
+
+/// estimate_sky_sun_ratio, array branch (sunsky.cpp:772-886): 200x200 Gauss-Legendre quadrature of the
+/// sky over the hemisphere and of the sun over its cone (done by `quad`), luminance ratio, and (spectral)
+/// the per-bin mean radiance that drives wavelength sampling.
+void estimate_sky_sun_ratio(HostEmitter &E, const QuadratureFn &quad) {
+    const EmitterBlock &B = E.block;
+    float sky_rad[11], sun_rad[11];
+    if (quad) quad(E, sky_rad, sun_rad); else quadrature_host(E, sky_rad, sun_rad);
 
     float sky_lum = B.sky_scale, sun_lum = B.sun_scale;
     if (!E.spectral) {

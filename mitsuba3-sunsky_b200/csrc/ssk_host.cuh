@@ -7,6 +7,8 @@
 #include "ssk_model.cuh"
 #include "../../include/sunsky_b200.h"
 #include <string>
+#include <functional>
+#include <memory>
 #include <vector>
 #include <stdexcept>
 #include <cstdio>
@@ -261,7 +263,7 @@ struct HostEmitter {
     ssk_params params;
     bool spectral = false;
     int n_channels = 3;
-    Datasets data;
+    std::shared_ptr<const Datasets> data;      // shared by every emitter created from the same directory
     EmitterBlock block;
     // reference-layout copies for ssk_get_state
     float sky_params[99], sky_radiance[11], gaussians[100], pmf[20], cdf[20];
@@ -279,8 +281,14 @@ struct HostEmitter {
 };
 
 void validate_params(const ssk_params &p, bool spectral);
-void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor);
-void estimate_sky_sun_ratio(HostEmitter &E);
+/// Computes the hemisphere integral of the sky and the cone integral of the sun per channel (x Jacobian) for an
+/// emitter whose block is complete except for the sampling weight; empty = quadrature_host
+using QuadratureFn = std::function<void(const HostEmitter &E, float sky_rad[11], float sun_rad[11])>;
+void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor, const QuadratureFn &quad = {});
+void quadrature_host(const HostEmitter &E, float sky_rad[11], float sun_rad[11]);
+void estimate_sky_sun_ratio(HostEmitter &E, const QuadratureFn &quad);
+std::shared_ptr<const Datasets> datasets_for(const std::string &dir, bool spectral);   // process-wide cache
+const std::vector<float> &gauss_legendre_200();     // 200 nodes followed by 200 weights
 void set_ray_pdf_scale(HotBlock &B);
 
 } // namespace ssk

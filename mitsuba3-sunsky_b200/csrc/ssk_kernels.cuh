@@ -327,6 +327,42 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
     }
 }
 
+// ---- emitter setup on the device: the two 200 x 200 quadratures of estimate_sky_sun_ratio ------------------
+// The reference integrates on the host / in a traced kernel and reduces with the LLVM backend's block sum:
+// sequential fp32 adds inside 16384-wide chunks, then over the chunk partials (ssk_host.cuh llvm_block_sum).
+// Here: one thread per node evaluates all channels (80 000 independent threads), values land chain-interleaved
+// so that the serial sums (one thread per chain = integrand x channel x chunk, at most 66) read coalesced.
+constexpr int kQuadNodes = kQuadN * kQuadN;
+constexpr int kQuadChunk = 16384;
+constexpr int kQuadChunks = (kQuadNodes + kQuadChunk - 1) / kQuadChunk;
+static_assert(kQuadNodes > 2 * kQuadChunk, "below 2 x 16384 elements the LLVM block sum is a single chain");
+
+__global__ void __launch_bounds__(kThreads)
+setup_quadrature_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, const float *__restrict__ gl,
+                        float *__restrict__ buf, int C) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= 2 * kQuadNodes) return;
+    const int which = idx / kQuadNodes, j = idx - which * kQuadNodes, iy = j / kQuadN, ix = j - iy * kQuadN;
+    const float gx_x = __ldg(gl + ix), gx_y = __ldg(gl + iy), gw_x = __ldg(gl + kQuadN + ix), gw_y = __ldg(gl + kQuadN + iy);
+    float v[kMaxChannels];
+    if (which == 0) quad_sky_node(U, C, gx_x, gx_y, gw_x, gw_y, v);
+    else quad_sun_node(U, blk->sun_rad, C, gx_x, gx_y, gw_x, gw_y, v);
+    const int nchains = 2 * C * kQuadChunks, chunk = j / kQuadChunk, pos = j - chunk * kQuadChunk;
+    for (int c = 0; c < C; ++c) buf[(size_t) pos * nchains + (which * C + c) * kQuadChunks + chunk] = v[c];
+}
+
+__global__ void __launch_bounds__(96)
+setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int nchains) {
+    const int chain = threadIdx.x;
+    if (chain >= nchains) return;
+    const int chunk = chain % kQuadChunks;
+    const int len = min(kQuadChunk, kQuadNodes - chunk * kQuadChunk);
+    float acc = 0.f;
+#pragma unroll 16
+    for (int j = 0; j < len; ++j) acc = acc + buf[(size_t) j * nchains + chain];
+    partial[chain] = acc;
+}
+
 // ---- sample_wavelengths / sample_ray -------------------------------------------------------------------
 /// sample_wavelengths, spectral (sunsky.cpp:463-473): one ray per thread; 4 planes in (wi, sample), 8 planes out
 template <int A>

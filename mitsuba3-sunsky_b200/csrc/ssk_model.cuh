@@ -826,6 +826,57 @@ template <int A> SSK_HD DirSample sample_dir(const HotBlock &U, const HotBlock &
     return r;
 }
 
+// ---- setup quadrature (estimate_sky_sun_ratio, sunsky.cpp:772-886): one node of the 200 x 200 grids --------
+constexpr int kQuadN = 200;
+/// Sky over the hemisphere, [-1,1]^2 -> [0,2pi] x [0,1] (sunsky.cpp:789-815): per-channel integrand x weights
+SSK_HD void quad_sky_node(const HotBlock &B, int C, float gx_x, float gx_y, float gw_x, float gw_y, float *out) {
+    float cos_theta = 0.5f * (gx_y + 1.f);
+    float sin_theta = safe_sqrt(1.f - cos_theta * cos_theta);
+    float phi = SSK_PI * (gx_x + 1.f), sp, cp;
+    dsincos(phi, sp, cp);
+    Vec3 n = { B.sun_n[0], B.sun_n[1], B.sun_n[2] };
+    Vec3 wo = { sin_theta * cp, sin_theta * sp, cos_theta };
+    RayTerms r = ray_terms<kExact>(cos_theta, unit_angle(n, wo));
+    for (int c = 0; c < C; ++c) out[c] = render_sky(B, c, r) * gw_x * gw_y;
+}
+SSK_HD float quad_sky_jacobian() { return 0.5f * SSK_PI; }
+/// Sun over its cone, [-1,1]^2 -> [0,2pi] x [cos(half aperture), 1] (sunsky.cpp:818-849)
+SSK_HD void quad_sun_node(const HotBlock &B, const float *sun_rad, int C, float gx_x, float gx_y, float gw_x, float gw_y,
+                          float *out) {
+    const float cutoff = B.cos_cutoff;
+    float cos_gamma = 0.5f * ((1.f - cutoff) * gx_y + (1.f + cutoff));
+    float sin_gamma = safe_sqrt(1.f - cos_gamma * cos_gamma);
+    float phi = SSK_PI * (gx_x + 1.f), sp, cp;
+    dsincos(phi, sp, cp);
+    Vec3 v = { sin_gamma * cp, sin_gamma * sp, cos_gamma };
+    float gamma = unit_angle_z(v);
+    Vec3 wo = { fmaf(B.sun_n[0], v.z, fmaf(B.sun_t[0], v.y, B.sun_s[0] * v.x)),
+                fmaf(B.sun_n[1], v.z, fmaf(B.sun_t[1], v.y, B.sun_s[1] * v.x)),
+                fmaf(B.sun_n[2], v.z, fmaf(B.sun_t[2], v.y, B.sun_s[2] * v.x)) };
+    float cos_theta = wo.z;
+    bool active = cos_theta >= 0.f;
+    float xk[4], cj[6];
+    SunSeg s = { 0, 0.f };
+    if (active) {
+        s = sun_segment(cos_theta);
+        powers4(s.x, xk);
+        powers6(cos_psi(B, gamma), cj);
+    }
+    for (int c = 0; c < C; ++c) {
+        float v0 = 0.f;
+        if (active) {
+            if (B.spectral) {
+                v0 = render_sun_spec(sun_rad, c, s, xk) * gw_x * gw_y;
+                v0 *= sun_ld(B, c, c, 0.f, cj);
+            } else {
+                v0 = render_sun_rgb(sun_rad, c, s, xk, cj) * gw_x * gw_y;
+            }
+        }
+        out[c] = v0;
+    }
+}
+SSK_HD float quad_sun_jacobian(const HotBlock &B) { return 0.5f * SSK_PI * (1.f - B.cos_cutoff); }
+
 // ---- sample_wavelengths / sample_ray (sunsky.cpp:463-480, 354-397) ---------------------------------------
 /// ContinuousDistribution::sample_pdf (distr_1d.h:468-502) over the emitter's 10-node wavelength density.
 /// U: constant-bank copy (uniform scalars), S: copy with lane-indexed tables (shared memory on the device).

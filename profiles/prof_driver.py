@@ -53,7 +53,17 @@ def main():
         "ray_rgb": lambda: sr.sample_ray(None, u, u),
         "ray_spec": lambda: ss.sample_ray(u1, u, u),
     }
-    for name in args.kernels.split(","):
+    if "setup" in args.kernels.split(","):
+        import time
+        for label, e in (("setup_rgb", er), ("setup_spec", es)):
+            e.update(turbidity=3.1); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for k in range(50):
+                e.update(turbidity=3.0 + 0.01 * k)
+            dt = (time.perf_counter() - t0) / 50
+            e.update(turbidity=3.0)
+            print(f"{label}: {dt * 1e3:.3f} ms per parameters_changed (host interpolation + device quadrature + block upload)")
+    for name in [k for k in args.kernels.split(",") if k != "setup"]:
         fn = runs[name]
         fn(); torch.cuda.synchronize()
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)

@@ -15,7 +15,7 @@ void *hostdbg_create(const ssk_params *p, const char *dir, int spectral) {
     HostEmitter *E = new HostEmitter();
     try {
         E->spectral = spectral; E->n_channels = spectral ? 11 : 3;
-        E->data = load_datasets(dir, spectral);
+        E->data = datasets_for(dir, spectral);
         build_emitter(*E, *p, true);
     } catch (const std::exception &e) { fprintf(stderr, "hostdbg: %s\n", e.what()); delete E; return nullptr; }
     return E;

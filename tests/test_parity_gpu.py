@@ -306,6 +306,25 @@ def test_fast_mode_matches_golden(ssk, name):
     assert_close(w, g["s_weight"], f"{name} fast weight", exact=False)
 
 
+@pytest.mark.parametrize("name", list(common.CONFIGS))
+def test_device_setup_quadrature_matches_reference_bitwise(ssk, name):
+    """Contexts with a device run estimate_sky_sun_ratio's two 200 x 200 quadratures on the GPU
+    (setup_quadrature_kernel + setup_sum_kernel): sampling weight and wavelength density stay bit-identical."""
+    g = emitters.golden(name)
+    e = emitters.make(ssk, name, g=g)
+    n0 = ssk.launch_count()
+    e.update(turbidity=float(common.CONFIGS[name][1]["turbidity"]))          # parameters_changed -> rebuild on the device
+    assert ssk.launch_count() - n0 == 2, "update() must run the two setup kernels"
+    s = e.state()
+    assert common.bit_equal(np.float32(s.sky_sampling_w), g["state_sky_sampling_w"]), (s.sky_sampling_w, g["state_sky_sampling_w"])
+    if e.spectral:
+        assert common.bit_equal(np.array(s.spectral_pdf[:10], np.float32), g["state_spectral_pdf"][:10])
+        assert common.bit_equal(np.array(s.spectral_cdf[:9], np.float32), g["state_spectral_cdf"][:9])
+        assert common.bit_equal(np.float32(s.spectral_normalization), g["state_spectral_normalization"])
+    h = emitters.make(ssk, name, device=-1, g=g).state()                     # host execution of the same quadrature
+    assert common.bit_equal(np.float32(h.sky_sampling_w), np.float32(s.sky_sampling_w))
+
+
 @pytest.mark.parametrize("arith", ["exact", "fast"])
 @pytest.mark.parametrize("name", list(common.CONFIGS))
 def test_sample_wavelengths_matches_golden(ssk, name, arith):
