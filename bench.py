@@ -361,6 +361,56 @@ def main():
             extra[mode] = ex
             for e in (es, er, e_sky, e_sun):
                 e.close()
+        # ---- configs[3] / configs[4]: env-map sweeps. Every frame needs its own emitter (parameters_changed:
+        #      host interpolation + device quadrature) before its map can be written; each rank renders its
+        #      share of the frames, optionally followed by the NCCL gather of finished frames on rank 0.
+        from sunsky_b200 import sharding, sweep as sweep_mod
+
+        def sweep_bench(config, width, height, chunk, gather):
+            spectral = config == "animation"
+            mode_ = "round_robin" if spectral else "blocked"
+            params = sharding.sweep_parameters(config)
+            mine = sharding.frames_for_rank(len(params), rank, world, mode_)
+            Cn = 4 if spectral else 3
+            buf = torch.empty((chunk, Cn, height, width), device=dev)
+            full = torch.empty((chunk * world, Cn, height, width), device=dev) if (gather and rank == 0) else None
+            t_setup = 0.0
+            l0 = ssk.launch_count()
+            barrier()
+            t0 = time.perf_counter()
+            for s0 in range(0, len(mine), chunk):
+                idx = mine[s0:s0 + chunk]
+                ts = time.perf_counter()
+                ems = sweep_mod.make_emitters([params[f] for f in idx], spectral, local, args.arith)
+                t_setup += time.perf_counter() - ts
+                ssk.envmaps(ems, width, height, (440.0, 520.0, 600.0, 680.0) if spectral else None, out=buf[:len(idx)])
+                if gather and world > 1:
+                    dist.gather(buf, list(full.split(chunk)) if rank == 0 else None, dst=0)
+                torch.cuda.synchronize()
+                for e_ in ems:
+                    e_.close()
+            barrier()
+            windows.append((t0, time.perf_counter()))
+            sec = max_over_ranks(windows[-1][1] - t0)
+            n_frames = len(params)
+            return {"frames": n_frames, "frames_per_gpu": len(mine), "resolution": [width, height], "seconds": sec,
+                    "frames_per_s": n_frames / sec, "Gpixels_s": n_frames * width * height / sec / 1e9,
+                    "setup_ms_per_frame": t_setup / max(len(mine), 1) * 1e3,
+                    "gpu_launches": ssk.launch_count() - l0, "gathered_to_rank0": bool(gather and world > 1),
+                    "out_GB_per_gpu": len(mine) * Cn * width * height * 4 / 1e9}
+
+        sw = {}
+        sweep_bench("time_of_day", 1024, 512, 8, False)                     # warm-up: contexts, scratch, NCCL
+        sw["time_of_day_256x4096x2048_rgb"] = sweep_bench("time_of_day", 4096, 2048, 8, False)
+        sw["animation_128x8192x4096_spectral"] = sweep_bench("animation", 8192, 4096, 2, False)
+        if world > 1:
+            sweep_bench("time_of_day", 1024, 512, 8, True)
+            sw["time_of_day_256x4096x2048_rgb_gather"] = sweep_bench("time_of_day", 4096, 2048, 8, True)
+            sw["animation_128x8192x4096_spectral_gather"] = sweep_bench("animation", 8192, 4096, 2, True)
+        sw["note"] = ("BASELINE configs[3] (64 sun elevations x 4 turbidities, RGB) and configs[4] (128-frame turbidity/albedo "
+                      "animation, spectral, wavelengths 440/520/600/680 nm); wall clock between barriers, max over ranks, "
+                      "includes creating every frame's emitter (host interpolation + device quadrature)")
+        extra["sweeps"] = sw
         extra["note"] = ("configs[1] inputs for eval/pdf (2^24 directions), configs[2] for sample_direction (2^26 samples, "
                          "t=6 a=0.5 eta=50.2deg; sky only = sampling_test.py). fp32_frac uses the algorithmic flops of SURVEY 8d.")
         del out3, pdf, u, d, spdf, wgt

@@ -3,6 +3,7 @@
 #include "ssk_host.cuh"
 #include "ssk_kernels.cuh"
 #include <atomic>
+#include <chrono>
 #include <cstdlib>
 #include <mutex>
 #include <string>
@@ -104,14 +105,22 @@ int quadrature_device(ssk_ctx *ctx, const HostEmitter &E, float sky_rad[11], flo
     SSK_CUDA(cudaSetDevice(ctx->device));
     if (int rc = ensure_setup_scratch(sc)) return rc;
     const int C = E.n_channels, nchains = 2 * C * kQuadChunks;
+    static const bool trace = getenv("SSK_SETUP_TRACE") != nullptr;      // stderr: microseconds per phase
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto t0 = now();
     SSK_CUDA(cudaMemcpyAsync(ctx->d_block, &E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, sc.stream));
     setup_quadrature_kernel<<<(2 * kQuadNodes + kThreads - 1) / kThreads, kThreads, 0, sc.stream>>>(
         E.block, ctx->d_block, sc.d_gl, sc.d_buf, C);
-    setup_sum_kernel<<<1, 96, 0, sc.stream>>>(sc.d_buf, sc.d_partial, nchains);
+    setup_sum_kernel<<<nchains, 32, 0, sc.stream>>>(sc.d_buf, sc.d_partial);
     g_launches += 2;
     SSK_CUDA(cudaGetLastError());
     SSK_CUDA(cudaMemcpyAsync(sc.h_partial, sc.d_partial, nchains * sizeof(float), cudaMemcpyDeviceToHost, sc.stream));
+    auto t1 = now();
     SSK_CUDA(cudaStreamSynchronize(sc.stream));
+    if (trace) {
+        auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+        fprintf(stderr, "ssk setup: enqueue %.1f us, device wait %.1f us\n", us(t0, t1), us(t1, now()));
+    }
     for (int which = 0; which < 2; ++which) {
         const float J = which == 0 ? quad_sky_jacobian() : quad_sun_jacobian(E.block);
         for (int c = 0; c < C; ++c) {
@@ -126,6 +135,9 @@ int quadrature_device(ssk_ctx *ctx, const HostEmitter &E, float sky_rad[11], flo
 /// build_emitter with the quadrature on the context's device (host execution for device-less contexts)
 void build_on(ssk_ctx *ctx, const ssk_params &p, bool from_constructor) {
     if (ctx->device < 0 || getenv("SSK_HOST_SETUP")) { build_emitter(ctx->E, p, from_constructor); return; }
+    auto t0 = std::chrono::steady_clock::now();
+    struct Trace { decltype(t0) t; ~Trace() { if (getenv("SSK_SETUP_TRACE")) fprintf(stderr, "ssk setup: build_emitter total %.1f us\n",
+        std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t).count()); } } tr{ t0 };
     build_emitter(ctx->E, p, from_constructor, [ctx](const HostEmitter &E, float *sky, float *sun) {
         if (quadrature_device(ctx, E, sky, sun)) throw std::runtime_error("setup quadrature: " + g_err);
     });

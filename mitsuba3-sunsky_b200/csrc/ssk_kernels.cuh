@@ -330,8 +330,8 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
 // ---- emitter setup on the device: the two 200 x 200 quadratures of estimate_sky_sun_ratio ------------------
 // The reference integrates on the host / in a traced kernel and reduces with the LLVM backend's block sum:
 // sequential fp32 adds inside 16384-wide chunks, then over the chunk partials (ssk_host.cuh llvm_block_sum).
-// Here: one thread per node evaluates all channels (80 000 independent threads), values land chain-interleaved
-// so that the serial sums (one thread per chain = integrand x channel x chunk, at most 66) read coalesced.
+// Here: one thread per node evaluates all channels (80 000 independent threads) and stores them chain-major
+// (chain = integrand x channel x chunk, at most 66); one warp per chain then adds its values in index order.
 constexpr int kQuadNodes = kQuadN * kQuadN;
 constexpr int kQuadChunk = 16384;
 constexpr int kQuadChunks = (kQuadNodes + kQuadChunk - 1) / kQuadChunk;
@@ -347,20 +347,40 @@ setup_quadrature_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *
     float v[kMaxChannels];
     if (which == 0) quad_sky_node(U, C, gx_x, gx_y, gw_x, gw_y, v);
     else quad_sun_node(U, blk->sun_rad, C, gx_x, gx_y, gw_x, gw_y, v);
-    const int nchains = 2 * C * kQuadChunks, chunk = j / kQuadChunk, pos = j - chunk * kQuadChunk;
-    for (int c = 0; c < C; ++c) buf[(size_t) pos * nchains + (which * C + c) * kQuadChunks + chunk] = v[c];
+    const int chunk = j / kQuadChunk, pos = j - chunk * kQuadChunk;
+    for (int c = 0; c < C; ++c) buf[(size_t) ((which * C + c) * kQuadChunks + chunk) * kQuadChunk + pos] = v[c];
 }
 
-__global__ void __launch_bounds__(96)
-setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int nchains) {
-    const int chain = threadIdx.x;
-    if (chain >= nchains) return;
+/// One warp per chain. Lanes fetch 32 consecutive values with one coalesced load (several tiles in flight), the
+/// values are then broadcast lane by lane and added in index order: the only serial dependency left is the
+/// 16384-long chain of fp32 adds itself (every lane carries the same accumulator).
+__global__ void __launch_bounds__(32)
+setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial) {
+    const int chain = blockIdx.x, lane = threadIdx.x;
     const int chunk = chain % kQuadChunks;
     const int len = min(kQuadChunk, kQuadNodes - chunk * kQuadChunk);
+    const float *p = buf + (size_t) chain * kQuadChunk;
+    constexpr int kTiles = 8;
     float acc = 0.f;
-#pragma unroll 16
-    for (int j = 0; j < len; ++j) acc = acc + buf[(size_t) j * nchains + chain];
-    partial[chain] = acc;
+    for (int j0 = 0; j0 < len; j0 += 32 * kTiles) {
+        float v[kTiles];
+#pragma unroll
+        for (int u = 0; u < kTiles; ++u) {
+            const int j = j0 + u * 32 + lane;
+            v[u] = j < len ? __ldcg(p + j) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < kTiles; ++u) {
+            const int left = len - (j0 + u * 32);                  // warp-uniform
+            if (left >= 32) {
+#pragma unroll
+                for (int k = 0; k < 32; ++k) acc = acc + __shfl_sync(0xffffffffu, v[u], k);
+            } else {
+                for (int k = 0; k < left; ++k) acc = acc + __shfl_sync(0xffffffffu, v[u], k);
+            }
+        }
+    }
+    if (lane == 0) partial[chain] = acc;
 }
 
 // ---- sample_wavelengths / sample_ray -------------------------------------------------------------------
