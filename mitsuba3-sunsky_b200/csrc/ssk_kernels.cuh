@@ -28,6 +28,16 @@ constexpr int kThreads = 256;
 #ifndef SSK_RGBP_MINB
 #define SSK_RGBP_MINB 3
 #endif
+#ifndef SSK_SPECF_MINB
+#define SSK_SPECF_MINB 3
+#endif
+#ifndef SSK_PAIR_PREFETCH
+#define SSK_PAIR_PREFETCH 1
+#endif
+#ifndef SSK_EVAL_PREFETCH
+#define SSK_EVAL_PREFETCH 1      /* FAST spectral eval: measured 54.5 (pipelined loads, 3 CTAs/SM, 85 regs) vs 50.5 Gevals/s; */
+                                 /* with 4 CTAs/SM (64 regs) the prefetched values spill and the gain is lost; L1 prefetch: none */
+#endif
 #ifndef SSK_SPECX_MINB
 #define SSK_SPECX_MINB 1
 #endif
@@ -89,6 +99,8 @@ template <int R> __device__ __forceinline__ void setk(float v[4], int k, float x
     v[0] = k == 0 ? x : v[0]; v[1] = k == 1 ? x : v[1]; v[2] = k == 2 ? x : v[2]; v[3] = k == 3 ? x : v[3];
 }
 
+__device__ __forceinline__ void prefetch_l1(const float *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
+
 struct Planes3 { const float *x, *y, *z; };
 struct Planes4 { const float *a, *b, *c, *d; };
 struct OutPlanes3 { float *x, *y, *z; };
@@ -116,6 +128,19 @@ eval_rgb_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restri
     }
 }
 
+// ---- two rays per thread: 64-bit plane accesses (planes 8-byte aligned) ------------------------------------
+__device__ __forceinline__ float2 ld2(const float *p, size_t i, bool two, float pad) {
+    return two ? __ldcs(reinterpret_cast<const float2 *>(p + i)) : make_float2(__ldcs(p + i), pad);
+}
+__device__ __forceinline__ void st2(float *p, size_t i, bool two, float2 v) {
+    if (two) __stcs(reinterpret_cast<float2 *>(p + i), v); else __stcs(p + i, v.x);
+}
+/// Three direction planes of ray pair i (pads 0, 0, 1 for the missing second ray of an odd tail)
+__device__ __forceinline__ Vec3p ld_dir2(const Planes3 &in, size_t i, size_t n) {
+    const bool two = i + 1 < n;
+    return { ld2(in.x, i, two, 0.f), ld2(in.y, i, two, 0.f), ld2(in.z, i, two, 1.f) };
+}
+
 /// eval / eval_direction, RGB, two consecutive rays per thread as float2 pairs (64-bit plane accesses, planes
 /// 8-byte aligned): every FP32 instruction of the model works on both rays (FFMA2 / FMUL2 / FADD2).
 template <int A>
@@ -124,30 +149,24 @@ eval_rgb_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
                      size_t n, float dir_sign) {
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * 2;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+    size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    // software-pipelined: the next grid-stride iteration's directions are requested before this pair's arithmetic
+    Vec3p next = { f2(0.f, 0.f), f2(0.f, 0.f), f2(1.f, 1.f) };
+    if (i < n) next = ld_dir2(in, i, n);
+    for (; i < n; i += stride) {
         const bool two = i + 1 < n;
-        float2 x, y, z;
-        if (two) {
-            x = __ldcs(reinterpret_cast<const float2 *>(in.x + i)); y = __ldcs(reinterpret_cast<const float2 *>(in.y + i));
-            z = __ldcs(reinterpret_cast<const float2 *>(in.z + i));
-        } else {
-            x = f2(in.x[i], 0.f); y = f2(in.y[i], 0.f); z = f2(in.z[i], 1.f);
-        }
-        Vec3p wi = { mul2s(x, dir_sign), mul2s(y, dir_sign), mul2s(z, dir_sign) };
+        Vec3p wi = { mul2s(next.x, dir_sign), mul2s(next.y, dir_sign), mul2s(next.z, dir_sign) };
+        if (SSK_PAIR_PREFETCH && i + stride < n) next = ld_dir2(in, i + stride, n);
         float2 o[3];
         eval_rgb_p<A>(U, sun_rad, wi, true, two, o);
-        if (two) {
-            __stcs(reinterpret_cast<float2 *>(out.x + i), o[0]); __stcs(reinterpret_cast<float2 *>(out.y + i), o[1]);
-            __stcs(reinterpret_cast<float2 *>(out.z + i), o[2]);
-        } else {
-            out.x[i] = o[0].x; out.y[i] = o[1].x; out.z[i] = o[2].x;
-        }
+        st2(out.x, i, two, o[0]); st2(out.y, i, two, o[1]); st2(out.z, i, two, o[2]);
+        if (!SSK_PAIR_PREFETCH && i + stride < n) next = ld_dir2(in, i + stride, n);
     }
 }
 
 /// eval / eval_direction, spectral (4 wavelengths per ray)
 template <int A, int R>
-__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? 4 : SSK_SPECX_MINB)
+__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? SSK_SPECF_MINB : SSK_SPECX_MINB)
 eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
                  OutPlanes4 out, size_t n, float dir_sign) {
     __shared__ __align__(16) HotBlock S;
@@ -155,8 +174,36 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
     stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
+    if (R == 1 && A == kFast && SSK_EVAL_PREFETCH == 1) {
+        // one ray per thread, software-pipelined: the 7 input planes of the next grid-stride iteration are
+        // requested before this ray's arithmetic starts (ncu: long_scoreboard was the top stall without it)
+        size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+        float nx = 0.f, ny = 0.f, nz = 0.f, na = 0.f, nb = 0.f, nc = 0.f, nd = 0.f;
+        if (i < n) {
+            nx = __ldcs(in.x + i); ny = __ldcs(in.y + i); nz = __ldcs(in.z + i);
+            na = __ldcs(wav.a + i); nb = __ldcs(wav.b + i); nc = __ldcs(wav.c + i); nd = __ldcs(wav.d + i);
+        }
+        for (; i < n; i += stride) {
+            Vec3 wi = { dir_sign * nx, dir_sign * ny, dir_sign * nz };
+            float wl[4] = { na, nb, nc, nd }, o[4];
+            const size_t j = i + stride;
+            if (j < n) {
+                nx = __ldcs(in.x + j); ny = __ldcs(in.y + j); nz = __ldcs(in.z + j);
+                na = __ldcs(wav.a + j); nb = __ldcs(wav.b + j); nc = __ldcs(wav.c + j); nd = __ldcs(wav.d + j);
+            }
+            eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
+            __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]); __stcs(out.d + i, o[3]);
+        }
+        return;
+    }
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
         float x[4], y[4], z[4], w0[4], w1[4], w2[4], w3[4], o0[4], o1[4], o2[4], o3[4];
+        if (R == 1 && SSK_EVAL_PREFETCH == 2 && i + stride < n) {
+            // non-binding L1 prefetch of the next grid-stride iteration's 7 input lines: no registers, no scoreboard
+            const size_t j = i + stride;
+            prefetch_l1(in.x + j); prefetch_l1(in.y + j); prefetch_l1(in.z + j);
+            prefetch_l1(wav.a + j); prefetch_l1(wav.b + j); prefetch_l1(wav.c + j); prefetch_l1(wav.d + j);
+        }
         loadr<R>(in.x, i, n, x); loadr<R>(in.y, i, n, y); loadr<R>(in.z, i, n, z);
         loadr<R>(wav.a, i, n, w0); loadr<R>(wav.b, i, n, w1); loadr<R>(wav.c, i, n, w2); loadr<R>(wav.d, i, n, w3);
 #pragma unroll 1
@@ -255,23 +302,20 @@ sample_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
     }
 }
 
-// ---- two rays per thread (float2 pairs, 64-bit plane accesses; planes 8-byte aligned) -------------------
-__device__ __forceinline__ float2 ld2(const float *p, size_t i, bool two, float pad) {
-    return two ? __ldcs(reinterpret_cast<const float2 *>(p + i)) : make_float2(__ldcs(p + i), pad);
-}
-__device__ __forceinline__ void st2(float *p, size_t i, bool two, float2 v) {
-    if (two) __stcs(reinterpret_cast<float2 *>(p + i), v); else __stcs(p + i, v.x);
-}
-
 /// pdf_direction, two directions per thread
 template <int A>
 __global__ void __launch_bounds__(kThreads, 4)
 pdf_pair_kernel(const __grid_constant__ HotBlock U, Planes3 in, float *__restrict__ pdf, size_t n) {
     const size_t stride = (size_t) gridDim.x * blockDim.x * 2;
-    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i < n; i += stride) {
+    size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2;
+    Vec3p next = { f2(0.f, 0.f), f2(0.f, 0.f), f2(1.f, 1.f) };
+    if (i < n) next = ld_dir2(in, i, n);
+    for (; i < n; i += stride) {
         const bool two = i + 1 < n;
-        Vec3p d = { ld2(in.x, i, two, 0.f), ld2(in.y, i, two, 0.f), ld2(in.z, i, two, 1.f) };
+        const Vec3p d = next;
+        if (SSK_PAIR_PREFETCH && i + stride < n) next = ld_dir2(in, i + stride, n);       // see eval_rgb_pair_kernel
         st2(pdf, i, two, pdf_direction_p<A>(U, d, true, two));
+        if (!SSK_PAIR_PREFETCH && i + stride < n) next = ld_dir2(in, i + stride, n);
     }
 }
 
