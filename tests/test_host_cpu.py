@@ -208,3 +208,26 @@ def test_golden_reproducible_from_reference(ref):
         r.set_scene(*common.SCENE_BBOX)
         ro, rd, rwav, rw = r.sample_ray(g["wl_sample"], g["s2"], g["u"])
         assert common.bit_equal(ro, g["ray_o"]) and common.bit_equal(rd, g["ray_d"]) and common.bit_equal(rw, g["ray_weight"])
+
+
+def test_adapter_plugin_type_checks():
+    """adapter/sunsky_b200.cpp (the Mitsuba-side binding of INTEGRATION.md) instantiates for the reference's array
+    types against the reference's own headers: every C-ABI call it makes matches include/sunsky_b200.h."""
+    import os
+    import shutil
+    import subprocess
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = os.environ.get("SSK_REFERENCE", "/root/reference")
+    gen = os.path.join(repo, "oracle", "_ref", "gen")
+    if not os.path.isdir(os.path.join(ref, "include", "mitsuba")) or not os.path.isdir(os.path.join(gen, "include")):
+        pytest.skip("needs the reference tree and oracle/_ref/gen (container only)")
+    cxx = shutil.which("g++")
+    inc = [os.path.join(repo, "include"), os.path.join(repo, "oracle", "ref_shadow"), gen, os.path.join(gen, "include"), ref,
+           os.path.join(ref, "include"), os.path.join(ref, "ext/drjit/include"),
+           os.path.join(ref, "ext/drjit/ext/drjit-core/include"),
+           os.path.join(ref, "ext/drjit/ext/drjit-core/ext/nanothread/include"), os.path.join(ref, "ext/tinyformat"),
+           os.path.join(ref, "ext/fastfloat/include"), os.path.join(ref, "ext/nanobind/include")]
+    cmd = [cxx, "-std=c++17", "-fsyntax-only", "-w", "-mavx2", "-mfma"] + [f"-I{d}" for d in inc] + \
+          [os.path.join(repo, "tests", "adapter", "instantiate.cpp")]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
