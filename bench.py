@@ -378,6 +378,7 @@ def main():
             l0 = ssk.launch_count()
             barrier()
             t0 = time.perf_counter()
+            pending = None
             for s0 in range(0, len(mine), chunk):
                 idx = mine[s0:s0 + chunk]
                 ts = time.perf_counter()
@@ -386,9 +387,15 @@ def main():
                 ssk.envmaps(ems, width, height, (440.0, 520.0, 600.0, 680.0) if spectral else None, out=buf[:len(idx)])
                 if gather and world > 1:
                     dist.gather(buf, list(full.split(chunk)) if rank == 0 else None, dst=0)
-                torch.cuda.synchronize()
-                for e_ in ems:
-                    e_.close()
+                ev = torch.cuda.Event(); ev.record()
+                if pending is not None:                  # previous chunk: contexts outlive their launches
+                    pending[0].synchronize()
+                    for e_ in pending[1]:
+                        e_.close()
+                pending = (ev, ems)
+            torch.cuda.synchronize()
+            for e_ in (pending[1] if pending else []):
+                e_.close()
             barrier()
             windows.append((t0, time.perf_counter()))
             sec = max_over_ranks(windows[-1][1] - t0)

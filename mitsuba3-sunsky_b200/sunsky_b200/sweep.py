@@ -42,12 +42,22 @@ def render_sweep(config, width, height, rank=0, world_size=1, device=0, arith="e
     dev = torch.device("cuda", device)
     if out is None:
         out = torch.empty((len(mine), C, height, width), dtype=torch.float32, device=dev)
+    pending = None                                        # (event, emitters) of the chunk still rendering
     for s in range(0, len(mine), chunk):
         idx = mine[s:s + chunk]
+        # the next chunk's emitters are set up (host interpolation + device quadrature on the setup stream)
+        # while the previous chunk's maps are still being written
         ems = make_emitters([params[f] for f in idx], spectral, device, arith)
         envmaps(ems, width, height, wavelengths4 if spectral else None, out=out[s:s + len(idx)])
-        torch.cuda.current_stream(dev).synchronize()      # the contexts must outlive their launches
-        for e in ems:
+        ev = torch.cuda.Event(); ev.record(torch.cuda.current_stream(dev))
+        if pending is not None:                           # the contexts must outlive their launches
+            pending[0].synchronize()
+            for e in pending[1]:
+                e.close()
+        pending = (ev, ems)
+    if pending is not None:
+        pending[0].synchronize()
+        for e in pending[1]:
             e.close()
     if gather:
         full = sharding.gather_frames(out, n_frames, mode=mode, dst=0)

@@ -58,9 +58,10 @@ def main():
         for label, e in (("setup_rgb", er), ("setup_spec", es)):
             e.update(turbidity=3.1); torch.cuda.synchronize()
             t0 = time.perf_counter()
-            for k in range(50):
+            n_up = 50 if args.reps >= 10 else args.reps
+            for k in range(n_up):
                 e.update(turbidity=3.0 + 0.01 * k)
-            dt = (time.perf_counter() - t0) / 50
+            dt = (time.perf_counter() - t0) / n_up
             e.update(turbidity=3.0)
             print(f"{label}: {dt * 1e3:.3f} ms per parameters_changed (host interpolation + device quadrature + block upload)")
     for name in [k for k in args.kernels.split(",") if k != "setup"]:

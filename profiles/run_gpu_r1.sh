@@ -14,16 +14,16 @@ python bench.py --arith exact --no-extra --steps 100 > $O/bench_exact.json 2> $O
 # launch list of the bench command itself (its kernel share of the step is what must agree with the live timing)
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_bench.csv \
     python bench.py --steps 20 --warmup 3 --no-extra > $O/ncu_launches_bench.log 2>&1; echo "bench launch list rc=$?"
-K="eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,sample_spec,envmap"
+K="setup,eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,sample_spec,envmap,wavelengths,ray_rgb,ray_spec"
 for A in fast exact; do
 python profiles/prof_driver.py --kernels $K --reps 3 --arith $A > $O/prof_plain_$A.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_$A.csv \
     python profiles/prof_driver.py --kernels $K --reps 3 --arith $A > $O/ncu_launches_$A.log 2>&1
 echo "launch list $A rc=$?"
 done
-python profiles/prof_driver.py --kernels eval_spec,eval_rgb,pdf,sample_rgb --reps 1 --arith fast > $O/prof_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'eval_|pdf_|sample_' -c 8 -f -o $O/prof_fast \
-    python profiles/prof_driver.py --kernels eval_spec,eval_rgb,pdf,sample_rgb --reps 1 --arith fast > $O/ncu_full_fast.log 2>&1
+python profiles/prof_driver.py --kernels setup,eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,wavelengths,ray_spec --reps 1 --arith fast > $O/prof_plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'eval_|pdf_|sample_|setup_' -c 40 -f -o $O/prof_fast \
+    python profiles/prof_driver.py --kernels setup,eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,wavelengths,ray_spec --reps 1 --arith fast > $O/ncu_full_fast.log 2>&1
 echo "full fast rc=$?"
 python profiles/prof_driver.py --kernels eval_spec,eval_rgb,pdf,sample_rgb --reps 1 --arith exact > $O/prof_plain3.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'eval_|pdf_|sample_' -c 8 -f -o $O/prof_exact \
