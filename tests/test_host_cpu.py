@@ -231,3 +231,26 @@ def test_adapter_plugin_type_checks():
           [os.path.join(repo, "tests", "adapter", "instantiate.cpp")]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
+
+
+def test_dataset_generators_reproduce_shipped_files(tmp_path):
+    """tools/make_datasets.py (the reference's commented-out write_* generators, sunsky.h:609-895, and
+    mk_sampling_dataset.py) rebuilds all eight dataset files byte for byte from the Hosek-Wilkie headers and the
+    TGMM fit table."""
+    import filecmp
+    import os
+    import subprocess
+    import sys
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = os.environ.get("SSK_REFERENCE", "/root/reference")
+    hosek = os.path.join(ref, "include", "mitsuba", "render", "sunsky")
+    csv = os.path.join(ref, "sunsky-testing", "res", "datasets", "model_hosek.csv")
+    if not (os.path.exists(os.path.join(hosek, "ArHosekSkyModelData_Spectral.h")) and os.path.exists(csv)):
+        pytest.skip("needs the Hosek-Wilkie data headers and model_hosek.csv (container only)")
+    subprocess.run([sys.executable, os.path.join(repo, "tools", "make_datasets.py"), "--hosek-dir", hosek, "--tgmm-csv", csv,
+                    "--out", str(tmp_path)], check=True)
+    shipped = os.path.join(repo, "mitsuba3-sunsky_b200", "data", "resources", "sunsky", "datasets")
+    names = sorted(os.listdir(shipped))
+    assert len(names) == 8
+    for n in names:
+        assert filecmp.cmp(os.path.join(shipped, n), os.path.join(str(tmp_path), n), shallow=False), f"{n} differs"
