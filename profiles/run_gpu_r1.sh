@@ -21,12 +21,22 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
     python profiles/prof_driver.py --kernels $K --reps 3 --arith $A > $O/ncu_launches_$A.log 2>&1
 echo "launch list $A rc=$?"
 done
-python profiles/prof_driver.py --kernels setup,eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,wavelengths,ray_spec --reps 1 --arith fast > $O/prof_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'eval_|pdf_|sample_|setup_' -c 40 -f -o $O/prof_fast \
-    python profiles/prof_driver.py --kernels setup,eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,wavelengths,ray_spec --reps 1 --arith fast > $O/ncu_full_fast.log 2>&1
+# full captures: summarised on the box (gpurun_out/ is capped at 64 MiB, a 40-kernel .ncu-rep is larger)
+KF="eval_spec,eval_rgb,pdf,sample_sky"
+python profiles/prof_driver.py --kernels $KF --reps 1 --arith fast > $O/prof_plain2.log 2>&1 &&
+ncu --set full --clock-control none --import-source on -k regex:'eval_|pdf_|sample_' -c 8 -f -o $O/prof_fast \
+    python profiles/prof_driver.py --kernels $KF --reps 1 --arith fast > $O/ncu_full_fast.log 2>&1
 echo "full fast rc=$?"
-python profiles/prof_driver.py --kernels eval_spec,eval_rgb,pdf,sample_rgb --reps 1 --arith exact > $O/prof_plain3.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:'eval_|pdf_|sample_' -c 8 -f -o $O/prof_exact \
-    python profiles/prof_driver.py --kernels eval_spec,eval_rgb,pdf,sample_rgb --reps 1 --arith exact > $O/ncu_full_exact.log 2>&1
+python profiles/ncu_summary.py $O/prof_fast.ncu-rep > $O/ncu_full_fast.txt 2>&1
+ncu -i $O/prof_fast.ncu-rep --page source --csv --kernel-name regex:eval_spec > $O/src_eval_spec_fast.csv 2>/dev/null
+python profiles/src_hot.py $O/src_eval_spec_fast.csv 30 > $O/hot_eval_spec_fast.txt 2>&1
+KS="setup,sample_rgb,sample_spec,wavelengths,ray_rgb,ray_spec,envmap"
+ncu --set full --clock-control none -k regex:'sample_|setup_|envmap_' --launch-skip 10 -c 24 -f -o $O/prof_fast2 \
+    python profiles/prof_driver.py --kernels $KS --reps 1 --arith fast > $O/ncu_full_fast2.log 2>&1
+echo "full fast2 rc=$?"
+python profiles/ncu_summary.py $O/prof_fast2.ncu-rep > $O/ncu_full_fast2.txt 2>&1; rm -f $O/prof_fast2.ncu-rep
+ncu --set full --clock-control none -k regex:'eval_|pdf_|sample_' -c 12 -f -o $O/prof_exact \
+    python profiles/prof_driver.py --kernels eval_spec,eval_rgb,pdf,sample_rgb,sample_sky,ray_spec --reps 1 --arith exact > $O/ncu_full_exact.log 2>&1
 echo "full exact rc=$?"
-ls -la $O
+python profiles/ncu_summary.py $O/prof_exact.ncu-rep > $O/ncu_full_exact.txt 2>&1; rm -f $O/prof_exact.ncu-rep
+du -sh $O; ls -la $O
