@@ -29,6 +29,7 @@ N_SAMPLE = 1 << 26          # BASELINE configs[2]: 64M samples
 FLOPS = dict(eval_spectral=1013, eval_rgb=426, pdf=761, sample_rgb=1776)
 BYTES = dict(eval_spectral=44, eval_rgb=24, pdf=16, sample_rgb=36)
 METRIC = "sky+sun radiance Gevals/s (spectral eval, 16M directions)"
+WORKLOAD = "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths per GPU, t=3 a=0.3 eta=30deg, sun+sky"
 # dram__bytes_read.sum + dram__bytes_write.sum of one eval_spec_kernel launch on 2^24 rays (ncu --set full,
 # profiles/r1_summary.md); the algorithmic figure is 44 B x 2^24 = 738 MB (part of the output is still in L2)
 NCU_TRAFFIC = {"fast": 699.0e6, "exact": 701.3e6}
@@ -115,15 +116,16 @@ def emitter_kwargs():
     return dict(turbidity=3.0, albedo=0.3, sun_direction=common.sun_dir_from_elevation(30.0))
 
 
-def cpu_reference_rate(n_sample, threads, spectral=True, seed=0):
-    """Times the reference's own CPU code (oracle/_ref: its sunsky.cpp compiled in place, array flavour)
-    on `n_sample` directions with `threads` host threads. Returns (Gevals/s, seconds)."""
+def cpu_reference_rate(n_sample, threads, spectral=True, seed=0, flavour=1):
+    """Times the reference's own CPU code (oracle/_ref: its sunsky.cpp compiled in place; flavour 1 = the array code
+    path of llvm_ad_*, flavour 0 = scalar_*) on `n_sample` directions with `threads` host threads.
+    Returns (Gevals/s, seconds)."""
     import ref_oracle
     import common
     rng = np.random.default_rng(seed)
     wo = common.hemisphere_dirs(n_sample, rng)
     wav = np.minimum(360.0 + 360.0 * rng.random((4, n_sample), dtype=np.float32), 719.99).astype(np.float32) if spectral else None
-    r = ref_oracle.RefEmitter(spectral=spectral, flavour=1, **emitter_kwargs())
+    r = ref_oracle.RefEmitter(spectral=spectral, flavour=flavour, **emitter_kwargs())
     r.eval(-wo[:, :4096], None if wav is None else wav[:, :4096], threads=1)
     t0 = time.perf_counter()
     r.eval(-wo, wav, threads=threads)
@@ -155,7 +157,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / len(rates) * (N_EVAL / n_sample),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths, t=3 a=0.3 eta=30deg, sun+sky"},
+        "config": {"workload": WORKLOAD},
         "cpu_baseline": {"value": value, "unit": "Gevals/s", "cores": threads, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": "Gevals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -433,10 +435,12 @@ def main():
                 n_s = 1 << 20
                 r, dt = cpu_reference_rate(n_s, threads, True)
                 r1, dt1 = cpu_reference_rate(1 << 16, 1, True)
+                rs, dts = cpu_reference_rate(1 << 18, threads, True, flavour=0)
                 cpu = {"value": r, "unit": "Gevals/s", "cores": threads, "kind": "reference",
-                       "sample": f"{n_s} of the {N_EVAL} directions (same distribution), {dt:.1f} s; "
-                                 f"1 thread: {r1 * 1e3:.3f} Mevals/s; host has {cores} logical cores",
-                       "single_thread_value": r1}
+                       "sample": f"{n_s} of the {N_EVAL} directions (same distribution), {dt:.1f} s, array variant (llvm_ad_* "
+                                 f"code path); 1 thread: {r1 * 1e3:.3f} Mevals/s; scalar_spectral variant on {threads} threads: "
+                                 f"{rs * 1e3:.3f} Mevals/s; host has {cores} logical cores",
+                       "single_thread_value": r1, "scalar_variant_value": rs}
         except Exception as ex:  # the baseline is reported, never required
             cpu = {"error": str(ex)}
 
@@ -449,8 +453,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths per GPU, "
-                                   "t=3 a=0.3 eta=30deg, sun+sky",
+            "config": {"workload": WORKLOAD,
                        "l2": "inputs (470 MB/step) exceed the 126 MB L2; no flush needed",
                        "arith": args.arith + (" (MUFU transcendentals for well-conditioned terms, within 1e-5 of the reference; "
                                               "directions bit-identical)" if args.arith == "fast" else

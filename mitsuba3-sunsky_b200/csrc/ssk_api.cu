@@ -26,12 +26,13 @@ int fail(int code, const std::string &msg) { g_err = msg; return code; }
     } while (0)
 
 struct Staging {            // per-context pinned + device scratch for the *_host entry points
-    static constexpr int kStreams = 3;
+    static constexpr int kStreams = 6;      // slots allocated; `active` of them are used (SSK_HOST_STREAMS, default 3)
+    int active = 3;
     size_t chunk = 0;       // elements per chunk
     int planes = 0;
-    float *pinned[kStreams] = { nullptr, nullptr, nullptr };
-    float *dev[kStreams] = { nullptr, nullptr, nullptr };
-    cudaStream_t stream[kStreams] = { nullptr, nullptr, nullptr };
+    float *pinned[kStreams] = {};
+    float *dev[kStreams] = {};
+    cudaStream_t stream[kStreams] = {};
     std::mutex mu;
 };
 
@@ -397,9 +398,13 @@ int launch_sample_ray(const ssk_ctx *ctx, const float *wl_sample, const float *c
 // ---- host entry points: chunked H2D -> kernel -> D2H over 3 streams with pinned staging ---------
 int ensure_staging(const ssk_ctx *ctx, int planes) {
     Staging &st = ctx->st;
-    const size_t chunk = (size_t) 1 << 20;          // 1 Mi elements per chunk and plane (4 MiB)
+    // elements per chunk and plane (default 1 Mi = 4 MiB) and streams in rotation: SSK_HOST_CHUNK_LOG2 / SSK_HOST_STREAMS
+    static const int chunk_log2 = getenv("SSK_HOST_CHUNK_LOG2") ? std::min(24, std::max(12, atoi(getenv("SSK_HOST_CHUNK_LOG2")))) : 20;
+    static const int n_streams = getenv("SSK_HOST_STREAMS") ? std::min(Staging::kStreams, std::max(1, atoi(getenv("SSK_HOST_STREAMS")))) : 3;
+    const size_t chunk = (size_t) 1 << chunk_log2;
     if (st.planes >= planes && st.chunk == chunk) return SSK_OK;
-    for (int i = 0; i < Staging::kStreams; ++i) {
+    st.active = n_streams;
+    for (int i = 0; i < st.active; ++i) {
         if (st.pinned[i]) cudaFreeHost(st.pinned[i]);
         if (st.dev[i]) cudaFree(st.dev[i]);
         st.pinned[i] = nullptr; st.dev[i] = nullptr;
@@ -433,6 +438,7 @@ int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *c
     const size_t n_chunks = (n + chunk - 1) / chunk;
     // pending[i]: chunk index whose results still sit in staging slot i (pageable outputs only)
     std::vector<long long> pending(Staging::kStreams, -1);
+    const int n_slots = st.active;
     auto drain = [&](int slot) -> int {
         if (pending[slot] < 0) return SSK_OK;
         SSK_CUDA(cudaStreamSynchronize(st.stream[slot]));
@@ -445,7 +451,7 @@ int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *c
         return SSK_OK;
     };
     for (size_t ci = 0; ci < n_chunks; ++ci) {
-        int slot = (int) (ci % Staging::kStreams);
+        int slot = (int) (ci % n_slots);
         if (int rc = drain(slot)) return rc;
         size_t off = ci * chunk, m = std::min(chunk, n - off);
         cudaStream_t s = st.stream[slot];
@@ -469,7 +475,7 @@ int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *c
         }
         pending[slot] = (long long) ci;
     }
-    for (int i = 0; i < Staging::kStreams; ++i)
+    for (int i = 0; i < n_slots; ++i)
         if (int rc = drain(i)) return rc;
     return SSK_OK;
 }
