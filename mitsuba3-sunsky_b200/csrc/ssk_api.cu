@@ -268,6 +268,13 @@ int launch_sample_pair_t(const ssk_ctx *ctx, const SampleArgs &a, size_t n, cuda
     sample_pair_kernel<A, Spectral><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
     return SSK_OK;
 }
+template <int A, bool Spectral>
+int launch_sample_sorted_t(const ssk_ctx *ctx, const SampleArgs &a, size_t n, cudaStream_t s) {
+    int grid = 1;
+    if (int rc = occupancy_grid(ctx, sample_sorted_kernel<A, Spectral>, n, &grid, 2)) return rc;
+    sample_sorted_kernel<A, Spectral><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    return SSK_OK;
+}
 /// every non-null plane of the argument block 8-byte aligned: the two-samples-per-thread kernel can be used
 bool sample_planes_aligned8(const SampleArgs &a) {
     const void *ps[] = { a.u0, a.u1, a.px, a.py, a.pz, a.w0, a.w1, a.w2, a.w3, a.dx, a.dy, a.dz, a.pdf,
@@ -279,6 +286,15 @@ bool sample_planes_aligned8(const SampleArgs &a) {
 template <int A>
 int launch_sample_a(const ssk_ctx *ctx, bool spectral, bool vec, const SampleArgs &a, size_t n, cudaStream_t s) {
     (void) vec;
+    // both techniques in play (0 < w < 1): technique-sorted tiles; one technique only: plain pairs
+    static const bool no_sort = getenv("SSK_SAMPLE_NOSORT") != nullptr;
+    const float w = ctx->E.block.sky_w;
+    // Measured on B200 (2^24 samples, t=6 a=0.5 eta=50.2): FAST RGB 18.1 -> 20.9 Gsamples/s sorted; FAST spectral
+    // 14.8 -> 13.6, EXACT RGB 13.8 -> 13.0, EXACT spectral 9.4 -> 6.6 (their 73-112 KB bodies already stall on
+    // instruction fetch, and warps of one CTA running different techniques widen the fetch working set) -- so only
+    // the FAST RGB kernel sorts.
+    if (A == kFast && !spectral && !getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a) && w > 0.f && w < 1.f && !no_sort)
+        return launch_sample_sorted_t<kFast, false>(ctx, a, n, s);
     if (!getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a))
         return spectral ? launch_sample_pair_t<A, true>(ctx, a, n, s) : launch_sample_pair_t<A, false>(ctx, a, n, s);
     if (spectral) return launch_sample_t<A, kSampleRays, true>(ctx, a, n, s);
@@ -398,8 +414,10 @@ int launch_sample_ray(const ssk_ctx *ctx, const float *wl_sample, const float *c
 // ---- host entry points: chunked H2D -> kernel -> D2H over 3 streams with pinned staging ---------
 int ensure_staging(const ssk_ctx *ctx, int planes) {
     Staging &st = ctx->st;
-    // elements per chunk and plane (default 1 Mi = 4 MiB) and streams in rotation: SSK_HOST_CHUNK_LOG2 / SSK_HOST_STREAMS
-    static const int chunk_log2 = getenv("SSK_HOST_CHUNK_LOG2") ? std::min(24, std::max(12, atoi(getenv("SSK_HOST_CHUNK_LOG2")))) : 20;
+    // elements per chunk and plane and streams in rotation (SSK_HOST_CHUNK_LOG2 / SSK_HOST_STREAMS). Measured on
+    // B200, spectral eval, 2^24 rays, pinned buffers: 2^18 1.29, 2^19 1.44, 2^20 1.54, 2^21 1.61, 2^22 1.57 Gevals/s;
+    // 2 to 6 streams within 1 % of each other -> 2 Mi elements (8 MiB per plane), 3 streams
+    static const int chunk_log2 = getenv("SSK_HOST_CHUNK_LOG2") ? std::min(24, std::max(12, atoi(getenv("SSK_HOST_CHUNK_LOG2")))) : 21;
     static const int n_streams = getenv("SSK_HOST_STREAMS") ? std::min(Staging::kStreams, std::max(1, atoi(getenv("SSK_HOST_STREAMS")))) : 3;
     const size_t chunk = (size_t) 1 << chunk_log2;
     if (st.planes >= planes && st.chunk == chunk) return SSK_OK;

@@ -371,6 +371,109 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
     }
 }
 
+// ---- sample_direction with both techniques active: technique-sorted tiles -------------------------------
+// With 0 < m_sky_sampling_w < 1 about half of the samples take the sun-cone technique and half the TGMM, at
+// random: in sample_pair_kernel every warp then executes both samplers and the sun-disc evaluation for a few
+// lanes each (measured: 18 vs 36 Gsamples/s sky-only). Here a CTA takes a tile of 512 consecutive samples,
+// ranks them by technique with warp ballots (sky samples first, sun samples after) and hands each thread two
+// samples of the SAME technique, so all warps but the one on the boundary are homogeneous. Inputs of the tile are
+// staged in shared memory, outputs are scattered back to their own slots (32-bit stores inside the tile's lines,
+// merged in L2). Per-sample arithmetic is the pair code unchanged: results are bit-identical to any other pairing.
+constexpr int kTile = 2 * kThreads;
+__device__ __forceinline__ float2 gld2(const float *p, size_t ia, size_t ib, bool two, float pad) {
+    return make_float2(__ldcs(p + ia), two ? __ldcs(p + ib) : pad);
+}
+__device__ __forceinline__ void gst2(float *p, size_t ia, size_t ib, bool two, float2 v) {
+    __stcs(p + ia, v.x);
+    if (two) __stcs(p + ib, v.y);
+}
+template <int A, bool Spectral>
+__global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
+sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
+    __shared__ __align__(8) float tu0[kTile], tu1[kTile];
+    __shared__ unsigned short perm[kTile];
+    __shared__ int wcount[kThreads / 32][2];
+    stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const size_t n_tiles = (n + kTile - 1) / kTile;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t base = tile * kTile;
+        const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
+        // 1. stage the tile's samples (coalesced 64-bit loads) and classify
+        const int l0 = 2 * t, l1 = 2 * t + 1;
+        float2 v0 = f2(0.f, 0.f), v1 = f2(0.f, 0.f);
+        if (l1 < valid) { v0 = __ldcs(reinterpret_cast<const float2 *>(a.u0 + base + l0)); v1 = __ldcs(reinterpret_cast<const float2 *>(a.u1 + base + l0)); }
+        else if (l0 < valid) { v0.x = __ldcs(a.u0 + base + l0); v1.x = __ldcs(a.u1 + base + l0); }
+        tu0[l0] = v0.x; tu0[l1] = v0.y; tu1[l0] = v1.x; tu1[l1] = v1.y;
+        const bool ok0 = l0 < valid, ok1 = l1 < valid;
+        const bool sky0 = ok0 && v0.x < U.sky_w, sky1 = ok1 && v0.y < U.sky_w;
+        const unsigned bs0 = __ballot_sync(0xffffffffu, sky0), bs1 = __ballot_sync(0xffffffffu, sky1);
+        const unsigned bn0 = __ballot_sync(0xffffffffu, ok0 && !sky0), bn1 = __ballot_sync(0xffffffffu, ok1 && !sky1);
+        if (lane == 0) { wcount[warp][0] = __popc(bs0) + __popc(bs1); wcount[warp][1] = __popc(bn0) + __popc(bn1); }
+        __syncthreads();
+        // 2. slot of each sample: sky samples first (warp-major), then sun samples
+        int sky_before = 0, sun_before = 0, sky_total = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) {
+            const int cs = wcount[w][0], cn = wcount[w][1];
+            if (w < warp) { sky_before += cs; sun_before += cn; }
+            sky_total += cs;
+        }
+        if (sky0) perm[sky_before + __popc(bs0 & lt)] = (unsigned short) l0;
+        else if (ok0) perm[sky_total + sun_before + __popc(bn0 & lt)] = (unsigned short) l0;
+        if (sky1) perm[sky_before + __popc(bs0) + __popc(bs1 & lt)] = (unsigned short) l1;
+        else if (ok1) perm[sky_total + sun_before + __popc(bn0) + __popc(bn1 & lt)] = (unsigned short) l1;
+        __syncthreads();
+        // 3. two samples of one technique per thread
+        if (l0 < valid) {
+            const bool two = l1 < valid;
+            const int la = perm[l0], lb = two ? perm[l1] : la;
+            const size_t ia = base + la, ib = base + lb;
+            DirSampleP s = sample_dir_p<A>(U, S, f2(tu0[la], two ? tu0[lb] : 0.5f), f2(tu1[la], two ? tu1[lb] : 0.5f));
+            gst2(a.dx, ia, ib, two, s.d_world.x); gst2(a.dy, ia, ib, two, s.d_world.y); gst2(a.dz, ia, ib, two, s.d_world.z);
+            gst2(a.pdf, ia, ib, two, s.pdf);
+            float2 e[4];
+            if (Spectral) {
+                float2 w0 = gld2(a.w0, ia, ib, two, 0.f), w1 = gld2(a.w1, ia, ib, two, 0.f), w2 = gld2(a.w2, ia, ib, two, 0.f),
+                       w3 = gld2(a.w3, ia, ib, two, 0.f);
+                float ea[4], eb[4];
+                const float wa[4] = { w0.x, w1.x, w2.x, w3.x }, wb[4] = { w0.y, w1.y, w2.y, w3.y };
+                eval_spec<A>(U, S, pairs, sun_rad, Vec3{ -s.d_world.x.x, -s.d_world.y.x, -s.d_world.z.x }, wa, s.active0, ea);
+                eval_spec<A>(U, S, pairs, sun_rad, Vec3{ -s.d_world.x.y, -s.d_world.y.y, -s.d_world.z.y }, wb, s.active1 && two, eb);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) e[c] = f2(ea[c], eb[c]);
+            } else {
+                Vec3p wi = { neg2(s.d_world.x), neg2(s.d_world.y), neg2(s.d_world.z) };
+                eval_rgb_p<A>(U, sun_rad, wi, s.active0, s.active1 && two, e);
+            }
+            const float2 inv_pdf = A == kFast ? f2(hw_rcp(s.pdf.x), hw_rcp(s.pdf.y)) : f2(fdiv(1.f, s.pdf.x), fdiv(1.f, s.pdf.y));
+#pragma unroll
+            for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
+                float2 w = mul2(e[c], inv_pdf);
+                w = f2((fabsf(w.x) < INFINITY) ? w.x : 0.f, (fabsf(w.y) < INFINITY) ? w.y : 0.f);
+                gst2(c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3, ia, ib, two, w);
+            }
+            if (a.ox || a.dist) {          // bounding-sphere bookkeeping (sunsky.cpp:415-421), as sample_pair_kernel
+                float2 px = f2(0.f, 0.f), py = px, pz = px;
+                if (a.px) { px = gld2(a.px, ia, ib, two, 0.f); py = gld2(a.py, ia, ib, two, 0.f); pz = gld2(a.pz, ia, ib, two, 0.f); }
+                Vec3p rel = { add2s(px, -U.bs_center[0]), add2s(py, -U.bs_center[1]), add2s(pz, -U.bs_center[2]) };
+                float2 nr = sqrt2(sqnorm3_p(rel));
+                float2 dd = mul2s(f2(fmaxf(U.bs_radius, nr.x), fmaxf(U.bs_radius, nr.y)), 2.f);
+                if (a.dist) gst2(a.dist, ia, ib, two, dd);
+                if (a.ox) {
+                    gst2(a.ox, ia, ib, two, fma2(s.d_world.x, dd, px)); gst2(a.oy, ia, ib, two, fma2(s.d_world.y, dd, py));
+                    gst2(a.oz, ia, ib, two, fma2(s.d_world.z, dd, pz));
+                }
+            }
+        }
+        __syncthreads();               // tu0 / tu1 / perm are rewritten by the next tile
+    }
+}
+
 // ---- emitter setup on the device: the two 200 x 200 quadratures of estimate_sky_sun_ratio ------------------
 // The reference integrates on the host / in a traced kernel and reduces with the LLVM backend's block sum:
 // sequential fp32 adds inside 16384-wide chunks, then over the chunk partials (ssk_host.cuh llvm_block_sum).
