@@ -380,24 +380,29 @@ def main():
             l0 = ssk.launch_count()
             barrier()
             t0 = time.perf_counter()
-            pending = None
-            for s0 in range(0, len(mine), chunk):
+            pools, events = [None, None], [None, None]      # two pools of contexts, re-parametrised in batches
+            for k, s0 in enumerate(range(0, len(mine), chunk)):
                 idx = mine[s0:s0 + chunk]
+                slot = k & 1
+                if events[slot] is not None:
+                    events[slot].synchronize()              # contexts outlive their previous launches
                 ts = time.perf_counter()
-                ems = sweep_mod.make_emitters([params[f] for f in idx], spectral, local, args.arith)
+                if pools[slot] is None or len(pools[slot]) != len(idx):
+                    for e_ in pools[slot] or []:
+                        e_.close()
+                    pools[slot] = sweep_mod.make_emitters([params[f] for f in idx], spectral, local, args.arith)
+                else:
+                    ssk.update_batch(pools[slot], [dict(turbidity=params[f]["turbidity"], albedo=params[f]["albedo"],
+                                                        sun_direction=sweep_mod.sun_direction(params[f]["eta_deg"])) for f in idx])
                 t_setup += time.perf_counter() - ts
-                ssk.envmaps(ems, width, height, (440.0, 520.0, 600.0, 680.0) if spectral else None, out=buf[:len(idx)])
+                ssk.envmaps(pools[slot], width, height, (440.0, 520.0, 600.0, 680.0) if spectral else None, out=buf[:len(idx)])
                 if gather and world > 1:
                     dist.gather(buf, list(full.split(chunk)) if rank == 0 else None, dst=0)
-                ev = torch.cuda.Event(); ev.record()
-                if pending is not None:                  # previous chunk: contexts outlive their launches
-                    pending[0].synchronize()
-                    for e_ in pending[1]:
-                        e_.close()
-                pending = (ev, ems)
+                events[slot] = torch.cuda.Event(); events[slot].record()
             torch.cuda.synchronize()
-            for e_ in (pending[1] if pending else []):
-                e_.close()
+            for slot in (0, 1):
+                for e_ in pools[slot] or []:
+                    e_.close()
             barrier()
             windows.append((t0, time.perf_counter()))
             sec = max_over_ranks(windows[-1][1] - t0)
@@ -418,7 +423,7 @@ def main():
             sw["animation_128x8192x4096_spectral_gather"] = sweep_bench("animation", 8192, 4096, 2, True)
         sw["note"] = ("BASELINE configs[3] (64 sun elevations x 4 turbidities, RGB) and configs[4] (128-frame turbidity/albedo "
                       "animation, spectral, wavelengths 440/520/600/680 nm); wall clock between barriers, max over ranks, "
-                      "includes creating every frame's emitter (host interpolation + device quadrature)")
+                      "includes setting up every frame's emitter (host interpolation + batched device quadrature, ssk_update_batch)")
         extra["sweeps"] = sw
         extra["note"] = ("configs[1] inputs for eval/pdf (2^24 directions), configs[2] for sample_direction (2^26 samples, "
                          "t=6 a=0.5 eta=50.2deg; sky only = sampling_test.py). fp32_frac uses the algorithmic flops of SURVEY 8d.")

@@ -106,6 +106,11 @@ int ssk_create(const ssk_params *p, const char *dataset_dir, int device, int mod
 
 /* parameters_changed() after mi.traverse(emitter) updates (src/emitters/sunsky.cpp:220-285). */
 int ssk_update(ssk_ctx *ctx, const ssk_params *p);
+/* parameters_changed for n emitters of one device and mode at once (time-of-day sweeps, animations): the same
+ * result as n ssk_update calls, but the setup quadratures of all emitters share one chain-sum launch and one
+ * synchronisation (0.14 ms per emitter one by one; see DESIGN.md for the batched figure). On failure no context is
+ * modified. */
+int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n);
 
 /* set_scene(): bounding sphere from the scene bbox; NULL pointers = invalid bbox (:287-301). */
 int ssk_set_scene(ssk_ctx *ctx, const float *bbox_min, const float *bbox_max);

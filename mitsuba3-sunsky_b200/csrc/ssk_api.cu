@@ -80,56 +80,72 @@ int upload_block(ssk_ctx *ctx) {
 // ---- device execution of the setup quadrature ---------------------------------------------------------------
 struct SetupScratch {       // one per device, shared by every context on it (setup calls serialise on `mu`)
     float *d_gl = nullptr, *d_buf = nullptr, *d_partial = nullptr, *h_partial = nullptr;
+    int capacity = 0;       // emitters d_buf / the partial buffers hold (1, grown to kSetupBatch by the first batch)
     cudaStream_t stream = nullptr;
     std::mutex mu;
 };
 constexpr int kMaxDevices = 64;
 SetupScratch g_setup[kMaxDevices];
 constexpr int kMaxChains = 2 * kMaxChannels * kQuadChunks;
+constexpr int kSetupBatch = 16;                       // emitters per batched quadrature (69 MB of scratch when used)
+constexpr size_t kEmitterStride = (size_t) kMaxChains * kQuadChunk;
 
-int ensure_setup_scratch(SetupScratch &sc) {
-    if (sc.d_gl) return SSK_OK;
-    SSK_CUDA(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
-    SSK_CUDA(cudaMalloc(&sc.d_gl, 2 * kQuadN * sizeof(float)));
-    SSK_CUDA(cudaMalloc(&sc.d_buf, (size_t) kMaxChains * kQuadChunk * sizeof(float)));
-    SSK_CUDA(cudaMalloc(&sc.d_partial, kMaxChains * sizeof(float)));
-    SSK_CUDA(cudaMallocHost(&sc.h_partial, kMaxChains * sizeof(float)));
-    SSK_CUDA(cudaMemcpy(sc.d_gl, gauss_legendre_200().data(), 2 * kQuadN * sizeof(float), cudaMemcpyHostToDevice));
+int ensure_setup_scratch(SetupScratch &sc, int emitters) {
+    if (!sc.d_gl) {
+        SSK_CUDA(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
+        SSK_CUDA(cudaMalloc(&sc.d_gl, 2 * kQuadN * sizeof(float)));
+        SSK_CUDA(cudaMemcpy(sc.d_gl, gauss_legendre_200().data(), 2 * kQuadN * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    if (sc.capacity >= emitters) return SSK_OK;
+    if (sc.d_buf) { cudaFree(sc.d_buf); cudaFree(sc.d_partial); cudaFreeHost(sc.h_partial); sc.d_buf = nullptr; sc.capacity = 0; }
+    SSK_CUDA(cudaMalloc(&sc.d_buf, (size_t) emitters * kEmitterStride * sizeof(float)));
+    SSK_CUDA(cudaMalloc(&sc.d_partial, (size_t) emitters * kMaxChains * sizeof(float)));
+    SSK_CUDA(cudaMallocHost(&sc.h_partial, (size_t) emitters * kMaxChains * sizeof(float)));
+    sc.capacity = emitters;
     return SSK_OK;
 }
 
-/// QuadratureFn of a context with a device: preliminary block up, 80 000 nodes evaluated, chain sums, 66 floats back
-int quadrature_device(ssk_ctx *ctx, const HostEmitter &E, float sky_rad[11], float sun_rad[11]) {
-    if (ctx->device >= kMaxDevices) return fail(SSK_ERR_UNSUPPORTED, "device ordinal too large");
-    SetupScratch &sc = g_setup[ctx->device];
+/// Quadratures of `n` emitters of one device and mode in groups of kSetupBatch: per emitter one block upload and one
+/// node-evaluation launch, per group ONE chain-sum launch, one copy back and one synchronisation.
+int quadrature_device_batch(ssk_ctx *const *ctxs, int n, float (*sky_rad)[11], float (*sun_rad)[11]) {
+    const int device = ctxs[0]->device;
+    if (device >= kMaxDevices) return fail(SSK_ERR_UNSUPPORTED, "device ordinal too large");
+    SetupScratch &sc = g_setup[device];
     std::lock_guard<std::mutex> lock(sc.mu);
-    SSK_CUDA(cudaSetDevice(ctx->device));
-    if (int rc = ensure_setup_scratch(sc)) return rc;
-    const int C = E.n_channels, nchains = 2 * C * kQuadChunks;
-    static const bool trace = getenv("SSK_SETUP_TRACE") != nullptr;      // stderr: microseconds per phase
-    auto now = [] { return std::chrono::steady_clock::now(); };
-    auto t0 = now();
-    SSK_CUDA(cudaMemcpyAsync(ctx->d_block, &E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, sc.stream));
-    setup_quadrature_kernel<<<(2 * kQuadNodes + kThreads - 1) / kThreads, kThreads, 0, sc.stream>>>(
-        E.block, ctx->d_block, sc.d_gl, sc.d_buf, C);
-    setup_sum_kernel<<<nchains, 32, 0, sc.stream>>>(sc.d_buf, sc.d_partial);
-    g_launches += 2;
-    SSK_CUDA(cudaGetLastError());
-    SSK_CUDA(cudaMemcpyAsync(sc.h_partial, sc.d_partial, nchains * sizeof(float), cudaMemcpyDeviceToHost, sc.stream));
-    auto t1 = now();
-    SSK_CUDA(cudaStreamSynchronize(sc.stream));
-    if (trace) {
-        auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
-        fprintf(stderr, "ssk setup: enqueue %.1f us, device wait %.1f us\n", us(t0, t1), us(t1, now()));
-    }
-    for (int which = 0; which < 2; ++which) {
-        const float J = which == 0 ? quad_sky_jacobian() : quad_sun_jacobian(E.block);
-        for (int c = 0; c < C; ++c) {
-            float total = 0.f;                       // llvm_block_sum: partials added in chunk order
-            for (int k = 0; k < kQuadChunks; ++k) total = total + sc.h_partial[(which * C + c) * kQuadChunks + k];
-            (which == 0 ? sky_rad : sun_rad)[c] = total * J;
+    SSK_CUDA(cudaSetDevice(device));
+    if (int rc = ensure_setup_scratch(sc, n > 1 ? kSetupBatch : 1)) return rc;
+    const int C = ctxs[0]->E.n_channels, nchains = 2 * C * kQuadChunks;
+    for (int g0 = 0; g0 < n; g0 += sc.capacity) {
+        const int m = std::min(sc.capacity, n - g0);
+        for (int e = 0; e < m; ++e) {
+            ssk_ctx *ctx = ctxs[g0 + e];
+            SSK_CUDA(cudaMemcpyAsync(ctx->d_block, &ctx->E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, sc.stream));
+            setup_quadrature_kernel<<<(2 * kQuadNodes + kThreads - 1) / kThreads, kThreads, 0, sc.stream>>>(
+                ctx->E.block, ctx->d_block, sc.d_gl, sc.d_buf + (size_t) e * kEmitterStride, C);
         }
+        setup_sum_kernel<<<m * nchains, 32, 0, sc.stream>>>(sc.d_buf, sc.d_partial, nchains, kEmitterStride);
+        g_launches += m + 1;
+        SSK_CUDA(cudaGetLastError());
+        SSK_CUDA(cudaMemcpyAsync(sc.h_partial, sc.d_partial, (size_t) m * nchains * sizeof(float), cudaMemcpyDeviceToHost, sc.stream));
+        SSK_CUDA(cudaStreamSynchronize(sc.stream));
+        for (int e = 0; e < m; ++e)
+            for (int which = 0; which < 2; ++which) {
+                const float J = which == 0 ? quad_sky_jacobian() : quad_sun_jacobian(ctxs[g0 + e]->E.block);
+                for (int c = 0; c < C; ++c) {
+                    float total = 0.f;                   // llvm_block_sum: partials added in chunk order
+                    for (int k = 0; k < kQuadChunks; ++k) total = total + sc.h_partial[e * nchains + (which * C + c) * kQuadChunks + k];
+                    (which == 0 ? sky_rad : sun_rad)[g0 + e][c] = total * J;
+                }
+            }
     }
+    return SSK_OK;
+}
+
+/// QuadratureFn of a context with a device: a batch of one
+int quadrature_device(ssk_ctx *ctx, const HostEmitter &, float sky_rad[11], float sun_rad[11]) {
+    float sky[1][11], sun[1][11];
+    if (int rc = quadrature_device_batch(&ctx, 1, sky, sun)) return rc;
+    memcpy(sky_rad, sky[0], sizeof(sky[0])); memcpy(sun_rad, sun[0], sizeof(sun[0]));
     return SSK_OK;
 }
 
@@ -580,6 +596,37 @@ int ssk_update(ssk_ctx *ctx, const ssk_params *p) {
         try { build_on(ctx, *p, false); }
         catch (...) { ctx->E = backup; upload_block(ctx); throw; }
         return upload_block(ctx);
+    });
+}
+
+int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n) {
+    if (n < 0 || (n > 0 && (!ctxs || !params))) return fail(SSK_ERR_INVALID, "null argument");
+    if (n == 0) return SSK_OK;
+    for (int i = 0; i < n; ++i) {
+        if (!ctxs[i]) return fail(SSK_ERR_INVALID, "null context");
+        if (ctxs[i]->device != ctxs[0]->device || ctxs[i]->mode != ctxs[0]->mode)
+            return fail(SSK_ERR_INVALID, "ssk_update_batch: contexts must share one device and one mode");
+    }
+    if (ctxs[0]->device < 0 || getenv("SSK_HOST_SETUP")) {
+        for (int i = 0; i < n; ++i) if (int rc = ssk_update(ctxs[i], &params[i])) return rc;
+        return SSK_OK;
+    }
+    return guarded([&]() -> int {
+        std::vector<HostEmitter> backup(n);
+        for (int i = 0; i < n; ++i) backup[i] = ctxs[i]->E;
+        auto rollback = [&] { for (int i = 0; i < n; ++i) { ctxs[i]->E = backup[i]; upload_block(ctxs[i]); } };
+        try {
+            for (int i = 0; i < n; ++i) build_emitter_pre(ctxs[i]->E, params[i], false);
+            std::vector<float> sky((size_t) n * 11), sun((size_t) n * 11);
+            if (int rc = quadrature_device_batch(ctxs, n, reinterpret_cast<float (*)[11]>(sky.data()),
+                                                 reinterpret_cast<float (*)[11]>(sun.data()))) { rollback(); return rc; }
+            for (int i = 0; i < n; ++i) {
+                build_emitter_post(ctxs[i]->E, &sky[(size_t) i * 11], &sun[(size_t) i * 11]);
+                // bounding sphere is scene state, not a property: keep it (as ssk_update does)
+            }
+        } catch (...) { rollback(); throw; }
+        for (int i = 0; i < n; ++i) if (int rc = upload_block(ctxs[i])) return rc;
+        return SSK_OK;
     });
 }
 

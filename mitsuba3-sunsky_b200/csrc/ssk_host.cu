@@ -49,6 +49,15 @@ static bool invert3(const float *m, float *inv) {
 /// The constructor (from_constructor = true, sunsky.cpp:162-218) or parameters_changed()
 /// (false, sunsky.cpp:242-285) applied to `p`.
 void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor, const QuadratureFn &quad) {
+    build_emitter_pre(E, p, from_constructor);
+    float sky_rad[11], sun_rad[11];
+    if (quad) quad(E, sky_rad, sun_rad); else quadrature_host(E, sky_rad, sun_rad);
+    build_emitter_post(E, sky_rad, sun_rad);
+}
+
+/// Everything up to the quadrature: after this the block is complete except for the sampling weight and the
+/// wavelength density (which need the two integrals)
+void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructor) {
     validate_params(p, E.spectral);
     if (!from_constructor && (p.use_record != 0) != E.active_record)
         throw std::invalid_argument("an emitter keeps the sun parametrisation (direction or date/location) it was created with");
@@ -183,8 +192,12 @@ void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor, c
         B.p_k_phi[k] = (float) (kk / (double) sg_p); B.p_k_theta[k] = (float) (kk / (double) sg_t);
         B.p_wv[k] = (float) ((double) E.pmf[i] * 0.15915494309189533577 / (double) volume);
     }
-    // --- sky / sun sampling weight and wavelength distribution (:207-209 / 282-284)
-    estimate_sky_sun_ratio(E, quad);
+}
+
+/// Sky / sun sampling weight and wavelength distribution (:207-209 / 282-284) from the two integrals
+void build_emitter_post(HostEmitter &E, const float sky_rad[11], const float sun_rad[11]) {
+    EmitterBlock &B = E.block;
+    estimate_sky_sun_ratio(E, sky_rad, sun_rad);
     B.sky_w = E.sky_w; B.r_sky_w = 1.f / E.sky_w;
     B.one_minus_sky_w = 1.f - E.sky_w; B.r_one_minus_sky_w = 1.f / B.one_minus_sky_w;
     for (int i = 0; i < 10; ++i) { B.wl_pdf[i] = E.spectral_pdf[i]; B.wl_cdf[i] = E.spectral_cdf[i]; }
@@ -245,12 +258,10 @@ void quadrature_host(const HostEmitter &E, float sky_rad[11], float sun_rad[11])
 }
 
 /// estimate_sky_sun_ratio, array branch (sunsky.cpp:772-886): 200x200 Gauss-Legendre quadrature of the
-/// sky over the hemisphere and of the sun over its cone (done by `quad`), luminance ratio, and (spectral)
+/// sky over the hemisphere and of the sun over its cone (`sky_rad`, `sun_rad`), luminance ratio, and (spectral)
 /// the per-bin mean radiance that drives wavelength sampling.
-void estimate_sky_sun_ratio(HostEmitter &E, const QuadratureFn &quad) {
+void estimate_sky_sun_ratio(HostEmitter &E, const float sky_rad[11], const float sun_rad[11]) {
     const EmitterBlock &B = E.block;
-    float sky_rad[11], sun_rad[11];
-    if (quad) quad(E, sky_rad, sun_rad); else quadrature_host(E, sky_rad, sun_rad);
 
     float sky_lum = B.sky_scale, sun_lum = B.sun_scale;
     if (!E.spectral) {

@@ -286,7 +286,9 @@ void validate_params(const ssk_params &p, bool spectral);
 using QuadratureFn = std::function<void(const HostEmitter &E, float sky_rad[11], float sun_rad[11])>;
 void build_emitter(HostEmitter &E, const ssk_params &p, bool from_constructor, const QuadratureFn &quad = {});
 void quadrature_host(const HostEmitter &E, float sky_rad[11], float sun_rad[11]);
-void estimate_sky_sun_ratio(HostEmitter &E, const QuadratureFn &quad);
+void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructor);
+void build_emitter_post(HostEmitter &E, const float sky_rad[11], const float sun_rad[11]);
+void estimate_sky_sun_ratio(HostEmitter &E, const float sky_rad[11], const float sun_rad[11]);
 std::shared_ptr<const Datasets> datasets_for(const std::string &dir, bool spectral);   // process-wide cache
 const std::vector<float> &gauss_legendre_200();     // 200 nodes followed by 200 weights
 void set_ray_pdf_scale(HotBlock &B);

@@ -502,11 +502,12 @@ setup_quadrature_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *
 /// values are then broadcast lane by lane and added in index order: the only serial dependency left is the
 /// 16384-long chain of fp32 adds itself (every lane carries the same accumulator).
 __global__ void __launch_bounds__(32)
-setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial) {
-    const int chain = blockIdx.x, lane = threadIdx.x;
+setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int nchains, size_t emitter_stride) {
+    // blockIdx.x = emitter * nchains + chain (batched setup: several emitters' chains in one launch)
+    const int emitter = blockIdx.x / nchains, chain = blockIdx.x - emitter * nchains, lane = threadIdx.x;
     const int chunk = chain % kQuadChunks;
     const int len = min(kQuadChunk, kQuadNodes - chunk * kQuadChunk);
-    const float *p = buf + (size_t) chain * kQuadChunk;
+    const float *p = buf + (size_t) emitter * emitter_stride + (size_t) chain * kQuadChunk;
     constexpr int kTiles = 8;
     float acc = 0.f;
     for (int j0 = 0; j0 < len; j0 += 32 * kTiles) {
@@ -527,7 +528,7 @@ setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial) {
             }
         }
     }
-    if (lane == 0) partial[chain] = acc;
+    if (lane == 0) partial[blockIdx.x] = acc;
 }
 
 // ---- sample_wavelengths / sample_ray -------------------------------------------------------------------

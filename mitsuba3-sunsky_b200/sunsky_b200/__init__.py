@@ -373,6 +373,30 @@ class SunskyEmitter:
         return o, d, wav, wgt
 
 
+def update_batch(emitters, props_list):
+    """parameters_changed for several emitters of one device and mode at once (ssk_update_batch): props_list[i] are
+    the keyword arguments `emitters[i].update()` would take. All or nothing: on an error no emitter changes."""
+    if len(emitters) != len(props_list):
+        raise ValueError("one property dict per emitter")
+    if not emitters:
+        return
+    n = len(emitters)
+    arr = (Params * n)()
+    new = []
+    for i, (e, props) in enumerate(zip(emitters, props_list)):
+        unknown = set(props) - set(_PARAM_KEYS) | ({"sun_aperture"} & set(props))
+        if unknown:
+            raise TypeError(f"not a traversable sunsky parameter: {sorted(unknown)}")
+        p = Params.from_buffer_copy(e._params)
+        e._fill(p, props, creating=False)
+        arr[i] = p
+        new.append(p)
+    ctxs = (_capi.CTX * n)(*[e._ctx for e in emitters])
+    _check(_capi.lib().ssk_update_batch(ctxs, arr, n))
+    for e, p in zip(emitters, new):
+        e._params = p
+
+
 def envmaps(emitters, width, height, wavelengths4=None, out=None):
     """Equirectangular radiance maps, one per emitter (all on one device, same mode), written by one
     kernel launch straight into a torch CUDA tensor of shape (n_maps, C, height, width)."""

@@ -6,7 +6,7 @@ the kernel only writes. Each rank renders the frames `sharding.frames_for_rank` 
 exchanged unless the caller asks for the frames on rank 0 (`gather=True`)."""
 import numpy as np
 
-from . import SunskyEmitter, envmaps
+from . import SunskyEmitter, envmaps, update_batch
 from . import sharding
 
 
@@ -42,22 +42,28 @@ def render_sweep(config, width, height, rank=0, world_size=1, device=0, arith="e
     dev = torch.device("cuda", device)
     if out is None:
         out = torch.empty((len(mine), C, height, width), dtype=torch.float32, device=dev)
-    pending = None                                        # (event, emitters) of the chunk still rendering
-    for s in range(0, len(mine), chunk):
+    # Two pools of `chunk` emitter contexts, re-parametrised in batches (ssk_update_batch: one chain-sum launch and
+    # one synchronisation per chunk): while pool A's maps are being written, pool B's emitters are set up.
+    pools, events = [None, None], [None, None]
+    for k, s in enumerate(range(0, len(mine), chunk)):
         idx = mine[s:s + chunk]
-        # the next chunk's emitters are set up (host interpolation + device quadrature on the setup stream)
-        # while the previous chunk's maps are still being written
-        ems = make_emitters([params[f] for f in idx], spectral, device, arith)
-        envmaps(ems, width, height, wavelengths4 if spectral else None, out=out[s:s + len(idx)])
-        ev = torch.cuda.Event(); ev.record(torch.cuda.current_stream(dev))
-        if pending is not None:                           # the contexts must outlive their launches
-            pending[0].synchronize()
-            for e in pending[1]:
+        slot = k & 1
+        if events[slot] is not None:
+            events[slot].synchronize()                    # the contexts must outlive their previous launches
+        props = [dict(turbidity=params[f]["turbidity"], albedo=params[f]["albedo"],
+                      sun_direction=sun_direction(params[f]["eta_deg"])) for f in idx]
+        if pools[slot] is None or len(pools[slot]) != len(idx):
+            for e in pools[slot] or []:
                 e.close()
-        pending = (ev, ems)
-    if pending is not None:
-        pending[0].synchronize()
-        for e in pending[1]:
+            pools[slot] = make_emitters([params[f] for f in idx], spectral, device, arith)
+        else:
+            update_batch(pools[slot], props)
+        envmaps(pools[slot], width, height, wavelengths4 if spectral else None, out=out[s:s + len(idx)])
+        events[slot] = torch.cuda.Event(); events[slot].record(torch.cuda.current_stream(dev))
+    for slot in (0, 1):
+        if events[slot] is not None:
+            events[slot].synchronize()
+        for e in pools[slot] or []:
             e.close()
     if gather:
         full = sharding.gather_frames(out, n_frames, mode=mode, dst=0)

@@ -325,6 +325,36 @@ def test_device_setup_quadrature_matches_reference_bitwise(ssk, name):
     assert common.bit_equal(np.float32(h.sky_sampling_w), np.float32(s.sky_sampling_w))
 
 
+@pytest.mark.parametrize("spectral", [False, True])
+def test_update_batch_equals_individual_updates(ssk, spectral):
+    """ssk_update_batch (one chain-sum launch for many emitters) leaves every emitter in exactly the state n
+    ssk_update calls produce, including more emitters than one batch group holds; an invalid entry changes nothing."""
+    import sunsky_b200.sweep as sw
+    n = 19
+    props = [dict(turbidity=1.5 + 0.4 * k, albedo=0.05 * k, sun_direction=sw.sun_direction(3.0 + 4.5 * k)) for k in range(n)]
+    base = dict(turbidity=3.0, albedo=0.3, sun_direction=sw.sun_direction(30.0))
+    a = [ssk.SunskyEmitter(spectral=spectral, **base) for _ in range(n)]
+    b = [ssk.SunskyEmitter(spectral=spectral, **base) for _ in range(n)]
+    ssk.update_batch(a, props)
+    for e, p in zip(b, props):
+        e.update(**p)
+    rng = np.random.default_rng(3)
+    wo = common.hemisphere_dirs(257, rng); u = rng.random((2, 257), dtype=np.float32)
+    wav = (360 + 359 * rng.random((4, 257), dtype=np.float32)).astype(np.float32) if spectral else None
+    for x, y in zip(a, b):
+        sx, sy = x.state(), y.state()
+        assert common.bit_equal(np.float32(sx.sky_sampling_w), np.float32(sy.sky_sampling_w))
+        assert common.bit_equal(np.array(sx.spectral_cdf[:9], np.float32), np.array(sy.spectral_cdf[:9], np.float32))
+        assert common.bit_equal(x.eval(-wo, wav), y.eval(-wo, wav))
+        dx, px, wx = x.sample_direction(u, None, wav); dy, py, wy = y.sample_direction(u, None, wav)
+        assert common.bit_equal(dx, dy) and common.bit_equal(px, py) and common.bit_equal(wx, wy)
+    before = a[3].state().sky_sampling_w
+    bad = [dict(turbidity=2.0)] * n; bad[7] = dict(turbidity=11.0)
+    with pytest.raises(ssk.SunskyError):
+        ssk.update_batch(a, bad)
+    assert a[3].state().sky_sampling_w == before and a[3].traverse()["turbidity"] == pytest.approx(props[3]["turbidity"])
+
+
 @pytest.mark.parametrize("arith", ["exact", "fast"])
 @pytest.mark.parametrize("name", list(common.CONFIGS))
 def test_sample_wavelengths_matches_golden(ssk, name, arith):
