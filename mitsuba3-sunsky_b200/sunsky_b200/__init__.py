@@ -102,6 +102,12 @@ class SunskyEmitter:
                                   MODE_SPECTRAL if spectral else MODE_RGB, C.byref(ctx)))
         self._ctx = ctx
         self.channels = self._L.ssk_channels(ctx)
+        if not p.use_record:
+            # the constructor normalises sun_direction (sunsky.cpp:922); parameters_changed() then works on the
+            # stored m_sun_dir as is, so later updates must start from the normalised vector, not the raw property
+            sd = self.state().sun_dir_world
+            for i in range(3):
+                self._params.sun_direction[i] = sd[i]
 
     # -- property surface ---------------------------------------------------------------------
     def _fill(self, p, props, creating):

@@ -254,3 +254,18 @@ def test_dataset_generators_reproduce_shipped_files(tmp_path):
     assert len(names) == 8
     for n in names:
         assert filecmp.cmp(os.path.join(shipped, n), os.path.join(str(tmp_path), n), shallow=False), f"{n} differs"
+
+
+def test_update_batch_on_device_less_contexts(ssk):
+    """ssk_update_batch on contexts without a device runs the host setup per emitter; errors leave the failing
+    emitter untouched and are reported like ssk_update's."""
+    es = [ssk.SunskyEmitter(spectral=False, device=-1, turbidity=3.0, albedo=0.3, sun_direction=[0.3, 0.2, 0.6]) for _ in range(3)]
+    ref = ssk.SunskyEmitter(spectral=False, device=-1, turbidity=4.5, albedo=0.1, sun_direction=[0.3, 0.2, 0.6])
+    ssk.update_batch(es, [dict(turbidity=4.5, albedo=0.1)] * 3)
+    for e in es:
+        assert e.state().sky_sampling_w == ref.state().sky_sampling_w
+        assert common.bit_equal(np.array(e.state().sky_params, np.float32), np.array(ref.state().sky_params, np.float32))
+    with pytest.raises(ssk.SunskyError):
+        ssk.update_batch(es, [dict(turbidity=0.5)] * 3)
+    with pytest.raises(ValueError):
+        ssk.update_batch(es, [dict(turbidity=2.0)])
