@@ -31,6 +31,9 @@ constexpr int kThreads = 256;
 #ifndef SSK_SPECF_MINB
 #define SSK_SPECF_MINB 3
 #endif
+#ifndef SSK_ENVMAP_MINB
+#define SSK_ENVMAP_MINB 3
+#endif
 #ifndef SSK_PAIR_PREFETCH
 #define SSK_PAIR_PREFETCH 1
 #endif
@@ -600,7 +603,7 @@ SSK_HD Vec3 envmap_dir(int x, int y, int width, int height) {
 /// Equirect env map of one emitter. Write-only: no direction buffer. A thread handles 4 consecutive
 /// pixels of one row (width % 4 == 0 on the vector path), so sin/cos(theta) is computed once per thread.
 template <int A, bool Spectral>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, Spectral ? 1 : SSK_ENVMAP_MINB)
 envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, float4 wav4,
               float *__restrict__ out, int width, int height) {
     __shared__ __align__(16) HotBlock S;
@@ -615,7 +618,24 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < npix; i += stride) {
         float o[4][4];
-        if (!Spectral) {
+        if (!Spectral && vec) {
+            // RGB, 4 pixels of one row: row / column from one division, theta once, the reciprocal of the width once
+            // (fdiv_by_safe returns the IEEE quotient of envmap_dir bit for bit), phi pairs on the packed path
+            const int y = (int) (i / (size_t) width), x = (int) (i - (size_t) y * width);
+            const float fw = (float) width, rw = fdiv(1.f, fw);
+            const float theta = fdiv(SSK_PI * ((float) y + 0.5f), (float) height);
+#pragma unroll 1
+            for (int k = 0; k < 4; k += 2) {
+                float2 phi = f2(fdiv_by_safe(SSK_TWO_PI * ((float) (x + k) + 0.5f), fw, rw),
+                                fdiv_by_safe(SSK_TWO_PI * ((float) (x + k + 1) + 0.5f), fw, rw));
+                Vec3p d = sphdir_p(f2(theta, theta), phi);
+                Vec3p wi = { neg2(d.x), neg2(d.y), neg2(d.z) };
+                float2 e[3];
+                eval_rgb_p<A>(U, sun_rad, wi, true, true, e);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) { setk<R>(o[c], k, e[c].x); setk<R>(o[c], k + 1, e[c].y); }
+            }
+        } else if (!Spectral) {
             // RGB: two pixels at a time on the packed two-ray path (the same functions as eval_rgb_pair_kernel)
 #pragma unroll 1
             for (int k = 0; k < 4; k += 2) {
