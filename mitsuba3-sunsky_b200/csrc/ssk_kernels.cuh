@@ -31,6 +31,9 @@ constexpr int kThreads = 256;
 #ifndef SSK_SPECF_MINB
 #define SSK_SPECF_MINB 3
 #endif
+#ifndef SSK_ENVMAP_SPEC_MINB
+#define SSK_ENVMAP_SPEC_MINB 2     /* measured, spectral 4096x2048 map: FAST 1 -> 53.7, 2 -> 66.9, 3 -> 64.4 Gpixels/s; EXACT 30.7 / 38.4 / 39.2 */
+#endif
 #ifndef SSK_ENVMAP_MINB
 #define SSK_ENVMAP_MINB 3
 #endif
@@ -603,7 +606,7 @@ SSK_HD Vec3 envmap_dir(int x, int y, int width, int height) {
 /// Equirect env map of one emitter. Write-only: no direction buffer. A thread handles 4 consecutive
 /// pixels of one row (width % 4 == 0 on the vector path), so sin/cos(theta) is computed once per thread.
 template <int A, bool Spectral>
-__global__ void __launch_bounds__(kThreads, Spectral ? 1 : SSK_ENVMAP_MINB)
+__global__ void __launch_bounds__(kThreads, Spectral ? (A == kFast ? SSK_ENVMAP_SPEC_MINB : 3) : SSK_ENVMAP_MINB)
 envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, float4 wav4,
               float *__restrict__ out, int width, int height) {
     __shared__ __align__(16) HotBlock S;
@@ -648,6 +651,22 @@ envmap_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict
                 eval_rgb_p<A>(U, sun_rad, wi, true, true, e);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) { setk<R>(o[c], k, e[c].x); setk<R>(o[c], k + 1, e[c].y); }
+            }
+        } else if (Spectral && vec) {
+            // spectral, 4 pixels of one row: as the RGB branch (sin / cos of theta shared by the 4 pixels)
+            const int y = (int) (i / (size_t) width), x = (int) (i - (size_t) y * width);
+            const float fw = (float) width, rw = fdiv(1.f, fw);
+            float st, ct;
+            dsincos(fdiv(SSK_PI * ((float) y + 0.5f), (float) height), st, ct);
+#pragma unroll 1
+            for (int k = 0; k < 4; ++k) {
+                float sp, cp;
+                dsincos(fdiv_by_safe(SSK_TWO_PI * ((float) (x + k) + 0.5f), fw, rw), sp, cp);
+                Vec3 wi = { -(cp * st), -(sp * st), -ct };
+                float e[4] = { 0, 0, 0, 0 };
+                eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, e);
+#pragma unroll
+                for (int c = 0; c < C; ++c) setk<R>(o[c], k, e[c]);
             }
         } else
 #pragma unroll 1

@@ -49,6 +49,7 @@ def main():
         "sample_sky": lambda: sky.sample_direction(u),
         "sample_spec": lambda: ss.sample_direction(u, None, wav),
         "envmap": lambda: ssk.envmaps([er], 4096, 2048),
+        "envmap_spec": lambda: ssk.envmaps([es], 4096, 2048, (440.0, 520.0, 600.0, 680.0)),
         "wavelengths": lambda: es.sample_wavelengths(wi, u2),
         "ray_rgb": lambda: sr.sample_ray(None, u, u),
         "ray_spec": lambda: ss.sample_ray(u1, u, u),
@@ -73,7 +74,7 @@ def main():
             fn()
         e1.record(); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / max(args.reps, 1)
-        units = n if name != "envmap" else 4096 * 2048
+        units = n if not name.startswith("envmap") else 4096 * 2048
         print(f"{name}: {ms:.4f} ms per launch incl. output allocation, {units / ms / 1e6:.2f} G/s")
 
 
