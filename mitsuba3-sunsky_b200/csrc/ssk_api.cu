@@ -92,7 +92,11 @@ constexpr size_t kEmitterStride = (size_t) kMaxChains * kQuadChunk;
 
 int ensure_setup_scratch(SetupScratch &sc, int emitters) {
     if (!sc.d_gl) {
-        SSK_CUDA(cudaStreamCreateWithFlags(&sc.stream, cudaStreamNonBlocking));
+        // highest priority: when query / env-map kernels of other streams occupy the device, the few setup CTAs are
+        // scheduled as soon as any CTA retires instead of after everything already queued
+        int prio_lo = 0, prio_hi = 0;
+        SSK_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        SSK_CUDA(cudaStreamCreateWithPriority(&sc.stream, cudaStreamNonBlocking, prio_hi));
         SSK_CUDA(cudaMalloc(&sc.d_gl, 2 * kQuadN * sizeof(float)));
         SSK_CUDA(cudaMemcpy(sc.d_gl, gauss_legendre_200().data(), 2 * kQuadN * sizeof(float), cudaMemcpyHostToDevice));
     }
@@ -615,17 +619,32 @@ int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n) {
         std::vector<HostEmitter> backup(n);
         for (int i = 0; i < n; ++i) backup[i] = ctxs[i]->E;
         auto rollback = [&] { for (int i = 0; i < n; ++i) { ctxs[i]->E = backup[i]; upload_block(ctxs[i]); } };
+        static const bool trace = getenv("SSK_SETUP_TRACE") != nullptr;
+        auto now = [] { return std::chrono::steady_clock::now(); };
+        auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+        auto t0 = now(), t1 = t0, t2 = t0, t3 = t0;
         try {
             for (int i = 0; i < n; ++i) build_emitter_pre(ctxs[i]->E, params[i], false);
+            t1 = now();
             std::vector<float> sky((size_t) n * 11), sun((size_t) n * 11);
             if (int rc = quadrature_device_batch(ctxs, n, reinterpret_cast<float (*)[11]>(sky.data()),
                                                  reinterpret_cast<float (*)[11]>(sun.data()))) { rollback(); return rc; }
-            for (int i = 0; i < n; ++i) {
+            t2 = now();
+            for (int i = 0; i < n; ++i)
                 build_emitter_post(ctxs[i]->E, &sky[(size_t) i * 11], &sun[(size_t) i * 11]);
-                // bounding sphere is scene state, not a property: keep it (as ssk_update does)
-            }
+            t3 = now();
         } catch (...) { rollback(); throw; }
-        for (int i = 0; i < n; ++i) if (int rc = upload_block(ctxs[i])) return rc;
+        {   // final blocks: enqueued together on the setup stream, one synchronisation
+            SetupScratch &sc = g_setup[ctxs[0]->device];
+            std::lock_guard<std::mutex> lock(sc.mu);
+            SSK_CUDA(cudaSetDevice(ctxs[0]->device));
+            for (int i = 0; i < n; ++i)
+                SSK_CUDA(cudaMemcpyAsync(ctxs[i]->d_block, &ctxs[i]->E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, sc.stream));
+            SSK_CUDA(cudaStreamSynchronize(sc.stream));
+        }
+        if (trace)
+            fprintf(stderr, "ssk update_batch n=%d: backup+pre %.1f us, quadrature %.1f us, post %.1f us, upload %.1f us\n", n,
+                    us(t0, t1), us(t1, t2), us(t2, t3), us(t3, now()));
         return SSK_OK;
     });
 }

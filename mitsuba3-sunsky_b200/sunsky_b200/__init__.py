@@ -112,7 +112,10 @@ class SunskyEmitter:
     # -- property surface ---------------------------------------------------------------------
     def _fill(self, p, props, creating):
         for k, v in props.items():
-            if k == "albedo":
+            if k == "albedo" and isinstance(v, (int, float)):
+                p.n_albedo = 1
+                p.albedo[0] = float(v)
+            elif k == "albedo":
                 a = np.atleast_1d(np.asarray(v, dtype=np.float32)).ravel()
                 if a.size not in (1, 3, 11):
                     raise SunskyError(_capi.SSK_ERR_INVALID, "albedo needs 1, 3 (RGB) or 11 (spectral) values")
