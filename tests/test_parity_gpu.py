@@ -207,6 +207,61 @@ def test_pdf_integrates_to_one(ssk):
             assert abs(integral - 1) < 2e-3, integral
 
 
+def test_chi2_sampling_matches_pdf_like_sampling_test(ssk):
+    """sunsky-testing/sampling_test.py:47-58 (mi.chi2.ChiSquareTest, SphericalDomain, res 216, ires 32, alpha 0.01) on
+    the configs[2] emitter (t=6, a=0.5, eta=50.2 deg, sky only) with 2^26 samples: the histogram of sampled
+    directions over (phi, cos theta) against pdf_direction integrated per cell with composite Simpson."""
+    import torch
+    from scipy.stats import chi2 as chi2_dist
+    e = emitters.make(ssk, "cfg3_rgb_sky", g=emitters.golden("cfg3_rgb_sky"))
+    res_y, res_x, ires = 216, 432, 32
+    n = 1 << 26
+    gen = torch.Generator(device="cuda"); gen.manual_seed(2024)
+    hist = torch.zeros(res_y * res_x, dtype=torch.float64, device="cuda")
+    for _ in range(4):                                             # 4 batches of 2^24 keep the footprint small
+        u = torch.rand((2, n // 4), device="cuda", generator=gen)
+        d, _, _ = e.sample_direction(u)
+        assert int((d[2] < 0).sum()) == 0
+        phi = torch.atan2(d[1].double(), d[0].double())
+        ix = ((phi + np.pi) / (2 * np.pi) * res_x).long().clamp_(0, res_x - 1)
+        iy = ((d[2].double() + 1) / 2 * res_y).long().clamp_(0, res_y - 1)
+        hist += torch.bincount(iy * res_x + ix, minlength=res_y * res_x).double()
+        del u, d, phi, ix, iy
+    # expected counts: pdf over the domain (d omega = d phi d cos theta), composite Simpson with `ires` intervals per cell
+    def simpson(m):
+        w = torch.ones(m + 1, dtype=torch.float64, device="cuda"); w[1:-1:2] = 4; w[2:-1:2] = 2
+        return w / 3
+    expected = torch.zeros(res_y, res_x, dtype=torch.float64, device="cuda")
+    wy, wx = simpson(ires), simpson(ires)
+    hy, hx = 2.0 / res_y / ires, 2 * np.pi / res_x / ires
+    rows = 8                                                       # cell rows per batch
+    for y0 in range(res_y // 2, res_y, rows):                      # the lower hemisphere has zero density
+        cz = -1 + (torch.arange(y0 * ires, (y0 + rows) * ires + 1, device="cuda", dtype=torch.float64)) * hy
+        ph = -np.pi + torch.arange(res_x * ires + 1, device="cuda", dtype=torch.float64) * hx
+        CZ, PH = torch.meshgrid(cz, ph, indexing="ij")
+        st = torch.sqrt((1 - CZ * CZ).clamp_min(0))
+        dirs = torch.stack([st * torch.cos(PH), st * torch.sin(PH), CZ]).reshape(3, -1).float().contiguous()
+        pdf = e.pdf_direction(dirs).double().reshape(CZ.shape)
+        # per-cell Simpson: windows of ires + 1 nodes sharing their border nodes
+        py = pdf.unfold(0, ires + 1, ires)                         # (rows, nx, ires+1)
+        pyx = py.unfold(1, ires + 1, ires)                         # (rows, res_x, ires+1 [y], ires+1 [x])
+        expected[y0:y0 + rows] = torch.einsum("rcyx,y,x->rc", pyx, wy, wx) * hy * hx
+        del CZ, PH, st, dirs, pdf, py, pyx
+    total = float(expected.sum())
+    assert abs(total - 1) < 2e-3, total                            # the density integrates to one
+    exp_counts = (expected.reshape(-1) * n)
+    obs = hist
+    small = exp_counts < 5                                         # pool low-expectation cells (mi.chi2 does the same)
+    stat = float((((obs - exp_counts) ** 2) / exp_counts.clamp_min(1e-300))[~small].sum())
+    dof = int((~small).sum()) - 1
+    if bool(small.any()):
+        eo, oo = float(exp_counts[small].sum()), float(obs[small].sum())
+        if eo > 0:
+            stat += (oo - eo) ** 2 / eo; dof += 1
+    p_value = float(chi2_dist.sf(stat, dof))
+    assert p_value >= 0.01, f"chi2 = {stat:.1f}, dof = {dof}, p = {p_value:.3e}"
+
+
 # ---- arithmetic shortcuts ------------------------------------------------------------------------------
 
 def test_division_by_constant_is_ieee(ssk):
