@@ -227,26 +227,25 @@ def test_chi2_sampling_matches_pdf_like_sampling_test(ssk):
         iy = ((d[2].double() + 1) / 2 * res_y).long().clamp_(0, res_y - 1)
         hist += torch.bincount(iy * res_x + ix, minlength=res_y * res_x).double()
         del u, d, phi, ix, iy
-    # expected counts: pdf over the domain (d omega = d phi d cos theta), composite Simpson with `ires` intervals per cell
-    def simpson(m):
-        w = torch.ones(m + 1, dtype=torch.float64, device="cuda"); w[1:-1:2] = 4; w[2:-1:2] = 2
-        return w / 3
+    # expected counts: the density integrated over each (phi, cos theta) cell. Integrated in theta, where
+    # pdf * sin(theta) is the smooth mixture itself (in cos theta the 1 / sin(theta) factor is singular at the zenith
+    # row), with the composite midpoint rule, `ires` nodes per cell and dimension (mi.chi2 uses `ires` trapezoid nodes)
     expected = torch.zeros(res_y, res_x, dtype=torch.float64, device="cuda")
-    wy, wx = simpson(ires), simpson(ires)
-    hy, hx = 2.0 / res_y / ires, 2 * np.pi / res_x / ires
-    rows = 8                                                       # cell rows per batch
+    hx = 2 * np.pi / res_x / ires
+    ph = -np.pi + (torch.arange(res_x * ires, device="cuda", dtype=torch.float64) + 0.5) * hx
+    rows = 12                                                      # cell rows per batch (divides res_y / 2)
     for y0 in range(res_y // 2, res_y, rows):                      # the lower hemisphere has zero density
-        cz = -1 + (torch.arange(y0 * ires, (y0 + rows) * ires + 1, device="cuda", dtype=torch.float64)) * hy
-        ph = -np.pi + torch.arange(res_x * ires + 1, device="cuda", dtype=torch.float64) * hx
-        CZ, PH = torch.meshgrid(cz, ph, indexing="ij")
-        st = torch.sqrt((1 - CZ * CZ).clamp_min(0))
-        dirs = torch.stack([st * torch.cos(PH), st * torch.sin(PH), CZ]).reshape(3, -1).float().contiguous()
-        pdf = e.pdf_direction(dirs).double().reshape(CZ.shape)
-        # per-cell Simpson: windows of ires + 1 nodes sharing their border nodes
-        py = pdf.unfold(0, ires + 1, ires)                         # (rows, nx, ires+1)
-        pyx = py.unfold(1, ires + 1, ires)                         # (rows, res_x, ires+1 [y], ires+1 [x])
-        expected[y0:y0 + rows] = torch.einsum("rcyx,y,x->rc", pyx, wy, wx) * hy * hx
-        del CZ, PH, st, dirs, pdf, py, pyx
+        edges = -1 + torch.arange(y0, y0 + rows + 1, device="cuda", dtype=torch.float64) * (2.0 / res_y)
+        th_edges = torch.acos(edges.clamp(-1, 1))                  # decreasing in cos theta
+        th_hi, th_lo = th_edges[:-1], th_edges[1:]
+        hth = (th_hi - th_lo) / ires                               # (rows,)
+        th = th_lo[:, None] + (torch.arange(ires, device="cuda", dtype=torch.float64) + 0.5)[None, :] * hth[:, None]
+        TH = th.reshape(-1)[:, None].expand(-1, ph.numel()); PH = ph[None, :].expand(TH.shape[0], -1)
+        st = torch.sin(TH)
+        dirs = torch.stack([st * torch.cos(PH), st * torch.sin(PH), torch.cos(TH)]).reshape(3, -1).float().contiguous()
+        f = e.pdf_direction(dirs).double().reshape(rows, ires, res_x, ires) * st.reshape(rows, ires, res_x, ires)
+        expected[y0:y0 + rows] = f.sum(dim=(1, 3)) * hth[:, None] * hx
+        del TH, PH, st, dirs, f
     total = float(expected.sum())
     assert abs(total - 1) < 2e-3, total                            # the density integrates to one
     exp_counts = (expected.reshape(-1) * n)
