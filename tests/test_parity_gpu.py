@@ -98,6 +98,27 @@ def test_empty_and_tiny_batches(ssk):
         assert common.bit_equal(e.eval(-g["wo"][:, 600:600 + n]), g["eval"][:, 600:600 + n])
         d, pdf, w = e.sample_direction(g["u"][:, :n])
         assert common.bit_equal(d, g["s_d"][:, :n]) and common.bit_equal(w, g["s_weight"][:, :n])
+    # ragged tails of every kernel family, both arithmetic modes, RGB and spectral: n around the 2-, 4- and
+    # 512-sample (sorted tile) granularities, at an offset that also misaligns the sliced planes' start
+    import torch
+    for name in ("cfg3_rgb_sunsky", "cfg3_spec_sunsky"):
+        g = emitters.golden(name)
+        for arith in ("exact", "fast"):
+            e = emitters.make(ssk, name, g=g, arith=arith)
+            e.set_scene(*common.SCENE_BBOX)
+            wav = g["wav"] if e.spectral else None
+            full_d, full_pdf, full_w = e.sample_direction(g["u"], None, wav)
+            full_o, full_rd, full_rwav, full_rw = e.sample_ray(g["wl_sample"], g["s2"], g["u"])
+            assert e.sample_ray(g["wl_sample"][:0], g["s2"][:, :0], g["u"][:, :0])[0].shape == (3, 0)
+            for n in (1, 2, 511, 513, 1025):
+                for off in (0, 1):
+                    sl = slice(off, off + n)
+                    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+                    d, pdf, w = e.sample_direction(t(g["u"])[:, sl], None, None if wav is None else t(wav)[:, sl])
+                    assert common.bit_equal(d.cpu().numpy(), full_d[:, sl]) and common.bit_equal(w.cpu().numpy(), full_w[:, sl])
+                    assert common.bit_equal(pdf.cpu().numpy(), full_pdf[sl])
+                    o, rd, rwav, rw = e.sample_ray(t(g["wl_sample"])[sl], t(g["s2"])[:, sl], t(g["u"])[:, sl])
+                    assert common.bit_equal(o.cpu().numpy(), full_o[:, sl]) and common.bit_equal(rw.cpu().numpy(), full_rw[:, sl])
 
 
 def test_update_and_set_scene_reach_the_device(ssk):
