@@ -42,7 +42,8 @@ constexpr int kThreads = 256;
 #endif
 #ifndef SSK_EVAL_PREFETCH
 #define SSK_EVAL_PREFETCH 1      /* FAST spectral eval: measured 54.5 (pipelined loads, 3 CTAs/SM, 85 regs) vs 50.5 Gevals/s; */
-                                 /* with 4 CTAs/SM (64 regs) the prefetched values spill and the gain is lost; L1 prefetch: none */
+                                 /* with 4 CTAs/SM (64 regs) the prefetched values spill and the gain is lost; a non-binding       */
+                                 /* prefetch.global.L1 of the next iteration instead measured no gain (profiles/r1_summary.md)  */
 #endif
 #ifndef SSK_SPECX_MINB
 #define SSK_SPECX_MINB 1
@@ -104,8 +105,6 @@ template <int R> __device__ __forceinline__ void setk(float v[4], int k, float x
     if (R == 1) { v[0] = x; return; }
     v[0] = k == 0 ? x : v[0]; v[1] = k == 1 ? x : v[1]; v[2] = k == 2 ? x : v[2]; v[3] = k == 3 ? x : v[3];
 }
-
-__device__ __forceinline__ void prefetch_l1(const float *p) { asm volatile("prefetch.global.L1 [%0];" :: "l"(p)); }
 
 struct Planes3 { const float *x, *y, *z; };
 struct Planes4 { const float *a, *b, *c, *d; };
@@ -204,12 +203,6 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
     }
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
         float x[4], y[4], z[4], w0[4], w1[4], w2[4], w3[4], o0[4], o1[4], o2[4], o3[4];
-        if (R == 1 && SSK_EVAL_PREFETCH == 2 && i + stride < n) {
-            // non-binding L1 prefetch of the next grid-stride iteration's 7 input lines: no registers, no scoreboard
-            const size_t j = i + stride;
-            prefetch_l1(in.x + j); prefetch_l1(in.y + j); prefetch_l1(in.z + j);
-            prefetch_l1(wav.a + j); prefetch_l1(wav.b + j); prefetch_l1(wav.c + j); prefetch_l1(wav.d + j);
-        }
         loadr<R>(in.x, i, n, x); loadr<R>(in.y, i, n, y); loadr<R>(in.z, i, n, z);
         loadr<R>(wav.a, i, n, w0); loadr<R>(wav.b, i, n, w1); loadr<R>(wav.c, i, n, w2); loadr<R>(wav.d, i, n, w3);
 #pragma unroll 1

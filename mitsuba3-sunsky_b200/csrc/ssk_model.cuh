@@ -964,25 +964,11 @@ template <int A> SSK_HD RaySample sample_ray_geom(const HotBlock &U, const HotBl
     return r;
 }
 
-// Optional out-of-line copies of the two largest duplicated transcendentals of the sampler. The sampling kernels
-// exceed the 32 KB instruction-cache level (ncu: no_instruction is their top stall), but the duplicates are only
-// ~6 % of the 56 KB body (IEEE divisions and square roots of the exact sampler are the bulk), and the calls cost
-// more than the fetches they save.
-#ifndef SSK_SAMPLE_CALLS
-#define SSK_SAMPLE_CALLS 0      /* measured on B200: calls 35.2 vs inlined 35.6 Gsamples/s (sky only) -- kept inlined */
-#endif
-SSK_COLD float4 dsincos_2_call(float2 x) { float2 s, c; dsincos_2(x, s, c); return make_float4(s.x, s.y, c.x, c.y); }
-SSK_COLD float2 derfinv_2_call(float2 x) { return derfinv_2(x); }
-SSK_HD void dsincos_2s(float2 x, float2 &s, float2 &c) {
-    if (SSK_SAMPLE_CALLS) { float4 r = dsincos_2_call(x); s = f2(r.x, r.y); c = f2(r.z, r.w); } else dsincos_2(x, s, c);
-}
-SSK_HD float2 derfinv_2s(float2 x) { return SSK_SAMPLE_CALLS ? derfinv_2_call(x) : derfinv_2(x); }
-
 // ---- two samples per thread: sample_direction ------------------------------------------------------------
 SSK_HD Vec3p sphdir_p(float2 theta, float2 phi) {
     float2 st, ct, sp, cp;
-    dsincos_2s(theta, st, ct);
-    dsincos_2s(phi, sp, cp);
+    dsincos_2(theta, st, ct);
+    dsincos_2(phi, sp, cp);
     return { mul2(cp, st), mul2(sp, st), ct };
 }
 /// sample_sky for two samples (see sample_sky)
@@ -993,8 +979,8 @@ SSK_HD Vec3p sample_sky_p(const HotBlock &U, const HotBlock &S, float2 u0, float
            sy = lerp2(f2(S.g_cdf_a_theta[i0], S.g_cdf_a_theta[i1]), f2(S.g_cdf_b_theta[i0], S.g_cdf_b_theta[i1]), u1);
     sx = f2(fmaxf(fminf(sx.x, SSK_ONE_MINUS_EPSILON), SSK_EPSILON), fmaxf(fminf(sx.y, SSK_ONE_MINUS_EPSILON), SSK_EPSILON));
     sy = f2(fmaxf(fminf(sy.x, SSK_ONE_MINUS_EPSILON), SSK_EPSILON), fmaxf(fminf(sy.y, SSK_ONE_MINUS_EPSILON), SSK_EPSILON));
-    float2 ex = mul2s(derfinv_2s(add2x(mul2s(sx, 2.f), splat2(-1.f))), SSK_SQRT_TWO),
-           ey = mul2s(derfinv_2s(add2x(mul2s(sy, 2.f), splat2(-1.f))), SSK_SQRT_TWO);
+    float2 ex = mul2s(derfinv_2(add2x(mul2s(sx, 2.f), splat2(-1.f))), SSK_SQRT_TWO),
+           ey = mul2s(derfinv_2(add2x(mul2s(sy, 2.f), splat2(-1.f))), SSK_SQRT_TWO);
     float2 phi = add2x(mul2(ex, f2(S.g_sigma_phi[i0], S.g_sigma_phi[i1])), f2(S.g_mu_phi[i0], S.g_mu_phi[i1])),
            theta = add2x(mul2(ey, f2(S.g_sigma_theta[i0], S.g_sigma_theta[i1])), f2(S.g_mu_theta[i0], S.g_mu_theta[i1]));
     phi = add2s(phi, U.sun_phi_shift);
@@ -1012,7 +998,7 @@ SSK_HD Vec3p sample_sun_p(const HotBlock &P, float2 u0, float2 u1) {
     phi = sel2(q0, q1, alt, phi);
     phi = sel2(z0, z1, f2(0.f, 0.f), phi);
     float2 s, c;
-    dsincos_2s(phi, s, c);
+    dsincos_2(phi, s, c);
     float2 px = mul2(r, c), py = mul2(r, s);
     float2 pn = fma2(py, py, mul2(px, px));
     float2 z = add2x(mul2s(add2(splat2(1.f), neg2(pn)), P.one_minus_cos_cutoff), splat2(P.cos_cutoff));
