@@ -148,6 +148,16 @@ int ssk_sample_direction_device(const ssk_ctx *ctx, const float *const u[2], con
                                 const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
                                 float *const weight[4], float *const p[3], float *dist, void *stream);
 
+/* Forward derivative of eval() along a tangent of the Differentiable parameters `turbidity` and `albedo`
+ * (src/emitters/sunsky.cpp:222-225; sunsky-testing/traversal_test.py:94-144 drives it with dr.forward_from):
+ *   out = d eval / d turbidity * d_turbidity + sum_c d eval / d albedo[c] * d_albedo[c]
+ * d_albedo has 0, 1 (same tangent for every channel) or n_channels (3 RGB / 11 spectral bins) entries. Planes as
+ * ssk_eval_device. The derivative is the one the reference's AD sees: the interpolated state is piecewise linear
+ * in both parameters and the sampling weight / TGMM are not part of eval(). Calls on one context must be ordered
+ * on `stream` (the context owns one tangent block). */
+int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo,
+                        const float *const wi[3], const float *const wav[4], size_t n, float *const out[4], void *stream);
+
 /* sample_wavelengths(si, sample) (src/emitters/sunsky.cpp:463-480).
  *   spectral: wavelengths[k] = ContinuousDistribution::sample_pdf(sample_shifted<4>(sample)[k]) over the emitter's
  *   mean sun+sky spectrum on [360, 720] nm (include/mitsuba/core/distr_1d.h:468-502, core/math.h:408-431), and

@@ -43,6 +43,7 @@ struct ssk_ctx {
     int device = -1;
     int mode = SSK_MODE_RGB;
     EmitterBlock *d_block = nullptr;
+    mutable TangentBlock *d_tangent = nullptr;       // eval_jvp: lazily allocated, rewritten by every call
     int sm_count = 0;
     mutable Staging st;
 };
@@ -683,6 +684,7 @@ void ssk_destroy(ssk_ctx *ctx) {
             if (ctx->st.dev[i]) cudaFree(ctx->st.dev[i]);
         }
         if (ctx->d_block) cudaFree(ctx->d_block);
+        if (ctx->d_tangent) cudaFree(ctx->d_tangent);
     }
     delete ctx;
 }
@@ -873,6 +875,44 @@ int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const
         float *od = want_dist ? dout[o++] : nullptr;
         return launch_sample(ctx, din, has_p ? dp : nullptr, spectral ? dw : nullptr, m, dout, dout[3], wq,
                              want_p ? op : nullptr, od, s);
+    });
+}
+
+int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo,
+                        const float *const wi[3], const float *const wav[4], size_t n, float *const out[4], void *stream) {
+    if (int rc = need_device(ctx)) return rc;
+    const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
+    const int C = spectral ? 4 : 3;
+    if (n_d_albedo != 0 && n_d_albedo != 1 && n_d_albedo != ctx->E.n_channels)
+        return fail(SSK_ERR_INVALID, "d_albedo needs 0, 1 or n_channels (3 RGB / 11 spectral) entries");
+    if (n_d_albedo && !d_albedo) return fail(SSK_ERR_INVALID, "null d_albedo");
+    if (n == 0) return SSK_OK;                     // empty batches carry null planes
+    if (!wi || !out || !wi[0] || !wi[1] || !wi[2]) return fail(SSK_ERR_INVALID, "null direction / output planes");
+    for (int c = 0; c < C; ++c) if (!out[c]) return fail(SSK_ERR_INVALID, "null output plane");
+    if (spectral && (!wav || !wav[0] || !wav[1] || !wav[2] || !wav[3]))
+        return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
+    return guarded([&]() -> int {
+        cudaStream_t s = (cudaStream_t) stream;
+        TangentBlock T;
+        state_tangent(ctx->E, d_turbidity, d_albedo, n_d_albedo, T);
+        if (!ctx->d_tangent) SSK_CUDA(cudaMalloc(&ctx->d_tangent, sizeof(TangentBlock)));
+        // pageable source: the copy is staged before the call returns, so the stack block may go out of scope
+        SSK_CUDA(cudaMemcpyAsync(ctx->d_tangent, &T, sizeof(T), cudaMemcpyHostToDevice, s));
+        Planes3 i3 = { wi[0], wi[1], wi[2] };
+        Planes4 w4 = { nullptr, nullptr, nullptr, nullptr };
+        if (spectral) w4 = { wav[0], wav[1], wav[2], wav[3] };
+        OutPlanes4 o4 = { out[0], out[1], out[2], spectral ? out[3] : nullptr };
+        int grid = 1;
+        if (spectral) {
+            if (int rc = occupancy_grid(ctx, eval_jvp_kernel<true>, n, &grid, 1)) return rc;
+            eval_jvp_kernel<true><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_tangent, i3, w4, o4, n);
+        } else {
+            if (int rc = occupancy_grid(ctx, eval_jvp_kernel<false>, n, &grid, 1)) return rc;
+            eval_jvp_kernel<false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_tangent, i3, w4, o4, n);
+        }
+        g_launches++;
+        SSK_CUDA(cudaGetLastError());
+        return SSK_OK;
     });
 }
 

@@ -319,4 +319,46 @@ void estimate_sky_sun_ratio(HostEmitter &E, const float sky_rad[11], const float
     }
 }
 
+/// State tangent for the direction (d_turbidity, d_albedo[]): the interpolated state is linear in turbidity inside a
+/// slab [t, t+1] and linear in each channel's albedo (sunsky.h:157-231 for the sky, :403-419 for the sun), so the
+/// exact derivative is a difference of states rebuilt at the slab ends / at albedo 0 and 1.
+void state_tangent(const HostEmitter &E, float d_turbidity, const float *d_albedo, int n_d_albedo, TangentBlock &T) {
+    memset(&T, 0, sizeof(T));
+    const int C = E.n_channels;
+    auto rebuilt = [&](float turbidity, float albedo) {
+        HostEmitter H = E;
+        ssk_params p = E.params;
+        if (turbidity > 0.f) p.turbidity = turbidity;
+        if (albedo >= 0.f) { p.n_albedo = 1; p.albedo[0] = albedo; }
+        build_emitter_pre(H, p, false);
+        return H;
+    };
+    auto axpy = [&](float w, const HostEmitter &hi, const HostEmitter &lo, int c0, int c1) {
+        for (int c = c0; c < c1; ++c) {
+            for (int k = 0; k < kSkyParams; ++k) T.sky_params[k][c] += w * (hi.block.sky_params[k][c] - lo.block.sky_params[k][c]);
+            T.sky_rad[c] += w * (hi.block.sky_rad[c] - lo.block.sky_rad[c]);
+        }
+    };
+    if (d_turbidity != 0.f) {
+        // slab [floor(t), floor(t) + 1]; reads above turbidity 10 are masked to zero (sunsky.h:176-186, :403-419)
+        float t = fminf(fmaxf(E.params.turbidity, 1.f), 10.f), t_lo = floorf(t);
+        HostEmitter lo = rebuilt(t_lo, -1.f), hi = lo;
+        if (t_lo < 10.f) hi = rebuilt(t_lo + 1.f, -1.f);
+        else {                                     // both tables read 0 above the last slab
+            memset(hi.block.sky_params, 0, sizeof(hi.block.sky_params));
+            memset(hi.block.sky_rad, 0, sizeof(hi.block.sky_rad));
+            memset(hi.block.sun_rad, 0, sizeof(hi.block.sun_rad));
+        }
+        axpy(d_turbidity, hi, lo, 0, C);
+        for (size_t i = 0; i < sizeof(T.sun_rad) / sizeof(float); ++i)
+            T.sun_rad[i] += d_turbidity * (hi.block.sun_rad[i] - lo.block.sun_rad[i]);
+    }
+    bool any = false;
+    for (int c = 0; c < n_d_albedo; ++c) any = any || d_albedo[c] != 0.f;
+    if (any) {
+        HostEmitter a0 = rebuilt(-1.f, 0.f), a1 = rebuilt(-1.f, 1.f);
+        for (int c = 0; c < C; ++c) axpy(n_d_albedo == 1 ? d_albedo[0] : d_albedo[c], a1, a0, c, c + 1);
+    }
+}
+
 } // namespace ssk

@@ -530,6 +530,27 @@ setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int
     if (lane == 0) partial[blockIdx.x] = acc;
 }
 
+// ---- forward derivative of eval (turbidity / albedo tangents) ----------------------------------------------
+template <bool Spectral>
+__global__ void __launch_bounds__(kThreads)
+eval_jvp_kernel(const __grid_constant__ HotBlock U, const TangentBlock *__restrict__ tangent, Planes3 in, Planes4 wav,
+                OutPlanes4 out, size_t n) {
+    const TangentBlock &T = *tangent;              // 14 KB, L1 / L2 resident; indexed per channel
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        Vec3 wi = { __ldcs(in.x + i), __ldcs(in.y + i), __ldcs(in.z + i) };
+        float o[4] = { 0.f, 0.f, 0.f, 0.f };
+        if (Spectral) {
+            const float wl[4] = { __ldcs(wav.a + i), __ldcs(wav.b + i), __ldcs(wav.c + i), __ldcs(wav.d + i) };
+            eval_spec_jvp(U, T, wi, wl, o);
+            __stcs(out.d + i, o[3]);
+        } else {
+            eval_rgb_jvp(U, T, wi, o);
+        }
+        __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]);
+    }
+}
+
 // ---- sample_wavelengths / sample_ray -------------------------------------------------------------------
 /// sample_wavelengths, spectral (sunsky.cpp:463-473): one ray per thread; 4 planes in (wi, sample), 8 planes out
 template <int A>

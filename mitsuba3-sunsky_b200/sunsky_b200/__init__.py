@@ -307,6 +307,29 @@ class SunskyEmitter:
         return (d, pdf, wgt, op, dist) if want_p else (d, pdf, wgt)
 
 
+    def eval_jvp(self, wi, wavelengths=None, d_turbidity=0.0, d_albedo=None):
+        """Forward derivative of eval() along (d_turbidity, d_albedo): what dr.forward_from(params['turbidity'] /
+        params['albedo']) gives on plugin.eval(si) (sunsky.cpp:222-225, sunsky-testing/traversal_test.py:94-144).
+        d_albedo: None, a scalar, or one tangent per channel (3 RGB / 11 spectral bins). Device tensors only."""
+        import torch
+        if not _is_torch(wi):
+            raise TypeError("eval_jvp takes CUDA tensors (float32, plane-major)")
+        d_pp, wi = _pp_t(wi, 3, "wi")
+        n = wi.shape[1]
+        w_pp = None
+        if self.spectral:
+            if wavelengths is None:
+                raise ValueError("spectral mode needs wavelengths of shape (4, n)")
+            w_pp, wavelengths = _pp_t(wavelengths, 4, "wavelengths")
+            if wavelengths.shape[1] != n:
+                raise ValueError("wavelengths: expected (4, n)")
+        da = np.zeros(0, np.float32) if d_albedo is None else np.ascontiguousarray(d_albedo, dtype=np.float32).reshape(-1)
+        out = torch.empty((self.channels, n), dtype=torch.float32, device=wi.device)
+        o_pp, _ = _pp_t(out, self.channels, "out")
+        _check(self._L.ssk_eval_jvp_device(self._ctx, float(d_turbidity), da.ctypes.data_as(_capi.FP) if da.size else None,
+                                           int(da.size), d_pp, w_pp, n, o_pp, self._stream()))
+        return out
+
     def sample_wavelengths(self, wi, sample=None):
         """Emitter.sample_wavelengths(si, sample) (sunsky.cpp:463-480). wi: (3, n); sample: (n,) in [0, 1).
         Spectral: returns (wavelengths (4, n), weight (4, n) = eval / pdf). RGB: (None, eval (3, n))."""

@@ -42,6 +42,18 @@ void hostdbg_eval(void *h, size_t n, const float *wi, const float *wav, float *o
         }
     }
 }
+void hostdbg_eval_jvp(void *h, float dt, const float *da, int nda, size_t n, const float *wi, const float *wav, float *out) {
+    HostEmitter &E = *(HostEmitter *) h;
+    static TangentBlock T;
+    state_tangent(E, dt, da, nda, T);
+    for (size_t i = 0; i < n; ++i) {
+        Vec3 v = { wi[i], wi[n + i], wi[2 * n + i] };
+        float o[4];
+        if (E.spectral) { float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }; eval_spec_jvp(E.block, T, v, w, o); }
+        else eval_rgb_jvp(E.block, T, v, o);
+        for (int c = 0; c < (E.spectral ? 4 : 3); ++c) out[c * n + i] = o[c];
+    }
+}
 void hostdbg_pdf(void *h, size_t n, const float *d, float *pdf) {
     HostEmitter &E = *(HostEmitter *) h;
     if (getenv("HOSTDBG_PAIR")) {

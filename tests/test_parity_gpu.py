@@ -506,6 +506,63 @@ def test_sample_wavelengths_density_integrates_to_one(ssk):
     assert np.abs(hist - want).max() < 6 * np.sqrt(want.max())
 
 
+# ---- forward derivatives ---------------------------------------------------------------
+# parity unpinned: the reference's derivative comes from Dr.Jit's AD, which cannot run here; the check is central
+# finite differences of our own EXACT eval (itself bit-identical to the reference's), tolerance 2e-3 of the largest
+# derivative, which is what a step of 1/64 and fp32 radiance allow.
+
+@pytest.mark.parametrize("spectral", [False, True])
+def test_eval_jvp_matches_finite_differences(ssk, spectral):
+    import torch
+    import sunsky_b200.sweep as sw
+    rng = np.random.default_rng(11)
+    n, n_sun, h = 4096, 512, 1.0 / 64
+    sun = np.asarray(sw.sun_direction(40.0), dtype=np.float32)
+    nch = 11 if spectral else 3
+    alb = np.linspace(0.2, 0.6, nch).astype(np.float32)
+    wo = common.hemisphere_dirs(n, rng)
+    near = sun[:, None] + 0.002 * rng.standard_normal((3, n_sun)).astype(np.float32)     # inside the 0.27 deg disc
+    wo[:, :n_sun] = near / np.linalg.norm(near, axis=0)
+    wi = torch.from_numpy(np.ascontiguousarray(-wo)).cuda()
+    wav = torch.from_numpy((300 + 440 * rng.random((4, n), dtype=np.float32)).astype(np.float32)).cuda() if spectral else None
+    mk = lambda t, a: ssk.SunskyEmitter(spectral=spectral, turbidity=t, albedo=a, sun_direction=sun, arith="exact")
+    ev = lambda e: e.eval(wi, wav).double().cpu().numpy()
+
+    def check(jvp, fd, what):
+        for part, sl in (("sky", slice(n_sun, None)), ("sun", slice(0, n_sun))):
+            scale = np.abs(fd[:, sl]).max()
+            assert scale > 0
+            err = np.abs(jvp[:, sl] - fd[:, sl]).max() / scale
+            assert err < 2e-3, f"{what} {part}: {err:.2e}"
+
+    for t in (3.25, 1.5, 9.5):
+        e = mk(t, alb)
+        j = e.eval_jvp(wi, wav, d_turbidity=1.0).double().cpu().numpy()
+        check(j, (ev(mk(t + h, alb)) - ev(mk(t - h, alb))) / (2 * h), f"turbidity {t}")
+        da = rng.uniform(-1, 1, nch).astype(np.float32)
+        j = e.eval_jvp(wi, wav, d_albedo=da).double().cpu().numpy()
+        fd = (ev(mk(t, alb + h * da)) - ev(mk(t, alb - h * da))) / (2 * h)
+        sl = slice(n_sun, None)                  # albedo does not reach the sun table; its FD there is rounding noise
+        assert np.abs(j[:, sl] - fd[:, sl]).max() / np.abs(fd[:, sl]).max() < 2e-3
+        # linearity in the tangent, scalar albedo tangent == the same value on every channel
+        both = e.eval_jvp(wi, wav, d_turbidity=0.5, d_albedo=da).double().cpu().numpy()
+        jt = e.eval_jvp(wi, wav, d_turbidity=0.5).double().cpu().numpy()
+        assert np.abs(both - (jt + j)).max() <= 1e-5 * max(np.abs(both).max(), 1.0)
+        assert torch.equal(e.eval_jvp(wi, wav, d_albedo=0.5), e.eval_jvp(wi, wav, d_albedo=[0.5] * nch))
+    # integer turbidity: the derivative is the right-hand one (slab [t, t+1]), as AD through floor() gives
+    e = mk(6.0, alb)
+    j = e.eval_jvp(wi, wav, d_turbidity=1.0).double().cpu().numpy()
+    fd = (ev(mk(6.0 + h, alb)) - ev(e)) / h
+    assert np.abs(j[:, n_sun:] - fd[:, n_sun:]).max() / np.abs(fd[:, n_sun:]).max() < 3e-2
+    # below the horizon and outside the wavelength range: 0, like eval
+    down = torch.from_numpy(np.ascontiguousarray(wo[:, :64])).cuda()       # wi pointing up = direction below horizon
+    z = e.eval_jvp(down, wav[:, :64].contiguous() if spectral else None, d_turbidity=1.0)
+    assert float(z.abs().max()) == 0.0
+    with pytest.raises(ssk.SunskyError):
+        e.eval_jvp(wi, wav, d_albedo=[0.1, 0.2])
+    assert e.eval_jvp(wi[:, :0].contiguous(), wav[:, :0].contiguous() if spectral else None, d_turbidity=1.0).shape[1] == 0
+
+
 # ---- environment maps and sweeps (BASELINE configs[3], configs[4]) ----------------------------------------
 
 @pytest.mark.parametrize("spectral", [False, True])
