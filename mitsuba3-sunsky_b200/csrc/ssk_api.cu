@@ -304,9 +304,31 @@ bool sample_planes_aligned8(const SampleArgs &a) {
     for (const void *q : ps) acc |= reinterpret_cast<uintptr_t>(q);
     return (acc & 7u) == 0;
 }
+/// spectral sample_direction as two kernels (see weight_spec_kernel): sampler pass (technique-sorted when both
+/// techniques are in play), then eval / pdf
+template <int A>
+int launch_sample_two_pass(const ssk_ctx *ctx, const SampleArgs &a, size_t n, bool sorted, cudaStream_t s) {
+    int grid = 1;
+    if (sorted) {
+        if (int rc = occupancy_grid(ctx, sample_sorted_kernel<A, false, false>, n, &grid, 2)) return rc;
+        sample_sorted_kernel<A, false, false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    } else {
+        if (int rc = occupancy_grid(ctx, sample_pair_kernel<A, false, false>, n, &grid, 2)) return rc;
+        sample_pair_kernel<A, false, false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    }
+    if (int rc = occupancy_grid(ctx, weight_spec_kernel<A>, n, &grid, 1)) return rc;
+    weight_spec_kernel<A><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    g_launches++;
+    return SSK_OK;
+}
 template <int A>
 int launch_sample_a(const ssk_ctx *ctx, bool spectral, bool vec, const SampleArgs &a, size_t n, cudaStream_t s) {
     (void) vec;
+    static const bool fused = getenv("SSK_SAMPLE_FUSED") != nullptr, two_pass_nosort = getenv("SSK_SAMPLE_2P_NOSORT") != nullptr;
+    if (spectral && !fused && !getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a)) {
+        const float w2 = ctx->E.block.sky_w;
+        return launch_sample_two_pass<A>(ctx, a, n, w2 > 0.f && w2 < 1.f && !two_pass_nosort, s);
+    }
     // both techniques in play (0 < w < 1): technique-sorted tiles; one technique only: plain pairs
     static const bool no_sort = getenv("SSK_SAMPLE_NOSORT") != nullptr;
     const float w = ctx->E.block.sky_w;

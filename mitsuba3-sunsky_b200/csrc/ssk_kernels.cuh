@@ -319,7 +319,9 @@ pdf_pair_kernel(const __grid_constant__ HotBlock U, Planes3 in, float *__restric
 }
 
 /// sample_direction, two samples per thread (see sample_kernel)
-template <int A, bool Spectral>
+/// Weight = false: first pass of the two-pass spectral path (direction, pdf and the `active` flag in q0; the
+/// weight comes from weight_spec_kernel)
+template <int A, bool Spectral, bool Weight = true>
 __global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
 sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
@@ -332,8 +334,10 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
         DirSampleP s = sample_dir_p<A>(U, S, ld2(a.u0, i, two, 0.5f), ld2(a.u1, i, two, 0.5f));
         st2(a.dx, i, two, s.d_world.x); st2(a.dy, i, two, s.d_world.y); st2(a.dz, i, two, s.d_world.z);
         st2(a.pdf, i, two, s.pdf);
+        if (!Weight) st2(a.q0, i, two, f2(s.active0 ? 1.f : 0.f, s.active1 ? 1.f : 0.f));
         // eval(si) with si.wi = -d (sunsky.cpp:430-438)
         float2 e[4];
+        if (Weight) {
         if (Spectral) {
             float2 w0 = ld2(a.w0, i, two, 0.f), w1 = ld2(a.w1, i, two, 0.f), w2 = ld2(a.w2, i, two, 0.f), w3 = ld2(a.w3, i, two, 0.f);
             float ea[4], eb[4];
@@ -354,6 +358,7 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
             w = f2((fabsf(w.x) < INFINITY) ? w.x : 0.f, (fabsf(w.y) < INFINITY) ? w.y : 0.f);
             st2(c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3, i, two, w);
         }
+        }
         // bounding-sphere bookkeeping (sunsky.cpp:415-421)
         if (a.ox || a.dist) {
             float2 px = f2(0.f, 0.f), py = px, pz = px;
@@ -366,6 +371,45 @@ sample_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
                 st2(a.ox, i, two, fma2(s.d_world.x, dd, px)); st2(a.oy, i, two, fma2(s.d_world.y, dd, py));
                 st2(a.oz, i, two, fma2(s.d_world.z, dd, pz));
             }
+        }
+    }
+}
+
+// ---- spectral sample_direction, second pass -------------------------------------------------------------
+// The fused spectral kernels carry the sampler AND the 4-wavelength evaluation in one 73-112 KB body and stall on
+// instruction fetch. Two kernels that each fit the instruction caches do the same arithmetic per sample: the first
+// pass writes d, pdf and the sampler's `active` flag (in weight plane 0), this one evaluates eval(wi = -d) / pdf.
+template <int A>
+__global__ void __launch_bounds__(kThreads, A == kFast ? SSK_SPECF_MINB : SSK_SPECX_MINB)
+weight_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
+    stage_block(&S, A == kFast ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    float nx = 0.f, ny = 0.f, nz = 0.f, np = 1.f, nf = 0.f, na = 0.f, nb = 0.f, nc = 0.f, nd = 0.f;
+    if (i < n) {
+        nx = __ldcs(a.dx + i); ny = __ldcs(a.dy + i); nz = __ldcs(a.dz + i); np = __ldcs(a.pdf + i); nf = __ldcs(a.q0 + i);
+        na = __ldcs(a.w0 + i); nb = __ldcs(a.w1 + i); nc = __ldcs(a.w2 + i); nd = __ldcs(a.w3 + i);
+    }
+    for (; i < n; i += stride) {
+        const Vec3 wi = { -nx, -ny, -nz };
+        const float wl[4] = { na, nb, nc, nd }, pdf = np;
+        const bool active = nf != 0.f;
+        float o[4];
+        const size_t j = i + stride;
+        if (j < n) {
+            nx = __ldcs(a.dx + j); ny = __ldcs(a.dy + j); nz = __ldcs(a.dz + j); np = __ldcs(a.pdf + j); nf = __ldcs(a.q0 + j);
+            na = __ldcs(a.w0 + j); nb = __ldcs(a.w1 + j); nc = __ldcs(a.w2 + j); nd = __ldcs(a.w3 + j);
+        }
+        eval_spec<A>(U, S, pairs, sun_rad, wi, wl, active, o);
+        const float inv_pdf = A == kFast ? hw_rcp(pdf) : fdiv(1.f, pdf);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float w = o[c] * inv_pdf;
+            w = (fabsf(w) < INFINITY) ? w : 0.f;
+            __stcs((c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3) + i, w);
         }
     }
 }
@@ -386,7 +430,7 @@ __device__ __forceinline__ void gst2(float *p, size_t ia, size_t ib, bool two, f
     __stcs(p + ia, v.x);
     if (two) __stcs(p + ib, v.y);
 }
-template <int A, bool Spectral>
+template <int A, bool Spectral, bool Weight = true>
 __global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
 sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
@@ -435,7 +479,9 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
             DirSampleP s = sample_dir_p<A>(U, S, f2(tu0[la], two ? tu0[lb] : 0.5f), f2(tu1[la], two ? tu1[lb] : 0.5f));
             gst2(a.dx, ia, ib, two, s.d_world.x); gst2(a.dy, ia, ib, two, s.d_world.y); gst2(a.dz, ia, ib, two, s.d_world.z);
             gst2(a.pdf, ia, ib, two, s.pdf);
+            if (!Weight) gst2(a.q0, ia, ib, two, f2(s.active0 ? 1.f : 0.f, s.active1 ? 1.f : 0.f));
             float2 e[4];
+            if (Weight) {
             if (Spectral) {
                 float2 w0 = gld2(a.w0, ia, ib, two, 0.f), w1 = gld2(a.w1, ia, ib, two, 0.f), w2 = gld2(a.w2, ia, ib, two, 0.f),
                        w3 = gld2(a.w3, ia, ib, two, 0.f);
@@ -455,6 +501,7 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
                 float2 w = mul2(e[c], inv_pdf);
                 w = f2((fabsf(w.x) < INFINITY) ? w.x : 0.f, (fabsf(w.y) < INFINITY) ? w.y : 0.f);
                 gst2(c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3, ia, ib, two, w);
+            }
             }
             if (a.ox || a.dist) {          // bounding-sphere bookkeeping (sunsky.cpp:415-421), as sample_pair_kernel
                 float2 px = f2(0.f, 0.f), py = px, pz = px;

@@ -41,6 +41,7 @@ def main():
     es, er = ssk.SunskyEmitter(spectral=True, **kw), ssk.SunskyEmitter(spectral=False, **kw)
     ss, sr = ssk.SunskyEmitter(spectral=True, **kw3), ssk.SunskyEmitter(spectral=False, **kw3)
     sky = ssk.SunskyEmitter(spectral=False, sun_scale=0.0, **kw3)
+    sky_s = ssk.SunskyEmitter(spectral=True, sun_scale=0.0, **kw3)
     runs = {
         "eval_spec": lambda: es.eval(wi, wav),
         "eval_rgb": lambda: er.eval(wi),
@@ -48,6 +49,7 @@ def main():
         "sample_rgb": lambda: sr.sample_direction(u),
         "sample_sky": lambda: sky.sample_direction(u),
         "sample_spec": lambda: ss.sample_direction(u, None, wav),
+        "sample_spec_sky": lambda: sky_s.sample_direction(u, None, wav),
         "envmap": lambda: ssk.envmaps([er], 4096, 2048),
         "envmap_spec": lambda: ssk.envmaps([es], 4096, 2048, (440.0, 520.0, 600.0, 680.0)),
         "wavelengths": lambda: es.sample_wavelengths(wi, u2),
