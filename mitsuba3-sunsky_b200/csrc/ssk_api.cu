@@ -415,6 +415,15 @@ int launch_sample_wavelengths(const ssk_ctx *ctx, const float *const wi[3], cons
 template <int A, bool Spectral>
 int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStream_t s) {
     int grid = 1;
+    static const bool fused = getenv("SSK_SAMPLE_FUSED") != nullptr;
+    if (Spectral && !fused) {                      // two kernels, see weight_spec_kernel
+        if (int rc = occupancy_grid(ctx, sample_ray_kernel<A, false, false>, n, &grid, 1)) return rc;
+        sample_ray_kernel<A, false, false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+        if (int rc = occupancy_grid(ctx, ray_weight_spec_kernel<A>, n, &grid, 1)) return rc;
+        ray_weight_spec_kernel<A><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+        g_launches++;
+        return SSK_OK;
+    }
     if (int rc = occupancy_grid(ctx, sample_ray_kernel<A, Spectral>, n, &grid, 1)) return rc;
     sample_ray_kernel<A, Spectral><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
     return SSK_OK;

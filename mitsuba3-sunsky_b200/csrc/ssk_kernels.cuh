@@ -627,7 +627,8 @@ struct RayArgs {
 };
 
 /// sample_ray, fused (sunsky.cpp:354-397): origin disc -> technique -> direction -> pdf -> wavelengths -> eval -> weight
-template <int A, bool Spectral>
+/// Weight = false: first pass of the two-pass spectral path (origin, direction, `active` in q0, pdf in q1)
+template <int A, bool Spectral, bool Weight = true>
 __global__ void __launch_bounds__(kThreads, 3)
 sample_ray_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, RayArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
@@ -639,6 +640,7 @@ sample_ray_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__rest
         RaySample r = sample_ray_geom<A>(U, S, __ldcs(a.s2x + i), __ldcs(a.s2y + i), __ldcs(a.s3x + i), __ldcs(a.s3y + i));
         __stcs(a.ox + i, r.origin.x); __stcs(a.oy + i, r.origin.y); __stcs(a.oz + i, r.origin.z);
         __stcs(a.dx + i, r.d_world.x); __stcs(a.dy + i, r.d_world.y); __stcs(a.dz + i, r.d_world.z);
+        if (!Weight) { __stcs(a.q0 + i, r.active ? 1.f : 0.f); __stcs(a.q1 + i, r.pdf); continue; }
         float e[4];
         if (Spectral) {
             float w[4];
@@ -653,6 +655,32 @@ sample_ray_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__rest
         for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
             float w = e[c] * inv_pdf;
             __stcs((c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3) + i, (fabsf(w) < INFINITY) ? w : 0.f);
+        }
+    }
+}
+
+/// spectral sample_ray, second pass (see weight_spec_kernel): wavelengths, eval and weight = eval / pdf for the rays
+/// the first pass generated
+template <int A>
+__global__ void __launch_bounds__(kThreads, 3)
+ray_weight_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, RayArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
+    stage_block(&S, A == kFast ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const size_t stride = (size_t) gridDim.x * blockDim.x;
+    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const Vec3 d = { __ldcs(a.dx + i), __ldcs(a.dy + i), __ldcs(a.dz + i) };
+        const bool active = __ldcs(a.q0 + i) != 0.f;
+        const float pdf = __ldcs(a.q1 + i);
+        float w[4], e[4];
+        sample_wavelengths_spec<A>(U, S, pairs, sun_rad, d, __ldcs(a.wl_sample + i), active, w, e);
+        __stcs(a.w0 + i, w[0]); __stcs(a.w1 + i, w[1]); __stcs(a.w2 + i, w[2]); __stcs(a.w3 + i, w[3]);
+        const float inv_pdf = A == kFast ? hw_rcp(pdf) : fdiv(1.f, pdf);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            float q = e[c] * inv_pdf;
+            __stcs((c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3) + i, (fabsf(q) < INFINITY) ? q : 0.f);
         }
     }
 }

@@ -7,3 +7,8 @@ for A in fast exact; do
   echo "== two-pass unsorted $A"; SSK_SAMPLE_2P_NOSORT=1 python profiles/prof_driver.py --kernels $K --reps 30 --arith $A
   echo "== fused $A"; SSK_SAMPLE_FUSED=1 python profiles/prof_driver.py --kernels $K --reps 30 --arith $A
 done 2>&1 | tee gpurun_out/r1_twopass_ab.log
+# spectral sample_ray: fused vs geometry pass + wavelength/weight pass
+for A in fast exact; do
+  echo "== ray two-pass $A"; python profiles/prof_driver.py --kernels ray_spec --reps 30 --arith $A
+  echo "== ray fused $A"; SSK_SAMPLE_FUSED=1 python profiles/prof_driver.py --kernels ray_spec --reps 30 --arith $A
+done 2>&1 | tee -a gpurun_out/r1_twopass_ab.log
