@@ -316,8 +316,13 @@ int launch_sample_two_pass(const ssk_ctx *ctx, const SampleArgs &a, size_t n, bo
         if (int rc = occupancy_grid(ctx, sample_pair_kernel<A, false, false>, n, &grid, 2)) return rc;
         sample_pair_kernel<A, false, false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
     }
-    if (int rc = occupancy_grid(ctx, weight_spec_kernel<A>, n, &grid, 1)) return rc;
-    weight_spec_kernel<A><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    if (sorted) {                                  // same tiles, same slot order as the first pass
+        if (int rc = occupancy_grid(ctx, weight_spec_sorted_kernel<A>, n, &grid, 2)) return rc;
+        weight_spec_sorted_kernel<A><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    } else {
+        if (int rc = occupancy_grid(ctx, weight_spec_kernel<A>, n, &grid, 1)) return rc;
+        weight_spec_kernel<A><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);
+    }
     g_launches++;
     return SSK_OK;
 }
