@@ -939,13 +939,14 @@ int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_al
         if (spectral) w4 = { wav[0], wav[1], wav[2], wav[3] };
         OutPlanes4 o4 = { out[0], out[1], out[2], spectral ? out[3] : nullptr };
         int grid = 1;
-        if (spectral) {
-            if (int rc = occupancy_grid(ctx, eval_jvp_kernel<true>, n, &grid, 1)) return rc;
-            eval_jvp_kernel<true><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_tangent, i3, w4, o4, n);
-        } else {
-            if (int rc = occupancy_grid(ctx, eval_jvp_kernel<false>, n, &grid, 1)) return rc;
-            eval_jvp_kernel<false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_tangent, i3, w4, o4, n);
-        }
+        auto launch = [&](auto kernel) -> int {
+            if (int rc = occupancy_grid(ctx, kernel, n, &grid, 1)) return rc;
+            kernel<<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_tangent, i3, w4, o4, n);
+            return SSK_OK;
+        };
+        int rc = fast(ctx) ? (spectral ? launch(eval_jvp_kernel<kFast, true>) : launch(eval_jvp_kernel<kFast, false>))
+                           : (spectral ? launch(eval_jvp_kernel<kExact, true>) : launch(eval_jvp_kernel<kExact, false>));
+        if (rc) return rc;
         g_launches++;
         SSK_CUDA(cudaGetLastError());
         return SSK_OK;

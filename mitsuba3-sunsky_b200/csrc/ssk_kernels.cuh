@@ -625,7 +625,7 @@ setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int
 }
 
 // ---- forward derivative of eval (turbidity / albedo tangents) ----------------------------------------------
-template <bool Spectral>
+template <int A, bool Spectral>
 __global__ void __launch_bounds__(kThreads)
 eval_jvp_kernel(const __grid_constant__ HotBlock U, const TangentBlock *__restrict__ tangent, Planes3 in, Planes4 wav,
                 OutPlanes4 out, size_t n) {
@@ -636,10 +636,10 @@ eval_jvp_kernel(const __grid_constant__ HotBlock U, const TangentBlock *__restri
         float o[4] = { 0.f, 0.f, 0.f, 0.f };
         if (Spectral) {
             const float wl[4] = { __ldcs(wav.a + i), __ldcs(wav.b + i), __ldcs(wav.c + i), __ldcs(wav.d + i) };
-            eval_spec_jvp(U, T, wi, wl, o);
+            eval_spec_jvp<A>(U, T, wi, wl, o);
             __stcs(out.d + i, o[3]);
         } else {
-            eval_rgb_jvp(U, T, wi, o);
+            eval_rgb_jvp<A>(U, T, wi, o);
         }
         __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]);
     }

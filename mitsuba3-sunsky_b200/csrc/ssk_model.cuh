@@ -836,26 +836,30 @@ struct TangentBlock {
     float sky_rad[kChanPad];
     float sun_rad[kSunSegments * 3 * 4 * kLd];
 };
-/// d render_sky(ch) for the state tangent T (product rule over sunsky.cpp:538-555)
-SSK_HD float render_sky_jvp(const HotBlock &P, const TangentBlock &T, int ch, const RayTerms &r) {
+/// d render_sky(ch) for the state tangent T (product rule over sunsky.cpp:538-555). A = kFast: MUFU ex2 / rsq /
+/// rcp for the transcendentals (the derivative has no bit-level reference to match)
+template <int A> SSK_HD float render_sky_jvp(const HotBlock &P, const TangentBlock &T, int ch, const RayTerms &r) {
     float A0 = P.sky_params[0][ch], A1 = P.sky_params[1][ch], A2 = P.sky_params[2][ch], A3 = P.sky_params[3][ch],
           A4 = P.sky_params[4][ch], A5 = P.sky_params[5][ch], A6 = P.sky_params[6][ch], A7 = P.sky_params[7][ch],
           A8 = P.sky_params[8][ch], L = P.sky_rad[ch];
     float d0 = T.sky_params[0][ch], d1 = T.sky_params[1][ch], d2 = T.sky_params[2][ch], d3 = T.sky_params[3][ch],
           d4 = T.sky_params[4][ch], d5 = T.sky_params[5][ch], d6 = T.sky_params[6][ch], d7 = T.sky_params[7][ch],
           d8 = T.sky_params[8][ch], dL = T.sky_rad[ch];
-    float e1 = dexp(A1 * r.inv_denom_c1);
+    constexpr float kLog2e = 1.44269504088896340736f;
+    float e1 = A == kFast ? hw_ex2(A1 * r.inv_denom_c1 * kLog2e) : dexp(A1 * r.inv_denom_c1);
     float c1 = 1.f + A0 * e1, dc1 = d0 * e1 + A0 * e1 * (d1 * r.inv_denom_c1);
     float arg = 1.f + A8 * A8 - 2.f * A8 * r.cos_gamma;
-    float chi = fdiv(r.one_plus_cg2, dpow15(arg));
-    float dchi = -1.5f * fdiv(chi, arg) * ((2.f * A8 - 2.f * r.cos_gamma) * d8);
-    float e4 = dexp(A4 * r.gamma);
+    float chi, chi_over_arg;
+    if (A == kFast) { float rs = hw_rsqrt(arg); chi = r.one_plus_cg2 * (rs * rs * rs); chi_over_arg = chi * (rs * rs); }
+    else { chi = fdiv(r.one_plus_cg2, dpow15(arg)); chi_over_arg = fdiv(chi, arg); }
+    float dchi = -1.5f * chi_over_arg * ((2.f * A8 - 2.f * r.cos_gamma) * d8);
+    float e4 = A == kFast ? hw_ex2(A4 * r.gamma * kLog2e) : dexp(A4 * r.gamma);
     float c2 = A2 + A3 * e4 + A5 * r.cos_gamma_sqr + A6 * chi + A7 * r.sqrt_cos_theta;
     float dc2 = d2 + d3 * e4 + A3 * e4 * (r.gamma * d4) + d5 * r.cos_gamma_sqr + d6 * chi + A6 * dchi + d7 * r.sqrt_cos_theta;
     return (dc1 * c2 + c1 * dc2) * L + c1 * c2 * dL;
 }
 /// d eval, RGB (mirrors eval_rgb; the sun term is linear in its table)
-SSK_HD void eval_rgb_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &wi, float out[3]) {
+template <int A> SSK_HD void eval_rgb_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &wi, float out[3]) {
     EvalGeom g = eval_geom<kExact>(U, wi, true);
     out[0] = out[1] = out[2] = 0.f;
     if (!g.active) return;
@@ -863,13 +867,13 @@ SSK_HD void eval_rgb_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &w
     SunSeg s = { 0, 0.f };
     if (g.hit_sun) { s = sun_segment(g.r.cos_theta); powers4(s.x, xk); powers6(cos_psi(U, g.r.gamma), cj); }
     for (int c = 0; c < 3; ++c) {
-        double res = (double) (U.sky_scale * render_sky_jvp(U, T, c, g.r));
+        double res = (double) (U.sky_scale * render_sky_jvp<A>(U, T, c, g.r));
         if (g.hit_sun) res += (double) (U.sun_scale * render_sun_rgb(T.sun_rad, c, s, xk, cj) * U.area_ratio) * 467.069280386;
         out[c] = (float) (res * (1.0 / 106.7502593994140625));
     }
 }
 /// d eval, spectral (mirrors eval_spec)
-SSK_HD void eval_spec_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &wi, const float wav[4], float out[4]) {
+template <int A> SSK_HD void eval_spec_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &wi, const float wav[4], float out[4]) {
     EvalGeom g = eval_geom<kExact>(U, wi, true);
     out[0] = out[1] = out[2] = out[3] = 0.f;
     if (!g.active) return;
@@ -880,7 +884,7 @@ SSK_HD void eval_spec_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &
         Bin b = wavelength_bin(wav[w]);
         if (!b.valid) continue;
         const int hi = b.lo + 1;                   // channel 11 is the zero pad (see HotBlock)
-        float d = U.sky_scale * lerp(render_sky_jvp(U, T, b.lo, g.r), render_sky_jvp(U, T, hi, g.r), b.f);
+        float d = U.sky_scale * lerp(render_sky_jvp<A>(U, T, b.lo, g.r), render_sky_jvp<A>(U, T, hi, g.r), b.f);
         if (g.hit_sun) {
             float lo_v = render_sun_spec(T.sun_rad, b.lo, s, xk), hi_v = hi < kMaxChannels ? render_sun_spec(T.sun_rad, hi, s, xk) : 0.f;
             d += U.sun_scale * lerp(lo_v, hi_v, b.f) * sun_ld(U, b.lo, hi, b.f, cj) * U.area_ratio;

@@ -55,6 +55,8 @@ def main():
         "wavelengths": lambda: es.sample_wavelengths(wi, u2),
         "ray_rgb": lambda: sr.sample_ray(None, u, u),
         "ray_spec": lambda: ss.sample_ray(u1, u, u),
+        "jvp_rgb": lambda: er.eval_jvp(wi, None, d_turbidity=1.0, d_albedo=0.5),
+        "jvp_spec": lambda: es.eval_jvp(wi, wav, d_turbidity=1.0, d_albedo=0.5),
     }
     if "setup" in args.kernels.split(","):
         import time
