@@ -108,10 +108,16 @@ public:
     }
 
     void fill_to_world() {
-        auto m = m_to_world.scalar().matrix;
+        // a Transform carries matrix AND inverse_transpose (transform.h:44-45); the reference's per-lane
+        // world -> local transform is m_to_world.value().inverse() = transpose(inverse_transpose) (:77-79),
+        // so hand the library exactly that inverse instead of letting it invert the matrix again
+        const auto &T = m_to_world.scalar();
         for (int r = 0; r < 4; ++r)
-            for (int c = 0; c < 4; ++c)
-                m_params.to_world[r * 4 + c] = m(r, c);
+            for (int c = 0; c < 4; ++c) {
+                m_params.to_world[r * 4 + c] = T.matrix(r, c);
+                m_params.to_local[r * 4 + c] = T.inverse_transpose(c, r);
+            }
+        m_params.flags |= SSK_FLAG_TO_LOCAL_GIVEN;
     }
 
     void traverse(TraversalCallback *cb) override {                                         // :220-240

@@ -40,6 +40,11 @@ extern "C" {
 
 /* ssk_params.flags */
 #define SSK_FLAG_SUN_DIR_NORMALIZED 1u  /* sun_direction is already unit length: use it verbatim */
+#define SSK_FLAG_TO_LOCAL_GIVEN     2u  /* to_local holds the inverse the caller's Transform4f carries
+                                           (include/mitsuba/core/transform.h:44-45, 59-62, 77-79: a Transform stores
+                                           matrix AND inverse_transpose, built analytically by rotate()/translate()/...);
+                                           without the flag the inverse is computed as Properties does for a to_world
+                                           property: fp64 cofactor inverse, rounded to fp32 */
 
 /* ssk_params.arith */
 #define SSK_ARITH_EXACT        0   /* replay the reference's op sequence (IEEE div/sqrt, CEPHES polynomials):
@@ -64,6 +69,7 @@ typedef struct ssk_params {
     float    to_world[16];                      /* row-major 4x4 affine, default identity */
     uint32_t flags;
     int32_t  arith;
+    float    to_local[16];                      /* row-major inverse of to_world; read only with SSK_FLAG_TO_LOCAL_GIVEN */
 } ssk_params;
 
 /* Interpolated per-emitter state, for parity checks against the reference's private members
@@ -89,6 +95,7 @@ typedef struct ssk_state {
     float   spectral_integral, spectral_normalization;
     float   area_ratio;
     int32_t sun_below_horizon;       /* the reference logs a warning in this case */
+    float   to_local[9];             /* row-major 3x3 linear part of m_to_world.inverse() as used per lane */
 } ssk_state;
 
 typedef struct ssk_ctx ssk_ctx;

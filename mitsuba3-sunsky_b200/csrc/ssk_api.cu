@@ -594,7 +594,7 @@ void ssk_params_default(ssk_params *p) {
     p->hour = 15.f; p->minute = 0.f; p->second = 0.f;
     p->sun_scale = 1.f; p->sky_scale = 1.f;
     p->sun_aperture_deg = (float) 0.5358;
-    for (int i = 0; i < 4; ++i) p->to_world[i * 5] = 1.f;
+    for (int i = 0; i < 4; ++i) p->to_world[i * 5] = p->to_local[i * 5] = 1.f;
     p->flags = 0; p->arith = SSK_ARITH_EXACT;
 }
 
@@ -754,6 +754,7 @@ int ssk_get_state(const ssk_ctx *ctx, ssk_state *s) {
     s->spectral_integral = E.spectral_integral; s->spectral_normalization = E.spectral_norm;
     s->area_ratio = E.area_ratio;
     s->sun_below_horizon = E.sun_below_horizon ? 1 : 0;
+    memcpy(s->to_local, E.block.to_local, sizeof(s->to_local));
     return SSK_OK;
 }
 

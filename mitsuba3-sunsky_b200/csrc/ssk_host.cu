@@ -34,15 +34,78 @@ void validate_params(const ssk_params &p, bool spectral) {
 static void mat3_from_4x4(const float *m16, float *m9) {
     for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) m9[r * 3 + c] = m16[r * 4 + c];
 }
-static bool invert3(const float *m, float *inv) {
-    double a = m[0], b = m[1], c = m[2], d = m[3], e = m[4], f = m[5], g = m[6], h = m[7], i = m[8];
-    double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+/// The inverse a `to_world` property carries in the reference. Properties stores transforms as
+/// Transform<Point<double, 4>> (include/mitsuba/core/properties.h:70), whose constructor computes
+/// dr::inverse_transpose in fp64 (transform.h:55-57); reading it back as ScalarTransform4f casts both matrices to
+/// fp32 (transform.h:64-67). This is drjit/matrix.h:440-500 (4 x 4 cofactor expansion on 4-wide packets) lane by
+/// lane in the same order, so the rounded result is the one the reference ends up with. `inv` = row-major inverse.
+namespace {
+struct V4 { double v[4]; };
+template <int A, int B, int C, int D> V4 shuf(const V4 &a) { return { { a.v[A], a.v[B], a.v[C], a.v[D] } }; }
+V4 vmul(const V4 &a, const V4 &b) { V4 r; for (int i = 0; i < 4; ++i) r.v[i] = a.v[i] * b.v[i]; return r; }
+V4 vfmadd(const V4 &a, const V4 &b, const V4 &c) { V4 r; for (int i = 0; i < 4; ++i) r.v[i] = fma(a.v[i], b.v[i], c.v[i]); return r; }
+V4 vfmsub(const V4 &a, const V4 &b, const V4 &c) { V4 r; for (int i = 0; i < 4; ++i) r.v[i] = fma(a.v[i], b.v[i], -c.v[i]); return r; }
+V4 vfnmadd(const V4 &a, const V4 &b, const V4 &c) { V4 r; for (int i = 0; i < 4; ++i) r.v[i] = fma(-a.v[i], b.v[i], c.v[i]); return r; }
+}
+static bool invert4_f64(const float *m16, float *inv16) {
+    V4 row0, row1, row2, row3;
+    for (int c = 0; c < 4; ++c) { row0.v[c] = m16[c]; row1.v[c] = m16[4 + c]; row2.v[c] = m16[8 + c]; row3.v[c] = m16[12 + c]; }
+    row1 = shuf<2, 3, 0, 1>(row1);
+    row3 = shuf<2, 3, 0, 1>(row3);
+    V4 temp, col0, col1, col2, col3;
+    temp = shuf<1, 0, 3, 2>(vmul(row2, row3));
+    col0 = vmul(row1, temp);
+    col1 = vmul(row0, temp);
+    temp = shuf<2, 3, 0, 1>(temp);
+    col0 = vfmsub(row1, temp, col0);
+    col1 = shuf<2, 3, 0, 1>(vfmsub(row0, temp, col1));
+
+    temp = shuf<1, 0, 3, 2>(vmul(row1, row2));
+    col0 = vfmadd(row3, temp, col0);
+    col3 = vmul(row0, temp);
+    temp = shuf<2, 3, 0, 1>(temp);
+    col0 = vfnmadd(row3, temp, col0);
+    col3 = shuf<2, 3, 0, 1>(vfmsub(row0, temp, col3));
+
+    temp = shuf<1, 0, 3, 2>(vmul(shuf<2, 3, 0, 1>(row1), row3));
+    row2 = shuf<2, 3, 0, 1>(row2);
+    col0 = vfmadd(row2, temp, col0);
+    col2 = vmul(row0, temp);
+    temp = shuf<2, 3, 0, 1>(temp);
+    col0 = vfnmadd(row2, temp, col0);
+    col2 = shuf<2, 3, 0, 1>(vfmsub(row0, temp, col2));
+
+    temp = shuf<1, 0, 3, 2>(vmul(row0, row1));
+    col2 = vfmadd(row3, temp, col2);
+    col3 = vfmsub(row2, temp, col3);
+    temp = shuf<2, 3, 0, 1>(temp);
+    col2 = vfmsub(row3, temp, col2);
+    col3 = vfnmadd(row2, temp, col3);
+
+    temp = shuf<1, 0, 3, 2>(vmul(row0, row3));
+    col1 = vfnmadd(row2, temp, col1);
+    col2 = vfmadd(row1, temp, col2);
+    temp = shuf<2, 3, 0, 1>(temp);
+    col1 = vfmadd(row2, temp, col1);
+    col2 = vfnmadd(row1, temp, col2);
+
+    temp = shuf<1, 0, 3, 2>(vmul(row0, row2));
+    col1 = vfmadd(row3, temp, col1);
+    col3 = vfnmadd(row1, temp, col3);
+    temp = shuf<2, 3, 0, 1>(temp);
+    col1 = vfnmadd(row3, temp, col1);
+    col3 = vfmadd(row1, temp, col3);
+
+    // dot() of two 4-wide double packets: sum(a * b) = (p0 + p2) + (p1 + p3) (drjit/packet_avx.h:738)
+    V4 pr = vmul(row0, col0);
+    double det = (pr.v[0] + pr.v[2]) + (pr.v[1] + pr.v[3]);
     if (det == 0.0 || !std::isfinite(det)) return false;
-    double r = 1.0 / det;
-    double o[9] = { (e * i - f * h) * r, (c * h - b * i) * r, (b * f - c * e) * r,
-                    (f * g - d * i) * r, (a * i - c * g) * r, (c * d - a * f) * r,
-                    (d * h - e * g) * r, (b * g - a * h) * r, (a * e - b * d) * r };
-    for (int k = 0; k < 9; ++k) inv[k] = (float) o[k];
+    double inv_det = 1.0 / det;
+    const V4 *cols[4] = { &col0, &col1, &col2, &col3 };
+    // cols[r] is row r of the inverse TRANSPOSE; the inverse itself is its transpose
+    for (int r = 0; r < 4; ++r)
+        for (int c = 0; c < 4; ++c)
+            inv16[c * 4 + r] = (float) (cols[r]->v[c] * inv_det);
     return true;
 }
 
@@ -71,7 +134,16 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
 
     // --- transforms
     mat3_from_4x4(p.to_world, B.to_world);
-    if (!invert3(B.to_world, B.to_local)) throw std::invalid_argument("to_world is not invertible");
+    if (p.flags & SSK_FLAG_TO_LOCAL_GIVEN) {
+        // the caller's Transform4f carries its own inverse (transform.h:59-62, 77-79): use it verbatim
+        mat3_from_4x4(p.to_local, B.to_local);
+        for (int i = 0; i < 9; ++i)
+            if (!std::isfinite(B.to_local[i])) throw std::invalid_argument("to_local is not finite");
+    } else {
+        float inv16[16];
+        if (!invert4_f64(p.to_world, inv16)) throw std::invalid_argument("to_world is not invertible");
+        mat3_from_4x4(inv16, B.to_local);
+    }
 
     // --- albedo per channel (extract_albedo, sunsky.cpp:956-978)
     float albedo[11];
@@ -90,9 +162,10 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
     } else {
         Vec3 v = { p.sun_direction[0], p.sun_direction[1], p.sun_direction[2] };
         if (!(p.flags & SSK_FLAG_SUN_DIR_NORMALIZED) && from_constructor) {
-            // dr::normalize on a scalar vector; the reference's SSE rsqrt path is CPU specific, so a
-            // caller that needs bit parity passes a unit vector and SSK_FLAG_SUN_DIR_NORMALIZED
-            float inv = 1.f / sqrtf(v.x * v.x + v.y * v.y + v.z * v.z);
+            // dr::normalize on a ScalarVector3f (sunsky.cpp:922): v * rsqrt(sum(v * v)); the 3-wide horizontal sum
+            // adds (x^2 + z^2) + y^2 (drjit/packet_sse42.h:1659-1666) and a scalar rsqrt is 1 / sqrt
+            // (drjit/array_utils.h:213-219)
+            float inv = 1.f / sqrtf((v.x * v.x + v.z * v.z) + v.y * v.y);
             v = { v.x * inv, v.y * inv, v.z * inv };
         }
         E.sun_dir_world = v;
@@ -108,6 +181,11 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
     B.sun_t[0] = ft.x; B.sun_t[1] = ft.y; B.sun_t[2] = ft.z;
     B.sun_phi_shift = E.sun_angles[0] - SSK_HALF_PI;
     const float eta = SSK_HALF_PI - E.sun_angles[1];
+    // A to_world that is not rigid leaves the local sun direction far from unit length and unit_angle_z returns NaN;
+    // the reference then dies in the TGMM weights (NaN fails `pmf >= 0`, distr_1d.h:221-222). Same failure, said earlier.
+    if (std::isnan(eta))
+        throw std::invalid_argument("local sun direction is not a unit vector (to_world must be a rigid transform): "
+                                    "DiscreteDistribution: entries must be non-negative!");
 
     // --- aperture-dependent constants
     B.cos_cutoff = dcos(E.half_aperture);
@@ -156,6 +234,9 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
     bool any_pos = false;
     for (int i = 0; i < kGauss; ++i) {
         E.pmf[i] = E.gaussians[i * 5 + 4];
+        // distr_1d.h:221-224 (a NaN weight -- local sun direction far from unit length under a sheared
+        // to_world -- fails the same test in the reference)
+        if (!(E.pmf[i] >= 0.f)) throw std::invalid_argument("DiscreteDistribution: entries must be non-negative!");
         any_pos |= E.pmf[i] > 0.f;
         acc = acc + E.pmf[i];
         E.cdf[i] = acc;

@@ -16,7 +16,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import (MODE_RGB, MODE_SPECTRAL, FLAG_SUN_DIR_NORMALIZED, ARITH_EXACT, ARITH_FAST, DATASET_DIR,
+from ._capi import (MODE_RGB, MODE_SPECTRAL, FLAG_SUN_DIR_NORMALIZED, FLAG_TO_LOCAL_GIVEN, ARITH_EXACT, ARITH_FAST, DATASET_DIR,
                     Params, State)
 
 __all__ = ["SunskyEmitter", "SunskyError", "sun_coordinates", "array_from_file", "array_to_file",
@@ -65,7 +65,7 @@ def _pp_t(t, k, name):
 
 
 _PARAM_KEYS = ("turbidity", "albedo", "sun_direction", "latitude", "longitude", "timezone", "year", "month",
-               "day", "hour", "minute", "second", "sun_scale", "sky_scale", "sun_aperture", "to_world")
+               "day", "hour", "minute", "second", "sun_scale", "sky_scale", "sun_aperture", "to_world", "to_local")
 
 
 class SunskyEmitter:
@@ -128,19 +128,25 @@ class SunskyEmitter:
                     p.sun_direction[i] = float(v[i])
             elif k == "sun_aperture":
                 p.sun_aperture_deg = float(v)
-            elif k == "to_world":
+            elif k in ("to_world", "to_local"):
+                # to_local: the inverse the caller's Transform4f carries (transform.h:44-45); without it the
+                # library inverts to_world the way a `to_world` property is inverted (fp64, rounded)
                 m = np.asarray(v, dtype=np.float32).reshape(16)
+                dst = p.to_world if k == "to_world" else p.to_local
                 for i in range(16):
-                    p.to_world[i] = float(m[i])
+                    dst[i] = float(m[i])
             elif k in ("year", "month", "day"):
                 setattr(p, k, int(v))
             else:
                 setattr(p, k, float(v))
         if creating and "sun_direction" not in props:
             p.use_record = 1
-        p.flags = FLAG_SUN_DIR_NORMALIZED if self._normalized else 0
-        p.arith = ARITH_FAST if self.arith == "fast" else ARITH_EXACT
         self._props.update(props)
+        if "to_world" in props and "to_local" not in props:
+            self._props.pop("to_local", None)          # a new to_world without its inverse: back to the computed one
+        p.flags = (FLAG_SUN_DIR_NORMALIZED if self._normalized else 0) | \
+                  (FLAG_TO_LOCAL_GIVEN if "to_local" in self._props else 0)
+        p.arith = ARITH_FAST if self.arith == "fast" else ARITH_EXACT
 
     def traverse(self):
         """Names and current values of the parameters `traverse()` exposes (sunsky.cpp:220-240)."""

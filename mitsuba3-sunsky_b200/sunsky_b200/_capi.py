@@ -11,6 +11,7 @@ DATASET_DIR = os.path.join(ROOT, "data", "resources", "sunsky", "datasets")
 SSK_OK, SSK_ERR_INVALID, SSK_ERR_IO, SSK_ERR_CUDA, SSK_ERR_UNSUPPORTED = 0, -1, -2, -3, -4
 MODE_RGB, MODE_SPECTRAL = 0, 1
 FLAG_SUN_DIR_NORMALIZED = 1
+FLAG_TO_LOCAL_GIVEN = 2
 ARITH_EXACT, ARITH_FAST = 0, 1
 
 
@@ -23,6 +24,7 @@ class Params(C.Structure):
         ("hour", C.c_float), ("minute", C.c_float), ("second", C.c_float),
         ("sun_scale", C.c_float), ("sky_scale", C.c_float), ("sun_aperture_deg", C.c_float),
         ("to_world", C.c_float * 16), ("flags", C.c_uint32), ("arith", C.c_int32),
+        ("to_local", C.c_float * 16),
     ]
 
 
@@ -37,7 +39,7 @@ class State(C.Structure):
         ("bsphere_center", C.c_float * 3), ("bsphere_radius", C.c_float),
         ("spectral_pdf", C.c_float * 10), ("spectral_cdf", C.c_float * 10),
         ("spectral_integral", C.c_float), ("spectral_normalization", C.c_float),
-        ("area_ratio", C.c_float), ("sun_below_horizon", C.c_int32),
+        ("area_ratio", C.c_float), ("sun_below_horizon", C.c_int32), ("to_local", C.c_float * 9),
     ]
 
 

@@ -129,6 +129,8 @@ struct ssk_ref_params {
     int32_t has_to_world;
     float to_world[16];        // row-major
     int32_t record_defaults;   // 1 -> leave every record field at the reference default except `hour`
+    int32_t has_to_local;      // 1 -> `to_local` is the inverse the Transform carries (a caller-built Transform4f,
+    float to_local[16];        //      transform.h:59-62); 0 -> dr::inverse_transpose in fp64 as Properties does
 };
 
 struct ssk_ref_state {
@@ -151,6 +153,7 @@ struct ssk_ref_state {
     float spectral_integral, spectral_normalization;
     int32_t n_spectral;
     int32_t flags;
+    float to_world[16], to_local[16];   // m_to_world.scalar().matrix and its carried inverse, row-major
 };
 
 } // extern "C"
@@ -201,7 +204,7 @@ Properties make_props(const ssk_ref_params &p, bool spectral) {
         props.set_float("second", p.second);
     }
     if (p.has_to_world)
-        props.set_matrix("to_world", p.to_world);
+        props.set_matrix("to_world", p.to_world, p.has_to_local ? p.to_local : nullptr);
     (void) spectral;
     return props;
 }
@@ -247,7 +250,7 @@ template <typename Float, typename Spectrum> struct RefImpl final : RefBase {
         if (p.n_albedo > 0)
             em->m_albedo = new Texture(std::vector<float>(p.albedo, p.albedo + p.n_albedo));
         if (p.has_to_world) {
-            Properties tmp; tmp.set_matrix("to_world", p.to_world);
+            Properties tmp; tmp.set_matrix("to_world", p.to_world, p.has_to_local ? p.to_local : nullptr);
             em->m_to_world = tmp.get<ScalarTransform4f>("to_world");
         }
         if (em->m_active_record) {
@@ -293,6 +296,14 @@ template <typename Float, typename Spectrum> struct RefImpl final : RefBase {
         s.bsphere_radius = sc(em->m_bsphere.radius);
         s.sun_half_aperture = em->m_sun_half_aperture;
         s.flags = (int32_t) em->m_flags;
+        {
+            const auto &T = em->m_to_world.scalar();
+            for (int r = 0; r < 4; ++r)
+                for (int c = 0; c < 4; ++c) {
+                    s.to_world[r * 4 + c] = T.matrix(r, c);
+                    s.to_local[r * 4 + c] = T.inverse_transpose(c, r);
+                }
+        }
         if constexpr (!IsRGB) {
             const auto &sd = em->m_spectral_distr;
             s.n_spectral = (int32_t) sd.pdf().size();
@@ -598,6 +609,19 @@ int ssk_ref_gauss_legendre(int n, float *nodes, float *weights) {
         auto [x, w] = quad::gauss_legendre<DynF>(n);
         for (int i = 0; i < n; ++i) { nodes[i] = x[i]; weights[i] = w[i]; }
     });
+}
+
+// dr::normalize on a ScalarVector3f, as init_from_props applies it to the sun_direction property (sunsky.cpp:922)
+void ssk_ref_normalize3(const float *in3, float *out3) {
+    using ScalarVector3f = Vector<float, 3>;
+    ScalarVector3f v = dr::normalize(ScalarVector3f(in3[0], in3[1], in3[2]));
+    for (int i = 0; i < 3; ++i) out3[i] = v[i];
+}
+// Transform<Point<double, 4>>(m) -> ScalarTransform4f: the inverse a to_world property ends up with, row-major
+void ssk_ref_invert4(const float *m16, float *inv16) {
+    Properties tmp; tmp.set_matrix("m", m16);
+    auto T = tmp.get<Transform<Point<float, 4>>>("m");
+    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) inv16[r * 4 + c] = T.inverse_transpose(c, r);
 }
 
 double ssk_ref_area_ratio_numerator() { return 1 - dr::cos(SUN_HALF_APERTURE); }

@@ -21,6 +21,7 @@ class RefParams(C.Structure):
         ("hour", C.c_float), ("minute", C.c_float), ("second", C.c_float),
         ("sun_scale", C.c_float), ("sky_scale", C.c_float), ("sun_aperture_deg", C.c_float),
         ("has_to_world", C.c_int32), ("to_world", C.c_float * 16), ("record_defaults", C.c_int32),
+        ("has_to_local", C.c_int32), ("to_local", C.c_float * 16),
     ]
 
 
@@ -36,6 +37,7 @@ class RefState(C.Structure):
         ("spectral_pdf", C.c_float * 10), ("spectral_cdf", C.c_float * 10),
         ("spectral_integral", C.c_float), ("spectral_normalization", C.c_float),
         ("n_spectral", C.c_int32), ("flags", C.c_int32),
+        ("to_world", C.c_float * 16), ("to_local", C.c_float * 16),
     ]
 
 
@@ -74,6 +76,8 @@ def lib():
         L.ssk_ref_area_ratio.restype = C.c_float
         L.ssk_ref_area_ratio.argtypes = [C.c_float]
         L.ssk_ref_set_resource_root.argtypes = [C.c_char_p]
+        L.ssk_ref_normalize3.argtypes = [FP, FP]
+        L.ssk_ref_invert4.argtypes = [FP, FP]
         for r in DEFAULT_ROOTS:
             if os.path.exists(os.path.join(r, "resources", "sunsky", "datasets", "tgmm_tables.bin")):
                 L.ssk_ref_set_resource_root(r.encode())
@@ -104,7 +108,7 @@ def math(op, x, y=None, flavour=1):
 
 
 def make_params(turbidity=3.0, albedo=None, sun_direction=None, record=None, hour=None, sun_scale=1.0,
-                sky_scale=1.0, sun_aperture=None, to_world=None):
+                sky_scale=1.0, sun_aperture=None, to_world=None, to_local=None):
     p = RefParams()
     p.turbidity = turbidity
     if albedo is None:
@@ -134,6 +138,11 @@ def make_params(turbidity=3.0, albedo=None, sun_direction=None, record=None, hou
         m = np.asarray(to_world, dtype=np.float32).reshape(16)
         for i in range(16):
             p.to_world[i] = m[i]
+    if to_local is not None:
+        p.has_to_local = 1
+        m = np.asarray(to_local, dtype=np.float32).reshape(16)
+        for i in range(16):
+            p.to_local[i] = m[i]
     return p
 
 
@@ -230,6 +239,20 @@ def sun_coordinates(year, month, day, hour, minute, second, latitude, longitude,
     if rc:
         raise RuntimeError(lib().ssk_ref_last_error().decode())
     return out
+
+
+def normalize3(v):
+    """dr::normalize(ScalarVector3f) as init_from_props applies it to `sun_direction` (sunsky.cpp:922)."""
+    a = _f32(v); out = np.empty(3, np.float32)
+    lib().ssk_ref_normalize3(_fp(a), _fp(out))
+    return out
+
+
+def invert4(m):
+    """The inverse a `to_world` property carries once read back as ScalarTransform4f (fp64 inverse, cast)."""
+    a = _f32(np.asarray(m, np.float32).reshape(16)); out = np.empty(16, np.float32)
+    lib().ssk_ref_invert4(_fp(a), _fp(out))
+    return out.reshape(4, 4)
 
 
 def pcg32_floats(n, stream_offset=0):

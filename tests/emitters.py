@@ -14,10 +14,6 @@ def make(ssk, name, device=0, g=None, **override):
     spectral, kw = common.CONFIGS[name]
     kw = dict(kw)
     kw.update(override)
-    normalized = False
-    if "sun_direction" in kw and g is not None:
-        # the reference normalises the property with an SSE rsqrt path that is CPU specific; hand our
-        # library the exact unit vector the reference ended up with
-        kw["sun_direction"] = [float(v) for v in g["state_sun_dir_world"]]
-        normalized = True
-    return ssk.SunskyEmitter(spectral=spectral, device=device, sun_direction_normalized=normalized, **kw)
+    # The raw property goes in, exactly as the golden generator handed it to the reference: the library
+    # normalises it with the reference's own op order (dr::normalize on a ScalarVector3f, sunsky.cpp:922).
+    return ssk.SunskyEmitter(spectral=spectral, device=device, **kw)

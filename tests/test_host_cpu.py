@@ -67,12 +67,13 @@ def test_state_against_live_reference(ssk, ref):
         for _ in range(4):
             t = float(rng.uniform(1, 10)); a = float(rng.uniform(0, 1))
             sd = common.sun_dir_from_elevation(float(rng.uniform(0.5, 89.5)), float(rng.uniform(-3, 3)))
+            scale = float(rng.uniform(0.1, 30.0))                 # the property need not be unit length
+            sd = [float(np.float32(v) * np.float32(scale)) for v in sd]
             r = ref.RefEmitter(spectral=spectral, flavour=1, turbidity=t, albedo=a, sun_direction=sd)
             rs = r.state()
-            e = ssk.SunskyEmitter(spectral=spectral, device=-1, sun_direction_normalized=True, turbidity=t, albedo=a,
-                                  sun_direction=list(rs.sun_dir_world))
+            e = ssk.SunskyEmitter(spectral=spectral, device=-1, turbidity=t, albedo=a, sun_direction=sd)
             s = e.state()
-            for f in ("gaussians", "cdf", "sun_angles", "frame_s", "frame_t"):
+            for f in ("sun_dir_world", "gaussians", "cdf", "sun_angles", "frame_s", "frame_t"):
                 assert common.bit_equal(np.array(getattr(s, f)), np.array(getattr(rs, f))), f
             assert common.bit_equal(np.array(s.sky_params[:s.n_channels * 9]), np.array(rs.sky_params[:s.n_channels * 9]))
             assert s.sky_sampling_w == rs.sky_sampling_w
@@ -120,6 +121,43 @@ def test_invalid_properties_match_reference(ssk, ref):
             ref.RefEmitter(spectral=False, flavour=0, **kw)
         with pytest.raises(ssk.SunskyError):
             ssk.SunskyEmitter(device=-1, **kw)
+
+
+def test_to_world_inverse_and_normalisation_match_reference(ssk, ref):
+    """Host state for rotated / scaled / sheared / translated to_world matrices and non-unit sun directions:
+    the inverse (fp64 cofactor expansion in the order of drjit/matrix.h:440-500, rounded to fp32 as
+    Properties -> ScalarTransform4f does) and dr::normalize(ScalarVector3f) are bit-identical to the reference's,
+    and so is everything derived from the local sun direction."""
+    rng = np.random.default_rng(17)
+    for it in range(40):
+        M = np.eye(4, dtype=np.float64)
+        if it % 2 == 0:                       # rotation x uniform scale + translation
+            q = rng.normal(size=4); q /= np.linalg.norm(q); w, x, y, z = q
+            R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                          [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                          [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+            M[:3, :3] = R * rng.uniform(0.3, 3.0)
+        else:                                 # general affine
+            M[:3, :3] = rng.normal(size=(3, 3))
+        M[:3, 3] = rng.normal(size=3) * 5
+        M = M.astype(np.float32)
+        sd = (rng.normal(size=3) * 10 ** rng.uniform(-2, 2)).astype(np.float32)
+        kw = dict(turbidity=3.5, albedo=0.4, sun_direction=list(sd), to_world=M)
+        try:
+            r = ref.RefEmitter(spectral=False, flavour=1, **kw)
+        except RuntimeError as err:           # sheared to_world: local sun direction not unit length -> NaN weights
+            assert "non-negative" in str(err)
+            with pytest.raises(ssk.SunskyError, match="non-negative"):
+                ssk.SunskyEmitter(spectral=False, device=-1, **kw)
+            continue
+        e = ssk.SunskyEmitter(spectral=False, device=-1, **kw)
+        rs, s = r.state(), e.state()
+        assert common.bit_equal(np.array(s.to_local).reshape(3, 3), ref.invert4(M)[:3, :3])
+        assert common.bit_equal(np.array(s.to_local).reshape(3, 3), np.array(rs.to_local).reshape(4, 4)[:3, :3])
+        assert common.bit_equal(np.array(s.sun_dir_world), ref.normalize3(sd))
+        for f in ("sun_dir_world", "sun_angles", "frame_s", "frame_t", "frame_n", "gaussians", "cdf"):
+            assert common.bit_equal(np.array(getattr(s, f)), np.array(getattr(rs, f))), (it, f)
+        assert common.bit_equal(np.array(s.sky_params[:27]), np.array(rs.sky_params[:27]))
 
 
 def test_update_is_parameters_changed(ssk):
