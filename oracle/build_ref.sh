@@ -25,7 +25,9 @@ test -s "$GEN/cie1931_tbl.inc"
 # 3. compile. -mfma + -ffp-contract=off: dr::fmadd is a hardware FMA, a*b+c is not contracted
 #    (what the LLVM backend emits: llvm.fma + plain fmul/fadd, no fast-math flags).
 CXX="${SSK_CXX:-/usr/bin/g++}"   # the system compiler: links libstdc++ dynamically (a static copy clashes with numpy/torch's)
-FLAGS="-std=c++17 -O2 -fPIC -shared -mavx2 -mfma -ffp-contract=off -fno-fast-math -w -pthread"
+# -fno-strict-aliasing: Dr.Jit requires it (ext/drjit/CMakeLists.txt:71 makes it an INTERFACE option of the drjit target);
+#    without it g++ -O2 miscompiles the scalar instantiation (the sky term of eval() comes out as 0)
+FLAGS="-std=c++17 -O2 -fPIC -shared -mavx2 -mfma -ffp-contract=off -fno-fast-math -fno-strict-aliasing -w -pthread"
 INC="-I $HERE/ref_shadow -I $GEN -I $GEN/include -I $REF -I $REF/include -I $REF/ext/drjit/include \
  -I $REF/ext/drjit/ext/drjit-core/include -I $REF/ext/drjit/ext/drjit-core/ext/nanothread/include \
  -I $REF/ext/tinyformat -I $REF/ext/fastfloat/include -I $REF/ext/nanobind/include"

@@ -1,0 +1,85 @@
+"""The oracle against the reference's own golden vectors (`-m "not gpu"`): the sky renders and the 80 sun spectra
+under resources/sunsky/test_data, at the tolerances of src/emitters/tests/test_sunsky.py.
+Also keeps the packed fixture honest: when the reference tree is present it is re-read and compared."""
+import os
+
+import numpy as np
+import pytest
+
+import reference_suite as rs
+
+
+@pytest.fixture(scope="module")
+def refdata():
+    return rs.load_refdata()
+
+
+def maker(ref, flavour):
+    return lambda spectral, **kw: ref.RefEmitter(spectral=spectral, flavour=flavour, **kw)
+
+
+@pytest.mark.parametrize("flavour", [0, 1])
+def test_oracle_reproduces_reference_sky_renders(ref, refdata, flavour):
+    for p in rs.RGB_CASES:                                              # test01, <= 0.017
+        assert rs.render_error(maker(ref, flavour), refdata, False, p, rs.rgb_key(p)) <= 0.017
+    for p in rs.SPEC_CASES:                                             # test02, <= 0.037
+        assert rs.render_error(maker(ref, flavour), refdata, True, p, rs.spec_key(p)) <= 0.037
+    assert rs.render_error(maker(ref, flavour), refdata, True, (np.radians(60), 4.2, rs.SPECIAL_ALBEDO),
+                           "sky_spectrum_special") <= 0.03             # test03
+
+
+def test_oracle_reproduces_reference_sun_spectra(ref, refdata):
+    err = rs.sun_spectrum_errors(maker(ref, 1), refdata)                # test04, <= 1e-2 each
+    assert err.max() <= 1e-2
+    assert err.max() <= 2e-3                                            # measured 1.63e-3 (fp32 sun polynomial)
+
+
+def test_packed_fixture_matches_the_reference_tree(refdata):
+    data = "/root/reference/resources/sunsky/test_data"
+    if not os.path.isdir(data):
+        pytest.skip("reference tree not present")
+    import exr_reader
+    import glob
+    files = sorted(glob.glob(os.path.join(data, "renders", "*.exr")))
+    assert len(files) == 7 and len(glob.glob(os.path.join(data, "spectrum", "*.spd"))) == 80
+    for f in files:
+        ch, names = exr_reader.read_exr(f)
+        order = ["R", "G", "B"] if set(names) == {"R", "G", "B"} else names
+        img = np.stack([ch[c] for c in order], axis=-1)
+        assert np.array_equal(img, refdata["render/" + os.path.splitext(os.path.basename(f))[0]])
+    t, eta, g = 5.5, np.linspace(1e-4, np.pi / 2 - 1e-4, 4)[1], np.linspace(0, rs.SUN_HALF_APERTURE_ANGLE - 1e-4, 4)[2]
+    rows = open(os.path.join(data, "spectrum", f"sun_spectrum_t{t:.1f}_eta{eta:.2f}_gamma{g:.3e}.spd")).read().split()
+    assert np.array_equal(np.array(rows[1::2], float), refdata["sun_spectra"][2, 1, 2])
+
+
+def test_pcg32_streams_match_the_reference():
+    """sunsky_b200.pcg32 (input generation for configs[1..2], test05) against dr::PCG32 (drjit/random.h)."""
+    import ref_oracle
+    if not ref_oracle.available():
+        pytest.skip("oracle/_ref not built")
+    from sunsky_b200 import pcg32
+    assert np.array_equal(pcg32.floats(50_000)[0].numpy(), ref_oracle.pcg32_floats(50_000))
+    assert np.array_equal(pcg32.floats(999, 1, 7_000_000_000)[0].numpy(), ref_oracle.pcg32_floats(999, 7_000_000_000))
+    pairs = pcg32.point2_pairs(1000).numpy()
+    flat = ref_oracle.pcg32_floats(2000)
+    assert np.array_equal(pairs[0], flat[0::2]) and np.array_equal(pairs[1], flat[1::2])
+
+
+@pytest.mark.parametrize("name", ["cfg1_rgb", "cfg2_spec", "cfg3_rgb_sunsky", "spec_alb11"])
+def test_scalar_and_array_flavours_agree(ref, name):
+    """Both arithmetic flavours of the oracle are the same formulas (they differ in erf's coefficient set, the
+    dot-product order and FMA use: SURVEY.md section 0.4), so they agree to a few ulp on well-conditioned lanes. Guards
+    the build recipe: without -fno-strict-aliasing (which Dr.Jit requires, ext/drjit/CMakeLists.txt:71) g++ -O2
+    miscompiled the scalar instantiation -- its sky term came out as 0 -- and round 1 timed that as the CPU arm."""
+    import common
+    import emitters
+    g = emitters.golden(name)
+    spectral, kw = common.CONFIGS[name]
+    wav = g["wav"] if spectral else None
+    a = ref.RefEmitter(spectral=spectral, flavour=0, **kw).eval(-g["wo"], wav)
+    b = g["eval"]
+    assert np.array_equal(a == 0, b == 0)                               # same lanes lit
+    nz = b != 0
+    rel = np.abs(a[nz] - b[nz]) / np.abs(b[nz])
+    assert np.median(rel) < 1e-6 and np.quantile(rel, 0.99) < 1e-4, (np.median(rel), rel.max())
+    assert np.array_equal(a, g["eval_scalar"])
