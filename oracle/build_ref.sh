@@ -27,9 +27,18 @@ test -s "$GEN/cie1931_tbl.inc"
 CXX="${SSK_CXX:-/usr/bin/g++}"   # the system compiler: links libstdc++ dynamically (a static copy clashes with numpy/torch's)
 # -fno-strict-aliasing: Dr.Jit requires it (ext/drjit/CMakeLists.txt:71 makes it an INTERFACE option of the drjit target);
 #    without it g++ -O2 miscompiles the scalar instantiation (the sky term of eval() comes out as 0)
-FLAGS="-std=c++17 -O2 -fPIC -shared -mavx2 -mfma -ffp-contract=off -fno-fast-math -fno-strict-aliasing -w -pthread"
+FLAGS="-std=c++17 -O3 -fPIC -shared -mfma -ffp-contract=off -fno-fast-math -fno-strict-aliasing -w -pthread"
 INC="-I $HERE/ref_shadow -I $GEN -I $GEN/include -I $REF -I $REF/include -I $REF/ext/drjit/include \
  -I $REF/ext/drjit/ext/drjit-core/include -I $REF/ext/drjit/ext/drjit-core/ext/nanothread/include \
  -I $REF/ext/tinyformat -I $REF/ext/fastfloat/include -I $REF/ext/nanobind/include"
-$CXX $FLAGS $INC "$HERE/ref_harness.cpp" -o "$OUT/libsunsky_ref.so"
-echo "built $OUT/libsunsky_ref.so"
+# Two ISA builds of the same harness (the library travels prebuilt to a GPU box whose host CPU is not known here):
+#   libsunsky_ref.so         AVX2 + FMA: runs anywhere the image runs; the PARITY oracle (flavours 0 and 1) and the
+#                            packet baseline on 8-wide packets
+#   libsunsky_ref_avx512.so  + AVX-512 F/VL/DQ/BW/CD: 16-wide packets for the timed CPU baseline; loaded only when
+#                            /proc/cpuinfo lists those features (oracle/ref_oracle.py)
+$CXX $FLAGS -mavx2 $INC "$HERE/ref_harness.cpp" -o "$OUT/libsunsky_ref.so" &
+P1=$!
+$CXX $FLAGS -mavx2 -mavx512f -mavx512vl -mavx512dq -mavx512bw -mavx512cd $INC "$HERE/ref_harness.cpp" -o "$OUT/libsunsky_ref_avx512.so" &
+P2=$!
+wait $P1; wait $P2
+echo "built $OUT/libsunsky_ref.so $OUT/libsunsky_ref_avx512.so"

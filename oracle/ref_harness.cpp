@@ -109,6 +109,62 @@ inline mitsuba::Spectrum<DynamicArray<float>, 11> sum_inner(const mitsuba::Spect
 #undef private
 #undef protected
 
+// ---- flavour 2: Float = dr::Packet<float, W>, the reference's query members on SIMD packets ----------------------
+// Stand-in for the speed of llvm_ad_*: the same member bodies (eval, sample_direction, pdf_direction, sample_ray,
+// sample_wavelengths: sunsky.cpp:303-480, 538-763) instantiated on AVX2 (W = 8) or AVX-512 (W = 16) packets, one
+// instruction per 8 / 16 lanes as the LLVM backend's vectorised kernels issue them. The constructor and
+// parameters_changed() are written for width-1 JIT arrays and do not instantiate on packets, so they are
+// explicitly specialised here: the state comes from a flavour-1 emitter built from the same properties. Packet
+// `rcp` is the hardware estimate plus one Newton step (drjit/packet_avx.h), so results sit within a few ulp of
+// flavour 1 instead of matching bit for bit: flavour 2 is the TIMED baseline, flavour 1 stays the parity target.
+#if defined(__AVX512F__)
+#  define SSK_REF_PACKET_WIDTH 16
+#else
+#  define SSK_REF_PACKET_WIDTH 8
+#endif
+namespace mitsuba {
+using PktF = drjit::Packet<float, SSK_REF_PACKET_WIDTH>;
+using ArrF = drjit::DynamicArray<float>;
+
+template <typename DstSpec, typename SrcSpec>
+void ssk_packet_state_from(SunskyEmitter<PktF, DstSpec> &d, const SunskyEmitter<ArrF, SrcSpec> &s) {
+    using Dst = SunskyEmitter<PktF, DstSpec>;
+    d.m_bsphere = typename Dst::BoundingSphere3f(typename Dst::ScalarPoint3f(0.f), 1.f);
+    d.m_turbidity = s.m_turbidity[0];
+    d.m_sky_sampling_w = s.m_sky_sampling_w[0];
+    d.m_sky_scale = s.m_sky_scale; d.m_sun_scale = s.m_sun_scale;
+    d.m_sun_half_aperture = s.m_sun_half_aperture;
+    d.m_active_record = s.m_active_record;
+    for (int i = 0; i < 3; ++i) {
+        d.m_sun_dir[i] = s.m_sun_dir[i][0];
+        d.m_local_sun_frame.s[i] = s.m_local_sun_frame.s[i][0];
+        d.m_local_sun_frame.t[i] = s.m_local_sun_frame.t[i][0];
+        d.m_local_sun_frame.n[i] = s.m_local_sun_frame.n[i][0];
+    }
+    d.m_sun_angles[0] = s.m_sun_angles[0][0]; d.m_sun_angles[1] = s.m_sun_angles[1][0];
+    d.m_sky_params = s.m_sky_params; d.m_sky_radiance = s.m_sky_radiance; d.m_sun_radiance = s.m_sun_radiance;
+    d.m_gaussians = s.m_gaussians; d.m_sun_ld = s.m_sun_ld;
+    d.m_gaussian_distr = DiscreteDistribution<PktF>(s.m_gaussian_distr.pmf());
+    if constexpr (is_spectral_v<DstSpec>) {
+        const Vector<float, 2> range = { WAVELENGTHS<float>[1], WAVELENGTHS<float>[NB_WAVELENGTHS - 1] };
+        d.m_spectral_distr = ContinuousDistribution<typename Dst::Wavelength>(range, s.m_spectral_distr.pdf());
+    }
+    d.m_flags = s.m_flags;
+}
+#define SSK_PACKET_SPECIALISE(DstSpec, SrcSpec)                                                                    \
+    template <> SunskyEmitter<PktF, DstSpec>::SunskyEmitter(const Properties &props) : Base(props) {              \
+        SunskyEmitter<ArrF, SrcSpec> src(props);                                                                   \
+        ssk_packet_state_from(*this, src);                                                                         \
+    }                                                                                                              \
+    template <> void SunskyEmitter<PktF, DstSpec>::parameters_changed(const std::vector<std::string> &) {          \
+        Throw("flavour 2 (packets) is a timing baseline: build a new emitter instead of updating one");            \
+    }                                                                                                              \
+    template <> void SunskyEmitter<PktF, DstSpec>::traverse(TraversalCallback *) { }
+#define SSK_COMMA ,
+SSK_PACKET_SPECIALISE(Color<PktF SSK_COMMA 3>, Color<ArrF SSK_COMMA 3>)
+SSK_PACKET_SPECIALISE(Spectrum<PktF SSK_COMMA 4>, Spectrum<ArrF SSK_COMMA 4>)
+} // namespace mitsuba
+
 namespace dr = drjit;
 using namespace mitsuba;
 
@@ -215,11 +271,19 @@ template <typename Float> struct lanes {
 
 // helpers to move between SoA float buffers and Float
 template <typename Float> Float load_f(const float *ptr, size_t off, size_t n) {
-    if constexpr (dr::is_array_v<Float>) return dr::load<Float>(ptr + off, n);
+    if constexpr (dr::is_packed_array_v<Float> && !dr::is_dynamic_array_v<Float>) {
+        if (n == Float::Size) return dr::load<Float>(ptr + off);
+        Float r = dr::zeros<Float>();                       // tail: zero-padded lanes
+        for (size_t i = 0; i < n; ++i) r[i] = ptr[off + i];
+        return r;
+    } else if constexpr (dr::is_array_v<Float>) return dr::load<Float>(ptr + off, n);
     else { (void) n; return ptr[off]; }
 }
 template <typename Float> void store_f(float *ptr, size_t off, size_t n, const Float &v) {
-    if constexpr (dr::is_array_v<Float>) {
+    if constexpr (dr::is_packed_array_v<Float> && !dr::is_dynamic_array_v<Float>) {
+        if (n == Float::Size) dr::store(ptr + off, v);
+        else for (size_t i = 0; i < n; ++i) ptr[off + i] = v[i];
+    } else if constexpr (dr::is_array_v<Float>) {
         if (v.size() == n) memcpy(ptr + off, v.data(), n * sizeof(float));
         else if (v.size() == 1) for (size_t i = 0; i < n; ++i) ptr[off + i] = v[0];
         else throw std::runtime_error("store_f: unexpected array size");
@@ -230,8 +294,9 @@ template <typename Float, typename Spectrum> struct RefImpl final : RefBase {
     using Emitter_ = SunskyEmitter<Float, Spectrum>;
     MI_IMPORT_TYPES(Scene, Texture)
     static constexpr bool IsArray = dr::is_array_v<Float>;
+    static constexpr bool IsPacket = dr::is_packed_array_v<Float> && !dr::is_dynamic_array_v<Float>;
     static constexpr bool IsRGB = is_rgb_v<Spectrum>;
-    static constexpr size_t Chunk = IsArray ? 16384 : 1;
+    static constexpr size_t Chunk = IsPacket ? dr::size_v<Float> : (IsArray ? 16384 : 1);
     static constexpr int C = IsRGB ? 3 : 4;
 
     std::unique_ptr<Emitter_> em;
@@ -446,6 +511,8 @@ void *ssk_ref_create(int flavour, int spectral, const ssk_ref_params *p) {
         else if (flavour == 0 && spectral) r = new RefImpl<float, Spectrum<float, 4>>(*p);
         else if (flavour == 1 && !spectral) r = new RefImpl<DynF, Color<DynF, 3>>(*p);
         else if (flavour == 1 && spectral) r = new RefImpl<DynF, Spectrum<DynF, 4>>(*p);
+        else if (flavour == 2 && !spectral) r = new RefImpl<PktF, Color<PktF, 3>>(*p);
+        else if (flavour == 2 && spectral) r = new RefImpl<PktF, Spectrum<PktF, 4>>(*p);
         else throw std::runtime_error("bad flavour");
     });
     return rc ? nullptr : r;
@@ -457,6 +524,7 @@ int ssk_ref_set_scene(void *h, const float *bmin, const float *bmax) {
     return guarded([&] { ((RefBase *) h)->set_scene(bmin, bmax); });
 }
 int ssk_ref_channels(void *h) { return ((RefBase *) h)->channels(); }
+int ssk_ref_packet_width() { return SSK_REF_PACKET_WIDTH; }
 int ssk_ref_warn_count() { return mitsuba::detail::oracle_warn_count(); }
 
 // All buffers are SoA: component c of element i lives at ptr[c * n + i].

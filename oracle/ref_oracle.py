@@ -6,7 +6,8 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_ref", "libsunsky_ref.so")
+LIB_PATH = os.path.join(_HERE, "_ref", "libsunsky_ref.so")               # AVX2 + FMA: the parity oracle
+LIB_PATH_AVX512 = os.path.join(_HERE, "_ref", "libsunsky_ref_avx512.so")  # 16-wide packets for the timed baseline
 REPO = os.path.dirname(_HERE)
 # dataset root: a directory that contains resources/sunsky/datasets/*.bin
 DEFAULT_ROOTS = ["/root/reference", os.path.join(REPO, "mitsuba3-sunsky_b200", "data")]
@@ -42,17 +43,45 @@ class RefState(C.Structure):
 
 
 _lib = None
+_libs = {}
 FP = C.POINTER(C.c_float)
+
+
+def host_has_avx512():
+    try:
+        flags = open("/proc/cpuinfo").read()
+    except OSError:
+        return False
+    return all((" " + f) in flags for f in ("avx512f", "avx512vl", "avx512dq", "avx512bw", "avx512cd"))
+
+
+def best_isa():
+    """ISA build for the timed CPU baseline: AVX-512 when the host has it and the library was built."""
+    return "avx512" if host_has_avx512() and os.path.exists(LIB_PATH_AVX512) else "avx2"
 
 
 def available():
     return os.path.exists(LIB_PATH)
 
 
-def lib():
+def lib(isa="avx2"):
+    """isa "avx2": the parity oracle (every golden vector comes from it). "avx512": same harness, 16-wide packets,
+    for timing only. "best": best_isa()."""
     global _lib
+    if isa == "best":
+        isa = best_isa()
+    if isa != "avx2":
+        if isa not in _libs:
+            _libs[isa] = _load(LIB_PATH_AVX512)
+        return _libs[isa]
     if _lib is None:
-        L = C.CDLL(LIB_PATH)
+        _lib = _load(LIB_PATH)
+    return _lib
+
+
+def _load(path):
+    if True:
+        L = C.CDLL(path)
         L.ssk_ref_last_error.restype = C.c_char_p
         L.ssk_ref_create.restype = C.c_void_p
         L.ssk_ref_create.argtypes = [C.c_int, C.c_int, C.POINTER(RefParams)]
@@ -82,8 +111,8 @@ def lib():
             if os.path.exists(os.path.join(r, "resources", "sunsky", "datasets", "tgmm_tables.bin")):
                 L.ssk_ref_set_resource_root(r.encode())
                 break
-        _lib = L
-    return _lib
+        L.ssk_ref_packet_width.restype = C.c_int
+    return L
 
 
 def _fp(a):
@@ -147,10 +176,11 @@ def make_params(turbidity=3.0, albedo=None, sun_direction=None, record=None, hou
 
 
 class RefEmitter:
-    """SunskyEmitter of the reference. flavour 0 = scalar_*, 1 = array (llvm_ad_*-like)."""
+    """SunskyEmitter of the reference. flavour 0 = scalar_* arithmetic, 1 = array arithmetic (llvm_ad_*-like; the
+    parity target), 2 = the query members on SIMD packets (timed baseline; within a few ulp of flavour 1)."""
 
-    def __init__(self, spectral=False, flavour=1, **kw):
-        self.L = lib()
+    def __init__(self, spectral=False, flavour=1, isa="avx2", **kw):
+        self.L = lib(isa)
         self.spectral = spectral
         self.params = make_params(**kw)
         self.h = self.L.ssk_ref_create(flavour, int(spectral), C.byref(self.params))
