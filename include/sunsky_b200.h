@@ -18,6 +18,15 @@
  *     last failure on the calling thread. There is no CPU fallback: without a CUDA device the
  *     compute entry points fail with SSK_ERR_CUDA.
  *   - a context is immutable between ssk_update() calls, so launches may be issued concurrently
+ *   - ordering of updates against launches: ssk_update / ssk_update_batch / ssk_set_scene never touch device memory
+ *     that launches already queued still read. Each context keeps a ring of 3 device blocks; an update writes the
+ *     next one (after waiting, on the host, for the launches that last used it -- those issued two updates ago) and
+ *     only launches issued AFTER the update call returns see the new state. So the Dr.Jit / torch pattern
+ *     "launch, parameters_changed, launch" on one stream needs no synchronisation by the caller. The wait is on
+ *     the event recorded after the most recent launch per block: a caller that issues launches on one context from
+ *     SEVERAL streams and updates more than twice while the oldest of them are still queued must synchronise
+ *     those streams itself.
+ *   - every call restores the calling thread's current CUDA device before it returns
  */
 #ifndef SUNSKY_B200_H
 #define SUNSKY_B200_H

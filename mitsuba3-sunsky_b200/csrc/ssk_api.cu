@@ -38,11 +38,20 @@ struct Staging {            // per-context pinned + device scratch for the *_hos
 
 } // namespace
 
+/// Device copies of the emitter block. Kernels take the hot part by value at launch but read the sun table and the
+/// shared-memory staging from global memory when they EXECUTE, so an update must not overwrite a block that queued
+/// launches still read. Every update therefore moves to the next block of a small ring and, before writing it,
+/// waits for the event recorded after the last launch that used it (launches issued two updates ago).
+constexpr int kBlockRing = 3;
+
 struct ssk_ctx {
     HostEmitter E;
     int device = -1;
     int mode = SSK_MODE_RGB;
-    EmitterBlock *d_block = nullptr;
+    EmitterBlock *d_block = nullptr;                 // = ring[cur]: what new launches read
+    EmitterBlock *ring[kBlockRing] = {};
+    cudaEvent_t used[kBlockRing] = {};               // recorded on the launch stream after every launch on ring[i]
+    int cur = 0;
     mutable TangentBlock *d_tangent = nullptr;       // eval_jvp: lazily allocated, rewritten by every call
     int sm_count = 0;
     mutable Staging st;
@@ -69,11 +78,50 @@ template <typename K> int occupancy_grid(const ssk_ctx *ctx, K kernel, size_t n_
     return SSK_OK;
 }
 
+/// Makes the context's device current for the scope of one C-ABI call and restores the caller's device on exit
+/// (a host application that drives several GPUs from one thread must not find its current device changed).
+struct DeviceGuard {
+    int prev = -1; bool active = false;
+    int enter(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { cudaGetLastError(); prev = -1; }
+        if (prev != device) { SSK_CUDA(cudaSetDevice(device)); active = prev >= 0; }
+        return SSK_OK;
+    }
+    ~DeviceGuard() { if (active) cudaSetDevice(prev); }
+};
+
+int alloc_blocks(ssk_ctx *ctx) {
+    for (int i = 0; i < kBlockRing; ++i) {
+        SSK_CUDA(cudaMalloc(&ctx->ring[i], sizeof(EmitterBlock)));
+        SSK_CUDA(cudaEventCreateWithFlags(&ctx->used[i], cudaEventDisableTiming));
+    }
+    ctx->cur = 0; ctx->d_block = ctx->ring[0];
+    return SSK_OK;
+}
+
+/// Next block of the ring becomes the one updates write and new launches read; waits (host side) until the launches
+/// that last read it have finished. Launches queued on the current block keep reading the current block.
+int rotate_block(ssk_ctx *ctx) {
+    if (ctx->device < 0) return SSK_OK;
+    const int next = (ctx->cur + 1) % kBlockRing;
+    SSK_CUDA(cudaEventSynchronize(ctx->used[next]));
+    ctx->cur = next; ctx->d_block = ctx->ring[next];
+    return SSK_OK;
+}
+
+/// Bookkeeping after a launch on `s` that reads the context's current device block
+int launched(const ssk_ctx *ctx, cudaStream_t s, int n = 1) {
+    g_launches += n;
+    SSK_CUDA(cudaGetLastError());
+    SSK_CUDA(cudaEventRecord(ctx->used[ctx->cur], s));
+    return SSK_OK;
+}
+
 int upload_block(ssk_ctx *ctx) {
     if (ctx->device < 0) return SSK_OK;
-    SSK_CUDA(cudaSetDevice(ctx->device));
-    if (!ctx->d_block) SSK_CUDA(cudaMalloc(&ctx->d_block, sizeof(EmitterBlock)));
-    // synchronous on purpose: a context is immutable between updates
+    DeviceGuard dg; if (int rc = dg.enter(ctx->device)) return rc;
+    // synchronous: when the update call returns the block is on the device, and nothing queued reads ring[cur]
+    // (rotate_block) -- except after ssk_set_scene, which patches the current block: see there
     SSK_CUDA(cudaMemcpy(ctx->d_block, &ctx->E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice));
     return SSK_OK;
 }
@@ -117,7 +165,7 @@ int quadrature_device_batch(ssk_ctx *const *ctxs, int n, float (*sky_rad)[11], f
     if (device >= kMaxDevices) return fail(SSK_ERR_UNSUPPORTED, "device ordinal too large");
     SetupScratch &sc = g_setup[device];
     std::lock_guard<std::mutex> lock(sc.mu);
-    SSK_CUDA(cudaSetDevice(device));
+    DeviceGuard dg; if (int rc = dg.enter(device)) return rc;
     if (int rc = ensure_setup_scratch(sc, n > 1 ? kSetupBatch : 1)) return rc;
     const int C = ctxs[0]->E.n_channels, nchains = 2 * C * kQuadChunks;
     for (int g0 = 0; g0 < n; g0 += sc.capacity) {
@@ -165,12 +213,11 @@ void build_on(ssk_ctx *ctx, const ssk_params &p, bool from_constructor) {
     });
 }
 
-int need_device(const ssk_ctx *ctx) {
+int need_device(const ssk_ctx *ctx, DeviceGuard &dg) {
     if (!ctx) return fail(SSK_ERR_INVALID, "null context");
     if (ctx->device < 0 || !ctx->d_block)
         return fail(SSK_ERR_CUDA, "context has no CUDA device: the sunsky kernels have no CPU fallback");
-    SSK_CUDA(cudaSetDevice(ctx->device));
-    return SSK_OK;
+    return dg.enter(ctx->device);
 }
 
 const HotBlock &hot(const ssk_ctx *ctx) { return ctx->E.block; }
@@ -194,7 +241,7 @@ int launch_eval_t(const ssk_ctx *ctx, bool spectral, const Planes3 &i3, const Pl
 
 int launch_eval(const ssk_ctx *ctx, const float *const in[3], const float *const wav[4], size_t n,
                 float *const out[4], float dir_sign, cudaStream_t s) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     if (!in || !out || !in[0] || !in[1] || !in[2]) return fail(SSK_ERR_INVALID, "null direction / output planes");
     if (n == 0) return SSK_OK;
     const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
@@ -234,9 +281,7 @@ int launch_eval(const ssk_ctx *ctx, const float *const in[3], const float *const
     else rc = vec ? launch_eval_t<kExact, 4>(ctx, spectral, i3, w4, out, n, dir_sign, s)
                   : launch_eval_t<kExact, 1>(ctx, spectral, i3, w4, out, n, dir_sign, s);
     if (rc) return rc;
-    g_launches++;
-    SSK_CUDA(cudaGetLastError());
-    return SSK_OK;
+    return launched(ctx, s);
 }
 
 template <int A, int R>
@@ -248,7 +293,7 @@ int launch_pdf_t(const ssk_ctx *ctx, const Planes3 &i3, float *pdf, size_t n, cu
 }
 
 int launch_pdf(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf, cudaStream_t s) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     if (!d || !d[0] || !d[1] || !d[2] || !pdf) return fail(SSK_ERR_INVALID, "null direction / pdf planes");
     if (n == 0) return SSK_OK;
     bool vec = !force_scalar() && aligned16(d[0]) && aligned16(d[1]) && aligned16(d[2]) && aligned16(pdf);
@@ -268,9 +313,7 @@ int launch_pdf(const ssk_ctx *ctx, const float *const d[3], size_t n, float *pdf
     if (fast(ctx)) rc = vec ? launch_pdf_t<kFast, 4>(ctx, i3, pdf, n, s) : launch_pdf_t<kFast, 1>(ctx, i3, pdf, n, s);
     else rc = vec ? launch_pdf_t<kExact, 4>(ctx, i3, pdf, n, s) : launch_pdf_t<kExact, 1>(ctx, i3, pdf, n, s);
     if (rc) return rc;
-    g_launches++;
-    SSK_CUDA(cudaGetLastError());
-    return SSK_OK;
+    return launched(ctx, s);
 }
 
 template <int A, int R, bool Spectral>
@@ -352,7 +395,7 @@ int launch_sample_a(const ssk_ctx *ctx, bool spectral, bool vec, const SampleArg
 int launch_sample(const ssk_ctx *ctx, const float *const u[2], const float *const it_p[3],
                   const float *const wav[4], size_t n, float *const d[3], float *pdf, float *const weight[4],
                   float *const p[3], float *dist, cudaStream_t s) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
     const int C = spectral ? 4 : 3;
     if (!u || !u[0] || !u[1] || !d || !d[0] || !d[1] || !d[2] || !pdf || !weight)
@@ -387,15 +430,13 @@ int launch_sample(const ssk_ctx *ctx, const float *const u[2], const float *cons
     if (dist) { a.dist = dist; vec = vec && aligned16(dist); }
     int rc = fast(ctx) ? launch_sample_a<kFast>(ctx, spectral, vec, a, n, s) : launch_sample_a<kExact>(ctx, spectral, vec, a, n, s);
     if (rc) return rc;
-    g_launches++;
-    SSK_CUDA(cudaGetLastError());
-    return SSK_OK;
+    return launched(ctx, s);
 }
 
 /// sample_wavelengths: spectral -> wavelength importance sampling + eval / pdf; RGB -> eval (sunsky.cpp:463-480)
 int launch_sample_wavelengths(const ssk_ctx *ctx, const float *const wi[3], const float *sample, size_t n,
                               float *const wav[4], float *const weight[4], cudaStream_t s) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
     if (!spectral) return launch_eval(ctx, wi, nullptr, n, weight, 1.f, s);      // Wavelength(0), eval(si)
     if (!wi || !wi[0] || !wi[1] || !wi[2] || !sample) return fail(SSK_ERR_INVALID, "null direction / sample planes");
@@ -412,9 +453,7 @@ int launch_sample_wavelengths(const ssk_ctx *ctx, const float *const wi[3], cons
         if (int rc = occupancy_grid(ctx, sample_wavelengths_kernel<kExact>, n, &grid, 1)) return rc;
         sample_wavelengths_kernel<kExact><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, sample, w4, q4, n);
     }
-    g_launches++;
-    SSK_CUDA(cudaGetLastError());
-    return SSK_OK;
+    return launched(ctx, s);
 }
 
 template <int A, bool Spectral>
@@ -437,7 +476,7 @@ int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStre
 int launch_sample_ray(const ssk_ctx *ctx, const float *wl_sample, const float *const s2[2], const float *const s3[2],
                       size_t n, float *const o[3], float *const d[3], float *const wav[4], float *const weight[4],
                       cudaStream_t s) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
     const int C = spectral ? 4 : 3;
     if (!s2 || !s2[0] || !s2[1] || !s3 || !s3[0] || !s3[1]) return fail(SSK_ERR_INVALID, "null sample planes");
@@ -463,9 +502,7 @@ int launch_sample_ray(const ssk_ctx *ctx, const float *wl_sample, const float *c
     if (fast(ctx)) rc = spectral ? launch_sample_ray_t<kFast, true>(ctx, a, n, s) : launch_sample_ray_t<kFast, false>(ctx, a, n, s);
     else rc = spectral ? launch_sample_ray_t<kExact, true>(ctx, a, n, s) : launch_sample_ray_t<kExact, false>(ctx, a, n, s);
     if (rc) return rc;
-    g_launches++;
-    SSK_CUDA(cudaGetLastError());
-    return SSK_OK;
+    return launched(ctx, s);
 }
 
 // ---- host entry points: chunked H2D -> kernel -> D2H over 3 streams with pinned staging ---------
@@ -501,7 +538,7 @@ bool is_pinned(const void *p) {
 template <typename Launch>
 int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *const *out, int n_out, size_t n,
                   Launch &&launch) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     if (n == 0) return SSK_OK;
     std::lock_guard<std::mutex> lock(ctx->st.mu);
     if (int rc = ensure_staging(ctx, n_in + n_out)) return rc;
@@ -618,9 +655,9 @@ int ssk_create(const ssk_params *p, const char *dataset_dir, int device, int mod
                 return fail(SSK_ERR_CUDA, std::string("CUDA device ") + std::to_string(device) + " is not available: " +
                                               (e != cudaSuccess ? cudaGetErrorString(e) : "ordinal out of range"));
             }
-            SSK_CUDA(cudaSetDevice(device));
+            DeviceGuard dg; if (int rc2 = dg.enter(device)) return rc2;
             SSK_CUDA(cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device));
-            SSK_CUDA(cudaMalloc(&ctx->d_block, sizeof(EmitterBlock)));
+            if (int rc2 = alloc_blocks(ctx)) return rc2;
         }
         build_on(ctx, *p, true);
         return upload_block(ctx);
@@ -634,8 +671,11 @@ int ssk_update(ssk_ctx *ctx, const ssk_params *p) {
     if (!ctx || !p) return fail(SSK_ERR_INVALID, "null argument");
     return guarded([&]() -> int {
         HostEmitter backup = ctx->E;
+        const int cur0 = ctx->cur;
+        // the new state goes to the next block of the ring: launches already queued keep reading the old one
+        if (int rc = rotate_block(ctx)) return rc;
         try { build_on(ctx, *p, false); }
-        catch (...) { ctx->E = backup; upload_block(ctx); throw; }
+        catch (...) { ctx->E = backup; ctx->cur = cur0; ctx->d_block = ctx->ring[cur0]; throw; }
         return upload_block(ctx);
     });
 }
@@ -649,13 +689,23 @@ int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n) {
             return fail(SSK_ERR_INVALID, "ssk_update_batch: contexts must share one device and one mode");
     }
     if (ctxs[0]->device < 0 || getenv("SSK_HOST_SETUP")) {
-        for (int i = 0; i < n; ++i) if (int rc = ssk_update(ctxs[i], &params[i])) return rc;
+        std::vector<HostEmitter> backup(n);
+        for (int i = 0; i < n; ++i) backup[i] = ctxs[i]->E;
+        for (int i = 0; i < n; ++i)
+            if (int rc = ssk_update(ctxs[i], &params[i])) {        // all or nothing: undo the ones already updated
+                std::string msg = g_err;
+                for (int j = 0; j < i; ++j) { ctxs[j]->E = backup[j]; if (ctxs[j]->device >= 0) { rotate_block(ctxs[j]); upload_block(ctxs[j]); } }
+                return fail(rc, msg);
+            }
         return SSK_OK;
     }
     return guarded([&]() -> int {
         std::vector<HostEmitter> backup(n);
-        for (int i = 0; i < n; ++i) backup[i] = ctxs[i]->E;
-        auto rollback = [&] { for (int i = 0; i < n; ++i) { ctxs[i]->E = backup[i]; upload_block(ctxs[i]); } };
+        std::vector<int> cur0(n);
+        for (int i = 0; i < n; ++i) { backup[i] = ctxs[i]->E; cur0[i] = ctxs[i]->cur; }
+        // on failure every context goes back to the block it was on (untouched: updates write the next one)
+        auto rollback = [&] { for (int i = 0; i < n; ++i) { ctxs[i]->E = backup[i]; ctxs[i]->cur = cur0[i]; ctxs[i]->d_block = ctxs[i]->ring[cur0[i]]; } };
+        for (int i = 0; i < n; ++i) if (int rc = rotate_block(ctxs[i])) { rollback(); return rc; }
         static const bool trace = getenv("SSK_SETUP_TRACE") != nullptr;
         auto now = [] { return std::chrono::steady_clock::now(); };
         auto us = [](auto a, auto b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
@@ -674,7 +724,7 @@ int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n) {
         {   // final blocks: enqueued together on the setup stream, one synchronisation
             SetupScratch &sc = g_setup[ctxs[0]->device];
             std::lock_guard<std::mutex> lock(sc.mu);
-            SSK_CUDA(cudaSetDevice(ctxs[0]->device));
+            DeviceGuard dg; if (int rc = dg.enter(ctxs[0]->device)) return rc;
             for (int i = 0; i < n; ++i)
                 SSK_CUDA(cudaMemcpyAsync(ctxs[i]->d_block, &ctxs[i]->E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, sc.stream));
             SSK_CUDA(cudaStreamSynchronize(sc.stream));
@@ -707,19 +757,23 @@ int ssk_set_scene(ssk_ctx *ctx, const float *bmin, const float *bmax) {
     for (int i = 0; i < 3; ++i) E.block.bs_center[i] = E.bs_center[i];
     E.block.bs_radius = E.bs_radius;
     set_ray_pdf_scale(E.block);
+    if (int rc = rotate_block(ctx)) return rc;
     return upload_block(ctx);
 }
 
 void ssk_destroy(ssk_ctx *ctx) {
     if (!ctx) return;
     if (ctx->device >= 0) {
-        cudaSetDevice(ctx->device);
+        DeviceGuard dg; dg.enter(ctx->device);
+        for (int i = 0; i < kBlockRing; ++i) {
+            if (ctx->used[i]) { cudaEventSynchronize(ctx->used[i]); cudaEventDestroy(ctx->used[i]); }
+            if (ctx->ring[i]) cudaFree(ctx->ring[i]);
+        }
         for (int i = 0; i < Staging::kStreams; ++i) {
             if (ctx->st.stream[i]) { cudaStreamSynchronize(ctx->st.stream[i]); cudaStreamDestroy(ctx->st.stream[i]); }
             if (ctx->st.pinned[i]) cudaFreeHost(ctx->st.pinned[i]);
             if (ctx->st.dev[i]) cudaFree(ctx->st.dev[i]);
         }
-        if (ctx->d_block) cudaFree(ctx->d_block);
         if (ctx->d_tangent) cudaFree(ctx->d_tangent);
     }
     delete ctx;
@@ -799,7 +853,7 @@ int ssk_envmap_device(ssk_ctx *const *ctxs, int n_maps, int width, int height, c
                       float *out, void *stream) {
     if (!ctxs || n_maps <= 0 || width <= 0 || height <= 0 || !out) return fail(SSK_ERR_INVALID, "bad envmap arguments");
     const ssk_ctx *c0 = ctxs[0];
-    if (int rc = need_device(c0)) return rc;
+    DeviceGuard dg; if (int rc = need_device(c0, dg)) return rc;
     const bool spectral = c0->mode == SSK_MODE_SPECTRAL;
     if (spectral && !wavelengths4) return fail(SSK_ERR_INVALID, "spectral env maps need 4 wavelengths per map");
     for (int i = 0; i < n_maps; ++i)
@@ -817,9 +871,8 @@ int ssk_envmap_device(ssk_ctx *const *ctxs, int n_maps, int width, int height, c
         if (fast(c)) rc = spectral ? launch_envmap_t<kFast, true>(c, wl, o, width, height, s) : launch_envmap_t<kFast, false>(c, wl, o, width, height, s);
         else rc = spectral ? launch_envmap_t<kExact, true>(c, wl, o, width, height, s) : launch_envmap_t<kExact, false>(c, wl, o, width, height, s);
         if (rc) return rc;
-        g_launches++;
+        if (int rc2 = launched(c, s)) return rc2;
     }
-    SSK_CUDA(cudaGetLastError());
     return SSK_OK;
 }
 
@@ -833,7 +886,7 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
 }
 
 int ssk_envmap_directions_device(const ssk_ctx *ctx, int width, int height, float *const d[3], void *stream) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     if (!d || !d[0] || !d[1] || !d[2]) return fail(SSK_ERR_INVALID, "null planes");
     envmap_dirs_kernel<<<ctx->sm_count * 4, 256, 0, (cudaStream_t) stream>>>(d[0], d[1], d[2], width, height);
     g_launches++;
@@ -917,7 +970,7 @@ int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const
 
 int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo,
                         const float *const wi[3], const float *const wav[4], size_t n, float *const out[4], void *stream) {
-    if (int rc = need_device(ctx)) return rc;
+    DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
     const int C = spectral ? 4 : 3;
     if (n_d_albedo != 0 && n_d_albedo != 1 && n_d_albedo != ctx->E.n_channels)
@@ -948,9 +1001,7 @@ int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_al
         int rc = fast(ctx) ? (spectral ? launch(eval_jvp_kernel<kFast, true>) : launch(eval_jvp_kernel<kFast, false>))
                            : (spectral ? launch(eval_jvp_kernel<kExact, true>) : launch(eval_jvp_kernel<kExact, false>));
         if (rc) return rc;
-        g_launches++;
-        SSK_CUDA(cudaGetLastError());
-        return SSK_OK;
+        return launched(ctx, s);
     });
 }
 

@@ -52,10 +52,13 @@ def _pp(planes):
     return arr
 
 
-def _pp_t(t, k, name):
+def _pp_t(t, k, name, device=None):
     import torch
     if t.dtype != torch.float32 or t.dim() != 2 or t.shape[0] != k:
         raise ValueError(f"{name}: expected float32 tensor of shape ({k}, n), got {tuple(t.shape)} {t.dtype}")
+    if not t.is_cuda or (device is not None and t.device.index != device):
+        # a host pointer handed to a kernel is a sticky illegal-address fault: refuse it here
+        raise ValueError(f"{name}: expected a CUDA tensor on device {device}, got {t.device}")
     if t.stride(1) != 1:
         t = t.contiguous()
     arr = (_capi.FP * k)()
@@ -210,22 +213,26 @@ class SunskyEmitter:
 
     # -- Emitter interface --------------------------------------------------------------------
     def _stream(self):
+        """torch's current stream ON THE CONTEXT'S DEVICE (not on whatever device happens to be current)."""
         import torch
-        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _pp_t(self, t, k, name):
+        return _pp_t(t, k, name, self.device)
 
     def _eval_impl(self, dirs, wavelengths, direction):
         Cn = self.channels
         if _is_torch(dirs):
             import torch
-            d_pp, dirs = _pp_t(dirs, 3, "directions")
+            d_pp, dirs = self._pp_t(dirs, 3, "directions")
             n = dirs.shape[1]
             w_pp = None
             if self.spectral:
                 if wavelengths is None:
                     raise ValueError("spectral mode needs wavelengths of shape (4, n)")
-                w_pp, wavelengths = _pp_t(wavelengths, 4, "wavelengths")
+                w_pp, wavelengths = self._pp_t(wavelengths, 4, "wavelengths")
             out = torch.empty((Cn, n), dtype=torch.float32, device=dirs.device)
-            o_pp, _ = _pp_t(out, Cn, "out")
+            o_pp, _ = self._pp_t(out, Cn, "out")
             fn = self._L.ssk_eval_direction_device if direction else self._L.ssk_eval_device
             _check(fn(self._ctx, d_pp, w_pp, n, o_pp, self._stream()))
             return out
@@ -254,7 +261,7 @@ class SunskyEmitter:
         """Solid-angle density of sample_direction() at world direction d: (3, n) -> (n,)"""
         if _is_torch(d):
             import torch
-            d_pp, d = _pp_t(d, 3, "d")
+            d_pp, d = self._pp_t(d, 3, "d")
             n = d.shape[1]
             out = torch.empty(n, dtype=torch.float32, device=d.device)
             _check(self._L.ssk_pdf_direction_device(self._ctx, d_pp, n, C.cast(out.data_ptr(), _capi.FP), self._stream()))
@@ -272,25 +279,25 @@ class SunskyEmitter:
         Cn = self.channels
         if _is_torch(u):
             import torch
-            u_pp, u = _pp_t(u, 2, "u")
+            u_pp, u = self._pp_t(u, 2, "u")
             n = u.shape[1]
             dev = u.device
             p_pp = w_pp = None
             if it_p is not None:
-                p_pp, it_p = _pp_t(it_p, 3, "it_p")
+                p_pp, it_p = self._pp_t(it_p, 3, "it_p")
             if self.spectral:
                 if wavelengths is None:
                     raise ValueError("spectral mode needs wavelengths of shape (4, n)")
-                w_pp, wavelengths = _pp_t(wavelengths, 4, "wavelengths")
+                w_pp, wavelengths = self._pp_t(wavelengths, 4, "wavelengths")
             d = torch.empty((3, n), dtype=torch.float32, device=dev)
             pdf = torch.empty(n, dtype=torch.float32, device=dev)
             wgt = torch.empty((Cn, n), dtype=torch.float32, device=dev)
-            d_pp, _ = _pp_t(d, 3, "d"); q_pp, _ = _pp_t(wgt, Cn, "weight")
+            d_pp, _ = self._pp_t(d, 3, "d"); q_pp, _ = self._pp_t(wgt, Cn, "weight")
             op_pp = dist_p = None
             if want_p:
                 op = torch.empty((3, n), dtype=torch.float32, device=dev)
                 dist = torch.empty(n, dtype=torch.float32, device=dev)
-                op_pp, _ = _pp_t(op, 3, "p"); dist_p = C.cast(dist.data_ptr(), _capi.FP)
+                op_pp, _ = self._pp_t(op, 3, "p"); dist_p = C.cast(dist.data_ptr(), _capi.FP)
             _check(self._L.ssk_sample_direction_device(self._ctx, u_pp, p_pp, w_pp, n, d_pp,
                                                        C.cast(pdf.data_ptr(), _capi.FP), q_pp, op_pp, dist_p,
                                                        self._stream()))
@@ -320,18 +327,18 @@ class SunskyEmitter:
         import torch
         if not _is_torch(wi):
             raise TypeError("eval_jvp takes CUDA tensors (float32, plane-major)")
-        d_pp, wi = _pp_t(wi, 3, "wi")
+        d_pp, wi = self._pp_t(wi, 3, "wi")
         n = wi.shape[1]
         w_pp = None
         if self.spectral:
             if wavelengths is None:
                 raise ValueError("spectral mode needs wavelengths of shape (4, n)")
-            w_pp, wavelengths = _pp_t(wavelengths, 4, "wavelengths")
+            w_pp, wavelengths = self._pp_t(wavelengths, 4, "wavelengths")
             if wavelengths.shape[1] != n:
                 raise ValueError("wavelengths: expected (4, n)")
         da = np.zeros(0, np.float32) if d_albedo is None else np.ascontiguousarray(d_albedo, dtype=np.float32).reshape(-1)
         out = torch.empty((self.channels, n), dtype=torch.float32, device=wi.device)
-        o_pp, _ = _pp_t(out, self.channels, "out")
+        o_pp, _ = self._pp_t(out, self.channels, "out")
         _check(self._L.ssk_eval_jvp_device(self._ctx, float(d_turbidity), da.ctypes.data_as(_capi.FP) if da.size else None,
                                            int(da.size), d_pp, w_pp, n, o_pp, self._stream()))
         return out
@@ -345,14 +352,14 @@ class SunskyEmitter:
             raise ValueError("spectral mode needs the wavelength sample of shape (n,)")
         if _is_torch(wi):
             import torch
-            d_pp, wi = _pp_t(wi, 3, "wi")
+            d_pp, wi = self._pp_t(wi, 3, "wi")
             n = wi.shape[1]
             sample = sample.contiguous()
-            if sample.dtype != torch.float32 or sample.numel() != n:
-                raise ValueError("sample: expected float32 tensor of n elements")
+            if sample.dtype != torch.float32 or sample.numel() != n or sample.device != wi.device:
+                raise ValueError("sample: expected float32 CUDA tensor of n elements on the emitter's device")
             wav = torch.empty((4, n), dtype=torch.float32, device=wi.device)
             wgt = torch.empty((4, n), dtype=torch.float32, device=wi.device)
-            w_pp, _ = _pp_t(wav, 4, "wavelengths"); q_pp, _ = _pp_t(wgt, 4, "weight")
+            w_pp, _ = self._pp_t(wav, 4, "wavelengths"); q_pp, _ = self._pp_t(wgt, 4, "weight")
             _check(self._L.ssk_sample_wavelengths_device(self._ctx, d_pp, C.cast(sample.data_ptr(), _capi.FP), n,
                                                          w_pp, q_pp, self._stream()))
             return wav, wgt
@@ -373,8 +380,8 @@ class SunskyEmitter:
         Cn = self.channels
         if _is_torch(sample2):
             import torch
-            a_pp, sample2 = _pp_t(sample2, 2, "sample2")
-            b_pp, sample3 = _pp_t(sample3, 2, "sample3")
+            a_pp, sample2 = self._pp_t(sample2, 2, "sample2")
+            b_pp, sample3 = self._pp_t(sample3, 2, "sample3")
             n = sample2.shape[1]
             dev = sample2.device
             wl_p = w_pp = wav = None
@@ -382,15 +389,15 @@ class SunskyEmitter:
                 if wavelength_sample is None:
                     raise ValueError("spectral mode needs wavelength_sample of shape (n,)")
                 wavelength_sample = wavelength_sample.contiguous()
-                if wavelength_sample.dtype != torch.float32 or wavelength_sample.numel() != n:
-                    raise ValueError("wavelength_sample: expected float32 tensor of n elements")
+                if wavelength_sample.dtype != torch.float32 or wavelength_sample.numel() != n or wavelength_sample.device != dev:
+                    raise ValueError("wavelength_sample: expected float32 CUDA tensor of n elements on the emitter's device")
                 wl_p = C.cast(wavelength_sample.data_ptr(), _capi.FP)
                 wav = torch.empty((4, n), dtype=torch.float32, device=dev)
-                w_pp, _ = _pp_t(wav, 4, "wavelengths")
+                w_pp, _ = self._pp_t(wav, 4, "wavelengths")
             o = torch.empty((3, n), dtype=torch.float32, device=dev)
             d = torch.empty((3, n), dtype=torch.float32, device=dev)
             wgt = torch.empty((Cn, n), dtype=torch.float32, device=dev)
-            o_pp, _ = _pp_t(o, 3, "o"); d_pp, _ = _pp_t(d, 3, "d"); q_pp, _ = _pp_t(wgt, Cn, "weight")
+            o_pp, _ = self._pp_t(o, 3, "o"); d_pp, _ = self._pp_t(d, 3, "d"); q_pp, _ = self._pp_t(wgt, Cn, "weight")
             _check(self._L.ssk_sample_ray_device(self._ctx, wl_p, a_pp, b_pp, n, o_pp, d_pp, w_pp, q_pp, self._stream()))
             return o, d, wav, wgt
         a = _planes_np(sample2, 2, "sample2"); b = _planes_np(sample3, 2, "sample3")

@@ -138,6 +138,45 @@ def test_update_and_set_scene_reach_the_device(ssk):
     assert np.allclose(p, it_p + d * dist, rtol=1e-6, atol=1e-4)
 
 
+def test_update_while_launches_are_in_flight(ssk):
+    """parameters_changed() between launches on a non-blocking stream, no synchronisation by the caller (what a
+    Dr.Jit / torch optimisation loop does): every launch must see exactly the state of the emitter at the time it was
+    ISSUED. Kernels read the sun table and their shared-memory staging from the device block when they execute, so an
+    update that overwrote the block in place would leak new tables into queued launches (round-1 advisor finding)."""
+    import torch
+    names = ["cfg1_rgb", "cfg3_rgb_sunsky", "rgb_t4p2_alb3", "rgb_t1_low"]
+    gs = [emitters.golden(n) for n in names]
+    kws = [common.CONFIGS[n][1] for n in names]
+    e = emitters.make(ssk, names[0], g=gs[0])
+    n_rep = 4096                                              # ~12 M rays per launch: updates overtake the kernels
+    ins = [torch.tensor(np.tile(-g["wo"], (1, n_rep))).cuda() for g in gs]
+    stream = torch.cuda.Stream()
+    outs = []
+    with torch.cuda.stream(stream):
+        for rnd in range(2):
+            for k, kw in enumerate(kws):
+                if rnd or k:
+                    sd = [float(v) for v in gs[k]["state_sun_dir_world"]]
+                    e.update(turbidity=kw["turbidity"], albedo=kw["albedo"], sun_direction=sd)
+                outs.append((k, e.eval(ins[k]), e.eval(ins[k])))          # two launches per state, none awaited
+    stream.synchronize()
+    for k, a, b in outs:
+        want = np.tile(gs[k]["eval"], (1, n_rep))
+        assert common.bit_equal(a.cpu().numpy(), want) and common.bit_equal(b.cpu().numpy(), want), names[k]
+
+
+def test_host_tensors_and_foreign_devices_are_rejected(ssk):
+    import torch
+    e = emitters.make(ssk, "cfg1_rgb", g=emitters.golden("cfg1_rgb"))
+    with pytest.raises(ValueError, match="CUDA tensor"):
+        e.eval(torch.zeros((3, 16)))
+    with pytest.raises(ValueError, match="CUDA tensor"):
+        e.sample_direction(torch.zeros((2, 16)))
+    assert torch.cuda.current_device() == 0
+    e.eval(torch.zeros((3, 16), device="cuda"))
+    assert torch.cuda.current_device() == 0
+
+
 @pytest.mark.parametrize("spectral", [False, True])
 def test_live_reference_random_configs(ssk, ref, spectral):
     """Fresh emitter parameters and inputs (not in the fixtures), compared against the reference library."""
