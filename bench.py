@@ -4,11 +4,14 @@
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 One JSON line on stdout. A "step" is one pass of SunskyEmitter.eval (spectral, sun + sky) over the
-BASELINE configs[1] batch: 2^24 random upper-hemisphere directions with 4 wavelengths each, resident in
-HBM (470 MB of inputs per step, larger than the 126 MB L2, so no flush is needed between steps).
-`value` = Gevals/s over all ranks (device time, CUDA events, max over ranks); `e2e` = the same through
-ssk_eval_host with pinned host buffers (H2D + kernel + D2H inside the timed region). `extra` carries the
-other kernels of the path (RGB eval, pdf_direction, fused sample_direction on the configs[2] batch)."""
+BASELINE configs[1] batch: 2^24 upper-hemisphere directions with 4 wavelengths each, drawn from PCG32 streams as
+SURVEY.md 8(d) cfg 2 lays them out, resident in HBM (470 MB of inputs per step, larger than the 126 MB L2, so no
+flush is needed between steps). `value` = Gevals/s over all ranks (device time, CUDA events, max over ranks);
+`e2e` = the same through ssk_eval_host with pinned host buffers (H2D + kernel + D2H inside the timed region), next
+to the bare-copy ceiling of the same bytes; `sweeps` = BASELINE configs[3] / [4] (with the frames gathered on rank 0
+when N > 1); `extra` carries the other kernels of the path (RGB eval, pdf_direction, fused sample_direction on the
+configs[2] batch) and BASELINE configs[0]. `--impl reference` times the reference's own CPU code (oracle/_ref) on
+the same batch with all host threads."""
 import argparse
 import json
 import os
@@ -30,9 +33,15 @@ FLOPS = dict(eval_spectral=1013, eval_rgb=426, pdf=761, sample_rgb=1776)      # 
 BYTES = dict(eval_spectral=44, eval_rgb=24, pdf=16, sample_rgb=36)
 METRIC = "sky+sun radiance Gevals/s (spectral eval, 16M directions)"
 WORKLOAD = "configs[1]: spectral eval, 2^24 upper-hemisphere directions x 4 wavelengths per GPU, t=3 a=0.3 eta=30deg, sun+sky"
-# dram__bytes_read.sum + dram__bytes_write.sum of one eval_spec_kernel launch on 2^24 rays (ncu --set full,
-# profiles/r1_summary.md); the algorithmic figure is 44 B x 2^24 = 738 MB (part of the output is still in L2)
-NCU_TRAFFIC = {"fast": 699.0e6, "exact": 701.3e6}
+# identical in both arms (the driver compares them)
+CONFIG = {"workload": WORKLOAD, "l2": "inputs (470 MB per step) exceed the 126 MB L2; no flush needed between steps"}
+# Constants read off the committed ncu --set full captures of eval_spec_kernel on 2^24 rays (profiles/NCU_SOURCE):
+# dram__bytes_read.sum + dram__bytes_write.sum per launch (algorithmic: 44 B x 2^24 = 738 MB; part of the output is
+# still in L2 when the kernel ends), issue-slot utilisation, and executed fp32 flop per ray (FFMA = 2, FADD / FMUL = 1,
+# packed f32x2 ops counted per element, MUFU listed apart). They are NOT measured in this run; the key says so.
+NCU_SOURCE = "profiles/r2_ncu_eval_spec.md"
+NCU = {"fast": dict(traffic=699.0e6, issue_frac=0.714, flop_per_ray=None, mufu_per_ray=None),
+       "exact": dict(traffic=701.3e6, issue_frac=0.73, flop_per_ray=None, mufu_per_ray=None)}
 
 
 def peaks():
@@ -116,25 +125,66 @@ def emitter_kwargs():
     return dict(turbidity=3.0, albedo=0.3, sun_direction=common.sun_dir_from_elevation(30.0))
 
 
-def cpu_reference_rate(n_sample, threads, spectral=True, seed=0, flavour=1):
-    """Times the reference's own CPU code (oracle/_ref: its sunsky.cpp compiled in place; flavour 1 = the array code
-    path of llvm_ad_*, flavour 0 = scalar_*) on `n_sample` directions with `threads` host threads.
-    Returns (Gevals/s, seconds)."""
+def configs1_inputs(n, device, rank=0):
+    """SURVEY.md 8(d) cfg 2: generator j of PCG32(size = 2n) gives one float; (u1, u2) = (float[2i], float[2i + 1]);
+    cos(theta) = u1, phi = 2 pi u2, wo = (sin cos, sin sin, cos), si.wi = -wo; wavelengths = 360 + 360 *
+    sample_shifted<4>(u3) with u3 from the next block of n generators (core/math.h:408-431). Ranks use disjoint
+    stream blocks. Returns (wi (3, n), wo (3, n), wavelengths (4, n)) as torch tensors on `device`."""
+    import torch
+    from sunsky_b200 import pcg32
+    base = rank * 3 * n
+    u = pcg32.point2_pairs(n, stream_offset=base, device=device)
+    u3 = pcg32.floats(n, 1, stream_offset=base + 2 * n, device=device)[0]
+    ct = u[0]; st = torch.sqrt(torch.clamp(1 - ct * ct, min=0)); ph = (2 * np.pi) * u[1]
+    wo = torch.stack([st * torch.cos(ph), st * torch.sin(ph), ct]).contiguous()
+    shifted = u3[None, :] + torch.arange(4, device=device, dtype=torch.float32)[:, None] / 4
+    shifted = torch.where(shifted >= 1, shifted - 1, shifted)
+    # 360 + 360 * (1 - 2^-24) rounds to 720.0f, where the reference gathers one bin past its tables (SURVEY.md C4)
+    wav = (360.0 + 360.0 * shifted).clamp_(max=719.99).contiguous()
+    return (-wo).contiguous(), wo, wav
+
+
+def cpu_rate(r, wi, wav, threads, n, repeat=1):
+    """Gevals/s and seconds of the reference emitter `r` over the first n lanes (numpy planes), best of `repeat`."""
+    wi_n = np.ascontiguousarray(wi[:, :n]); wav_n = None if wav is None else np.ascontiguousarray(wav[:, :n])
+    best = 1e30
+    for _ in range(repeat):
+        t0 = time.perf_counter()
+        r.eval(wi_n, wav_n, threads=threads)
+        best = min(best, time.perf_counter() - t0)
+    return n / best / 1e9, best
+
+
+def cpu_flavours(wi, wav, threads, budget_s=24.0):
+    """The reference's CPU flavours on (a bounded sample of) the configs[1] batch: scalar (= scalar_spectral) and
+    packets (its query members on AVX2 / AVX-512 packets, the stand-in for llvm_ad_spectral's vectorised kernels),
+    one thread and all threads. Sample sizes are chosen from a calibration pass so the whole call stays near
+    `budget_s` seconds of CPU work."""
     import ref_oracle
-    import common
-    rng = np.random.default_rng(seed)
-    wo = common.hemisphere_dirs(n_sample, rng)
-    wav = np.minimum(360.0 + 360.0 * rng.random((4, n_sample), dtype=np.float32), 719.99).astype(np.float32) if spectral else None
-    r = ref_oracle.RefEmitter(spectral=spectral, flavour=flavour, **emitter_kwargs())
-    r.eval(-wo[:, :4096], None if wav is None else wav[:, :4096], threads=1)
-    t0 = time.perf_counter()
-    r.eval(-wo, wav, threads=threads)
-    dt = time.perf_counter() - t0
-    return n_sample / dt / 1e9, dt
+    isa = ref_oracle.best_isa()
+    kw = emitter_kwargs()
+    out = {"isa": isa, "packet_width": int(ref_oracle.lib(isa).ssk_ref_packet_width()), "threads": threads}
+    n_max = wi.shape[1]
+    for name, flavour in (("scalar", 0), ("packet", 2)):
+        r = ref_oracle.RefEmitter(spectral=True, flavour=flavour, isa=isa, **kw)
+        r.eval(wi[:, :4096].copy(), wav[:, :4096].copy(), threads=1)
+        cal, _ = cpu_rate(r, wi, wav, threads, min(n_max, 1 << 18))
+        n_all = int(min(n_max, max(1 << 18, 2 ** int(np.log2(cal * 1e9 * budget_s / 6)))))
+        n_one = int(min(n_max, max(1 << 16, n_all // max(threads, 1))))
+        v_all, t_all = cpu_rate(r, wi, wav, threads, n_all, repeat=2)
+        v_one, t_one = cpu_rate(r, wi, wav, 1, n_one)
+        out[name] = {"value": v_all, "single_thread_value": v_one, "lanes": n_all, "seconds": t_all,
+                     "single_thread_lanes": n_one}
+    return out
 
 
 def run_reference(args):
-    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only)."""
+    """--impl reference: the reference's CPU implementation of the path on the host cores (rank 0 only). The timed
+    flavour is the fastest one the reference's code has on this box: its eval() on dr::Packet<float, 16 | 8> (what
+    llvm_ad_spectral executes per SIMD lane group, minus the JIT) on every host thread. Every step is the FULL
+    configs[1] batch (2^24 directions) unless a calibration pass shows that warmup + steps would take more than
+    about three minutes; then the step shrinks to the largest power of two that fits, and `ms_per_step` is the
+    measured time of THAT step, never an extrapolation."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
@@ -142,28 +192,37 @@ def run_reference(args):
     if not ref_oracle.available():
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libsunsky_ref.so was not built"}))
         return 0
-    cores = os.cpu_count() or 1
-    threads = min(cores, 64)
-    # The reference's fastest CPU flavour that can be built here is its scalar_spectral variant run on all host threads
-    # (the array flavour standing in for llvm_ad_spectral pays a heap allocation per Dr.Jit operation and is ~10x slower;
-    # the real LLVM JIT cannot run on this box). The scalar variant is therefore the one timed as the reference arm.
-    n_sample = 1 << 21
-    rates = []
+    import torch
+    threads = min(os.cpu_count() or 1, 64)
+    torch.set_num_threads(threads)
+    wi_t, _, wav_t = configs1_inputs(N_EVAL, "cpu", 0)
+    wi, wav = wi_t.numpy(), wav_t.numpy()
+    isa = ref_oracle.best_isa()
+    width = int(ref_oracle.lib(isa).ssk_ref_packet_width())
+    r = ref_oracle.RefEmitter(spectral=True, flavour=2, isa=isa, **emitter_kwargs())
+    cal, _ = cpu_rate(r, wi, wav, threads, 1 << 20)
+    n_step = N_EVAL
+    while n_step > (1 << 18) and (args.warmup + args.steps) * n_step / (cal * 1e9) > 170.0:
+        n_step //= 2
+    times = []
     for i in range(args.warmup + args.steps):
-        rate, dt = cpu_reference_rate(n_sample, threads, True, seed=i, flavour=0)
+        _, dt = cpu_rate(r, wi, wav, threads, n_step)
         if i >= args.warmup:
-            rates.append((rate, dt))
-    total_t = sum(dt for _, dt in rates)
-    value = n_sample * len(rates) / total_t / 1e9
-    r_arr, _ = cpu_reference_rate(1 << 18, threads, True, seed=99, flavour=1)
-    sample = (f"{n_sample} of the {N_EVAL} directions per step (same distribution), scalar_spectral variant of the reference "
-              f"on {threads} threads; array flavour (llvm_ad_* code path, no JIT) on the same threads: {r_arr * 1e3:.2f} Mevals/s")
+            times.append(dt)
+    total_t = sum(times)
+    value = n_step * len(times) / total_t / 1e9
+    rs = ref_oracle.RefEmitter(spectral=True, flavour=0, isa=isa, **emitter_kwargs())
+    v_scalar, _ = cpu_rate(rs, wi, wav, threads, 1 << 20)
+    sample = (f"{n_step} of the {N_EVAL} directions per step" + (" (the full batch)" if n_step == N_EVAL else " (calibrated to the time budget)") +
+              f"; the reference's eval() on dr::Packet<float, {width}> ({isa}) over {threads} host threads; its scalar_spectral "
+              f"flavour on the same threads: {v_scalar * 1e3:.2f} Mevals/s")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / len(rates) * (N_EVAL / n_sample),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD},
-        "cpu_baseline": {"value": value, "unit": "Gevals/s", "cores": threads, "kind": "reference", "sample": sample},
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total_t / len(times),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic (PCG32 streams, SURVEY.md 8d cfg 2)",
+        "config": CONFIG,
+        "cpu_baseline": {"value": value, "unit": "Gevals/s", "cores": threads, "kind": "reference", "sample": sample,
+                         "isa": isa, "packet_width": width, "scalar_value": v_scalar, "lanes_per_step": n_step},
         "e2e": {"value": value, "unit": "Gevals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -211,12 +270,6 @@ def main():
         return ms
 
     warm = max(args.warmup, 3)
-    gen = torch.Generator(device=dev); gen.manual_seed(1234 + rank)
-
-    def hemisphere(n):
-        u1 = torch.rand(n, device=dev, generator=gen); u2 = torch.rand(n, device=dev, generator=gen)
-        st = torch.sqrt(torch.clamp(1 - u1 * u1, min=0)); ph = 2 * np.pi * u2
-        return torch.stack([st * torch.cos(ph), st * torch.sin(ph), u1]).contiguous()
 
     windows = []                                    # host-time (t0, t1) of every timed region, for the clock record
 
@@ -255,8 +308,7 @@ def main():
         return C.cast(t.data_ptr(), _capi.FP)
 
     # ---- inputs, resident in HBM ----------------------------------------------------------------------
-    wo = hemisphere(N_EVAL); wi = (-wo).contiguous()
-    wav = (360.0 + 360.0 * torch.rand((4, N_EVAL), device=dev, generator=gen)).clamp_(max=719.99).contiguous()
+    wi, wo, wav = configs1_inputs(N_EVAL, dev, rank)
     out = torch.empty((4, N_EVAL), device=dev)
     wi_pp, wo_pp, wav_pp, out_pp = planes(wi), planes(wo), planes(wav), planes(out)
 
@@ -280,22 +332,28 @@ def main():
     value = world * N_EVAL / (ms_per_step * 1e-3) / 1e9
     per_gpu = value / world
     achieved_tf = per_gpu * 1e9 * FLOPS["eval_spectral"] / 1e12
+    ncu = NCU[args.arith]
+    exec_tf = None if not ncu["flop_per_ray"] else per_gpu * 1e9 * ncu["flop_per_ray"] / 1e12
     roofline = {"bound": "fp32", "achieved": achieved_tf, "peak": fp32_peak, "unit": "TFLOP/s",
-                "frac": achieved_tf / fp32_peak, "traffic": NCU_TRAFFIC.get(args.arith),
+                "frac": achieved_tf / fp32_peak, "traffic": ncu["traffic"],
+                # what the hardware executed, as opposed to what the reference's op sequence would cost
+                "issue_frac": ncu["issue_frac"],
+                "executed": {"flop_per_ray": ncu["flop_per_ray"], "mufu_per_ray": ncu["mufu_per_ray"],
+                             "achieved": exec_tf, "frac": None if exec_tf is None else exec_tf / fp32_peak, "unit": "TFLOP/s",
+                             "source": f"constants from the ncu --set full capture in {NCU_SOURCE}, not measured in this run"},
                 "peak_source": f"{sm_count} SMs x 128 lanes x 2 flop x {pk['sm_max_mhz']:.0f} MHz ({pk['source']} max SM clock); "
                                "not a tensor-core path",
                 "kernel": f"eval_spec_kernel<{args.arith}>", "flops_per_eval": FLOPS["eval_spectral"],
                 "flops_note": "algorithmic flops of the reference op sequence (SURVEY.md 8d), not executed instructions",
-                "traffic_note": "dram read+write bytes per launch from the ncu capture under profiles/ (algorithmic: 738 MB)",
+                "traffic_note": f"dram read+write bytes per launch, constant from the ncu capture in {NCU_SOURCE} (algorithmic: 738 MB)",
                 "hbm": {"achieved": per_gpu * BYTES["eval_spectral"], "peak": pk["hbm_gbs"], "unit": "GB/s",
                         "frac": per_gpu * BYTES["eval_spectral"] / pk["hbm_gbs"], "bytes_per_eval": BYTES["eval_spectral"]}}
 
     # ---- e2e: same workload through the host entry point with pinned buffers ------------------------
     n_e2e = N_EVAL
-    h_wi = torch.empty((3, n_e2e), pin_memory=True); h_wi.copy_(wi)
-    h_wav = torch.empty((4, n_e2e), pin_memory=True); h_wav.copy_(wav)
+    h_in = torch.empty((7, n_e2e), pin_memory=True); h_in[:3].copy_(wi); h_in[3:].copy_(wav)     # si.wi | si.wavelengths
     h_out = torch.empty((4, n_e2e), pin_memory=True)
-    hwi_pp, hwav_pp, hout_pp = planes(h_wi), planes(h_wav), planes(h_out)
+    hwi_pp, hwav_pp, hout_pp = planes(h_in[:3]), planes(h_in[3:]), planes(h_out)
 
     def step_e2e():
         rc = L.ssk_eval_host(em_spec._ctx, hwi_pp, hwav_pp, n_e2e, hout_pp)
@@ -313,19 +371,32 @@ def main():
     windows.append((t0, time.perf_counter()))
     e2e_s = (windows[-1][1] - t0) / e2e_steps
     e2e_ms = max_over_ranks(e2e_s * 1e3)
+    # the bare transfers of the same bytes, all ranks at once: what the host <-> device links of this box allow
+    ceil_s = C.c_double()
+    barrier()
+    rc = L.ssk_host_copy_ceiling(local, 7 * 4 * n_e2e, 4 * 4 * n_e2e, 7 * 4 * (1 << 21), 3, C.byref(ceil_s))
+    assert rc == 0, L.ssk_last_error()
+    barrier()
+    ceil_ms = max_over_ranks(ceil_s.value * 1e3)
+    e2e_bytes = (7 + 4) * 4 * n_e2e
     e2e = {"value": world * n_e2e / (e2e_ms * 1e-3) / 1e9, "unit": "Gevals/s",
            "h2d_bytes_per_step": 7 * 4 * n_e2e, "d2h_bytes_per_step": 4 * 4 * n_e2e, "ms_per_step": e2e_ms,
            "launches_per_step": (ssk.launch_count() - l0) // e2e_steps,
-           "pcie_gbs": (7 + 4) * 4 * n_e2e / (e2e_ms * 1e-3) / 1e9,
-           "note": "ssk_eval_host: pinned host planes, 1 Mi-ray chunks over 3 streams, H2D + kernel + D2H inside the timed region"}
-    del h_wi, h_wav, h_out
+           "pcie_gbs": e2e_bytes / (e2e_ms * 1e-3) / 1e9,
+           "pcie_peak_gbs": e2e_bytes / (ceil_ms * 1e-3) / 1e9, "copy_ceiling_ms": ceil_ms, "frac": ceil_ms / e2e_ms,
+           "note": "ssk_eval_host: pinned host planes, 2 Mi-ray chunks over 3 streams, one strided H2D and one strided D2H copy per "
+                   "chunk, kernel in between, all inside the timed region. pcie_peak_gbs: the same bytes as bare pinned copies "
+                   "(H2D on one stream, D2H on another, every rank at once; ssk_host_copy_ceiling), per GPU, max over ranks; "
+                   "frac = ceiling time / e2e time"}
+    del h_in, h_out
 
     # ---- the other kernels of the path, both arithmetic modes ----------------------------------------------
     extra = {}
     if not args.no_extra:
         out3 = torch.empty((3, N_EVAL), device=dev); o3_pp = planes(out3)
         pdf = torch.empty(N_EVAL, device=dev)
-        u = torch.rand((2, N_SAMPLE), device=dev, generator=gen)
+        from sunsky_b200 import pcg32
+        u = pcg32.point2_pairs(N_SAMPLE, stream_offset=(1 << 40) + rank * 2 * N_SAMPLE, device=dev)   # sampling_test.py:30-32
         d = torch.empty((3, N_SAMPLE), device=dev); spdf = torch.empty(N_SAMPLE, device=dev)
         wgt = torch.empty((3, N_SAMPLE), device=dev)
         u_pp, d_pp, w_pp = planes(u), planes(d), planes(wgt)
@@ -368,71 +439,98 @@ def main():
             extra[mode] = ex
             for e in (es, er, e_sky, e_sun):
                 e.close()
-        # ---- configs[3] / configs[4]: env-map sweeps. Every frame needs its own emitter (parameters_changed:
-        #      host interpolation + device quadrature) before its map can be written; each rank renders its
-        #      share of the frames, optionally followed by the NCCL gather of finished frames on rank 0.
-        from sunsky_b200 import sharding, sweep as sweep_mod
+        del out3, pdf, u, d, spdf, wgt
+        torch.cuda.empty_cache()
+
+    # ---- configs[3] / configs[4]: env-map sweeps through ssk_sweep_render (C++ loop: pooled contexts re-parametrised
+    #      in batches, setup quadrature overlapping the queued maps). Each rank renders its share of the frames; with
+    #      N > 1 the frames are also collected on rank 0, (a) by the kernels themselves storing into rank 0's
+    #      IPC-mapped buffer over NVLink and (b) by the library's NCCL send/recv gather on a second stream.
+    sweeps = None
+    if not args.no_extra:
+        from sunsky_b200 import multi, sharding, sweep as sweep_mod
+        NVLINK_INGEST_GBS = 900.0        # NVLink 5 per direction per GPU (nominal): floor of all-frames-to-one-GPU
 
         def sweep_bench(config, width, height, chunk, gather):
             spectral = config == "animation"
-            mode_ = "round_robin" if spectral else "blocked"
-            params = sharding.sweep_parameters(config)
-            mine = sharding.frames_for_rank(len(params), rank, world, mode_)
+            mode_ = multi.SHARD_ROUND_ROBIN if spectral else multi.SHARD_BLOCKED
+            allp = sharding.sweep_parameters(config)
+            n_frames = len(allp)
+            mine = multi.frames_for_rank(n_frames, rank, world, mode_)
+            props = [dict(turbidity=allp[f]["turbidity"], albedo=allp[f]["albedo"],
+                          sun_direction=sweep_mod.sun_direction(allp[f]["eta_deg"])) for f in mine]
+            fparams = multi.frame_params(props, spectral, args.arith)
             Cn = 4 if spectral else 3
-            buf = torch.empty((chunk, Cn, height, width), device=dev)
-            full = torch.empty((chunk * world, Cn, height, width), device=dev) if (gather and rank == 0) else None
-            t_setup = 0.0
+            frame_floats = Cn * width * height
+            wl = (440.0, 520.0, 600.0, 680.0)
+            peer = comm = full = staging = buf = None
+            if gather == "peer":
+                peer = multi.PeerFrames(n_frames * frame_floats, local, rank, 0, dist if world > 1 else None)
+                allptr = peer.frame_pointers(frame_floats, n_frames)
+                ptrs = (_capi.FP * max(len(mine), 1))(*[allptr[f] for f in mine])
+            elif gather == "nccl":
+                comm = multi.Comm(rank, world, local, dist)
+                staging = torch.empty((2 * chunk, Cn, height, width), device=dev)
+                full = torch.empty((n_frames, Cn, height, width), device=dev) if rank == 0 else None
+            else:                                    # frames stay where they are rendered (a ring of 2 chunks is kept)
+                buf = torch.empty((2 * chunk, Cn, height, width), device=dev)
+                ptrs = (_capi.FP * max(len(mine), 1))(*[C.cast(buf[k % (2 * chunk)].data_ptr(), _capi.FP) for k in range(len(mine))])
             l0 = ssk.launch_count()
             barrier()
             t0 = time.perf_counter()
-            pools, events = [None, None], [None, None]      # two pools of contexts, re-parametrised in batches
-            for k, s0 in enumerate(range(0, len(mine), chunk)):
-                idx = mine[s0:s0 + chunk]
-                slot = k & 1
-                if events[slot] is not None:
-                    events[slot].synchronize()              # contexts outlive their previous launches
-                ts = time.perf_counter()
-                if pools[slot] is None or len(pools[slot]) != len(idx):
-                    for e_ in pools[slot] or []:
-                        e_.close()
-                    pools[slot] = sweep_mod.make_emitters([params[f] for f in idx], spectral, local, args.arith)
-                else:
-                    ssk.update_batch(pools[slot], [dict(turbidity=params[f]["turbidity"], albedo=params[f]["albedo"],
-                                                        sun_direction=sweep_mod.sun_direction(params[f]["eta_deg"])) for f in idx])
-                t_setup += time.perf_counter() - ts
-                ssk.envmaps(pools[slot], width, height, (440.0, 520.0, 600.0, 680.0) if spectral else None, out=buf[:len(idx)])
-                if gather and world > 1:
-                    dist.gather(buf, list(full.split(chunk)) if rank == 0 else None, dst=0)
-                events[slot] = torch.cuda.Event(); events[slot].record()
+            if gather == "nccl":
+                wl_np = np.ascontiguousarray(np.broadcast_to(np.asarray(wl, np.float32), (max(len(mine), 1), 4)))
+                rc = L.ssk_sweep_render_gather_nccl(comm.h, fparams, n_frames, mode_, _capi.DATASET_DIR.encode(),
+                                                    _capi.MODE_SPECTRAL if spectral else _capi.MODE_RGB, width, height,
+                                                    wl_np.ctypes.data_as(_capi.FP) if spectral else None, fp(staging),
+                                                    fp(full) if rank == 0 else None, 0, chunk, stream)
+                assert rc == 0, L.ssk_multi_last_error()
+            else:
+                multi.sweep_render(fparams, spectral, width, height, local, ptrs, wavelengths4=wl, chunk=chunk)
             torch.cuda.synchronize()
-            for slot in (0, 1):
-                for e_ in pools[slot] or []:
-                    e_.close()
             barrier()
             windows.append((t0, time.perf_counter()))
             sec = max_over_ranks(windows[-1][1] - t0)
-            n_frames = len(params)
-            return {"frames": n_frames, "frames_per_gpu": len(mine), "resolution": [width, height], "seconds": sec,
-                    "frames_per_s": n_frames / sec, "Gpixels_s": n_frames * width * height / sec / 1e9,
-                    "setup_ms_per_frame": t_setup / max(len(mine), 1) * 1e3,
-                    "gpu_launches": ssk.launch_count() - l0, "gathered_to_rank0": bool(gather and world > 1),
-                    "out_GB_per_gpu": len(mine) * Cn * width * height * 4 / 1e9}
+            res = {"frames": n_frames, "frames_per_gpu": len(mine), "resolution": [width, height], "seconds": sec,
+                   "frames_per_s": n_frames / sec, "Gpixels_s": n_frames * width * height / sec / 1e9,
+                   "gpu_launches": ssk.launch_count() - l0, "gather": gather or "none",
+                   "out_GB_total": n_frames * frame_floats * 4 / 1e9}
+            if gather:
+                remote = (n_frames - len(multi.frames_for_rank(n_frames, 0, world, mode_))) * frame_floats * 4
+                floor = remote / (NVLINK_INGEST_GBS * 1e9)
+                res.update(floor_seconds=floor, seconds_over_floor=sec / floor if floor > 0 else None,
+                           ingest_GB_s=remote / sec / 1e9,
+                           floor_note=f"bytes that must enter rank 0 ({remote / 1e9:.1f} GB) / {NVLINK_INGEST_GBS:.0f} GB/s NVLink ingest of one GPU")
+                if rank == 0:                        # the gathered frames are really there: spot-check one remote frame
+                    got = peer.tensor((n_frames, Cn, height, width)) if gather == "peer" else full
+                    res["checksum_last_frame"] = float(got[n_frames - 1].double().sum().item())
+            for o in (peer, comm):
+                if o is not None:
+                    o.close()
+            del full, staging, buf
+            torch.cuda.empty_cache()
+            return res
 
         sw = {}
-        sweep_bench("time_of_day", 1024, 512, 8, False)                     # warm-up: contexts, scratch, NCCL
-        sw["time_of_day_256x4096x2048_rgb"] = sweep_bench("time_of_day", 4096, 2048, 8, False)
-        sw["animation_128x8192x4096_spectral"] = sweep_bench("animation", 8192, 4096, 2, False)
+        sweep_bench("time_of_day", 1024, 512, 8, None)                      # warm-up: contexts, scratch
+        sw["time_of_day_256x4096x2048_rgb"] = sweep_bench("time_of_day", 4096, 2048, 8, None)
+        sw["animation_128x8192x4096_spectral"] = sweep_bench("animation", 8192, 4096, 2, None)
         if world > 1:
-            sweep_bench("time_of_day", 1024, 512, 8, True)
-            sw["time_of_day_256x4096x2048_rgb_gather"] = sweep_bench("time_of_day", 4096, 2048, 8, True)
-            sw["animation_128x8192x4096_spectral_gather"] = sweep_bench("animation", 8192, 4096, 2, True)
+            for how in ("peer", "nccl"):
+                sweep_bench("time_of_day", 1024, 512, 8, how)
+                sw[f"time_of_day_256x4096x2048_rgb_gather_{how}"] = sweep_bench("time_of_day", 4096, 2048, 8, how)
+                sw[f"animation_128x8192x4096_spectral_gather_{how}"] = sweep_bench("animation", 8192, 4096, 2, how)
+        L.ssk_sweep_release()
         sw["note"] = ("BASELINE configs[3] (64 sun elevations x 4 turbidities, RGB) and configs[4] (128-frame turbidity/albedo "
-                      "animation, spectral, wavelengths 440/520/600/680 nm); wall clock between barriers, max over ranks, "
-                      "includes setting up every frame's emitter (host interpolation + batched device quadrature, ssk_update_batch)")
-        extra["sweeps"] = sw
+                      "animation, spectral, wavelengths 440/520/600/680 nm); wall clock between barriers, max over ranks, includes "
+                      "setting up every frame's emitter (host interpolation + batched device quadrature). gather_peer: every rank's "
+                      "envmap kernels store straight into rank 0's IPC-mapped buffer over NVLink (no staging, no copy afterwards); "
+                      "gather_nccl: grouped ncclSend/ncclRecv on a second stream, double-buffered against the next chunk's kernels")
+        sweeps = sw
+
+    if not args.no_extra:
         extra["note"] = ("configs[1] inputs for eval/pdf (2^24 directions), configs[2] for sample_direction (2^26 samples, "
                          "t=6 a=0.5 eta=50.2deg; sky only = sampling_test.py). fp32_frac uses the algorithmic flops of SURVEY 8d.")
-        del out3, pdf, u, d, spdf, wgt
 
     # ---- CPU baseline: the reference's own CPU code on the box's host cores (rank 0, N = 1 only) -------
     cpu = None
@@ -442,18 +540,45 @@ def main():
             if ref_oracle.available():
                 cores = os.cpu_count() or 1
                 threads = min(cores, 64)
-                n_s = 1 << 22
-                r, dt = cpu_reference_rate(n_s, threads, True, flavour=0)
-                r1, dt1 = cpu_reference_rate(1 << 18, 1, True, flavour=0)
-                ra, dta = cpu_reference_rate(1 << 19, threads, True, flavour=1)
-                cpu = {"value": r, "unit": "Gevals/s", "cores": threads, "kind": "reference",
-                       "sample": f"{n_s} of the {N_EVAL} directions (same distribution), {dt:.1f} s, the reference's scalar_spectral "
-                                 f"variant on {threads} threads (its fastest CPU flavour buildable here); 1 thread: {r1 * 1e3:.3f} "
-                                 f"Mevals/s; array flavour (llvm_ad_* code path without the JIT) on {threads} threads: "
-                                 f"{ra * 1e3:.3f} Mevals/s; host has {cores} logical cores",
-                       "single_thread_value": r1, "array_variant_value": ra}
+                wi_h, wav_h = wi.cpu().numpy(), wav.cpu().numpy()
+                fl = cpu_flavours(wi_h, wav_h, threads)
+                best = max(("packet", "scalar"), key=lambda k: fl[k]["value"])
+                cpu = {"value": fl[best]["value"], "unit": "Gevals/s", "cores": threads, "kind": "reference",
+                       "sample": f"{fl[best]['lanes']} of the {N_EVAL} configs[1] directions, best of 2 ({fl[best]['seconds']:.2f} s), the "
+                                 f"reference's eval() on {'dr::Packet<float, %d> (%s)' % (fl['packet_width'], fl['isa']) if best == 'packet' else 'float'} "
+                                 f"over {threads} host threads (the faster of its two CPU flavours; host has {cores} logical cores)",
+                       "scalar_value": fl["scalar"]["value"], "scalar_single_thread_value": fl["scalar"]["single_thread_value"],
+                       "packet_value": fl["packet"]["value"], "packet_single_thread_value": fl["packet"]["single_thread_value"],
+                       "isa": fl["isa"], "packet_width": fl["packet_width"]}
+                # BASELINE configs[0]: scalar_rgb eval over the 512 x 256 lat-long grid of test_sunsky.py:93-100 (t=3, a=0.3,
+                # sun elevation 30 deg), one host thread; and the same grid on the GPU, compared with the reference's output
+                grid = common.latlong_grid(512, 256)
+                r0 = ref_oracle.RefEmitter(spectral=False, flavour=0, **kw)
+                r0.eval(grid[:, :1024].copy())
+                t_best = 1e30
+                for _ in range(3):
+                    t0 = time.perf_counter(); ref0 = r0.eval(grid); t_best = min(t_best, time.perf_counter() - t0)
+                e0 = ssk.SunskyEmitter(spectral=False, device=local, arith="exact", **kw)
+                g_t = torch.tensor(grid, device=dev)
+                o_t = torch.empty((3, grid.shape[1]), device=dev)
+                g_pp, o_pp = planes(g_t), planes(o_t)
+
+                def step_grid():
+                    assert L.ssk_eval_device(e0._ctx, g_pp, None, grid.shape[1], o_pp, stream) == 0
+                ms_g, _ = timed(step_grid, 50, 5)
+                ref1 = ref_oracle.RefEmitter(spectral=False, flavour=1, **kw).eval(grid)
+                got = o_t.cpu().numpy()
+                nz = ref0 != 0
+                extra["configs0_scalar_rgb_latlong_512x256"] = {
+                    "rays": int(grid.shape[1]),
+                    "reference_scalar_rgb_1_thread_ms": t_best * 1e3, "reference_Mevals_s": grid.shape[1] / t_best / 1e6,
+                    "gpu_exact_ms": ms_g / 50, "gpu_Mevals_s": grid.shape[1] / (ms_g / 50 * 1e-3) / 1e6,
+                    "gpu_bit_identical_to_array_flavour": bool(np.array_equal(got.view(np.uint32), ref1.view(np.uint32))),
+                    "gpu_vs_scalar_flavour_max_rel": float((np.abs(got[nz] - ref0[nz]) / np.abs(ref0[nz])).max()),
+                    "note": "the GPU figure is launch-latency bound (131072 rays = 0.4 waves); parity is against both reference flavours"}
+                e0.close()
         except Exception as ex:  # the baseline is reported, never required
-            cpu = {"error": str(ex)}
+            cpu = {"error": repr(ex)}
 
     sampler.stop()
     clocks = sampler.summary(headline_window)
@@ -463,14 +588,13 @@ def main():
         print(json.dumps({
             "metric": METRIC, "value": value, "unit": "Gevals/s", "n_gpus": world, "steps": args.steps,
             "warmup": warm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD,
-                       "l2": "inputs (470 MB/step) exceed the 126 MB L2; no flush needed",
-                       "arith": args.arith + (" (MUFU transcendentals for well-conditioned terms, within 1e-5 of the reference; "
-                                              "directions bit-identical)" if args.arith == "fast" else
-                                              " (reference op order, bit-identical results)")},
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic (PCG32 streams, SURVEY.md 8d cfg 2)",
+            "config": CONFIG,
+            "arith": args.arith + (" (MUFU transcendentals for well-conditioned terms, within 1e-5 of the reference; "
+                                   "directions bit-identical)" if args.arith == "fast" else
+                                   " (reference op order, bit-identical results)"),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "extra": extra,
+            "sweeps": sweeps, "extra": extra,
         }))
     if world > 1:
         dist.destroy_process_group()

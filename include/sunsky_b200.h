@@ -216,9 +216,84 @@ int ssk_sample_ray_host(const ssk_ctx *ctx, const float *wl_sample, const float 
                         size_t n, float *const o[3], float *const d[3], float *const wavelengths[4],
                         float *const weight[4]);
 
+/* ---- multi-GPU (one 8 x B200 box) -----------------------------------------------------------------------
+ * The reference has no multi-device layer (no NCCL / MPI under src/ or include/). Rays, samples and pixels are
+ * independent given the 17 KB emitter block, which every GPU builds for itself: query batches shard as contiguous
+ * ray ranges, env-map sweeps as whole frames, with NO data-path collective. The one optional exchange is collecting
+ * finished frames on one GPU. These entry points serve both deployment shapes: one process per GPU (bench.py under
+ * torchrun; handles and ids travel through any host channel) and one process driving all GPUs (ssk_group_*). */
+#define SSK_SHARD_BLOCKED      0   /* consecutive frames per GPU (configs[3]: 256 maps, 32 per GPU) */
+#define SSK_SHARD_ROUND_ROBIN  1   /* frame f on GPU f % world (configs[4]: animations of any length stay balanced) */
+#define SSK_PEER_HANDLE_BYTES  64
+#define SSK_COMM_ID_BYTES      128
+
+const char *ssk_multi_last_error(void);
+
+/* [begin, end) of an n-ray batch for `rank`: boundaries are multiples of `align` rays (planes stay 16-byte aligned
+ * with align = 4), the last rank takes the ragged tail, shards differ by at most `align` rays. */
+int ssk_shard_ray_range(size_t n, int rank, int world, size_t align, size_t *begin, size_t *end);
+/* Frame indices rendered by `rank` (frames may be NULL to query the count). */
+int ssk_shard_frames(int n_frames, int rank, int world, int mode, int *frames, int *count);
+
+/* Frame buffers other GPUs can store into. ssk_peer_alloc: device memory on `device` plus (handle != NULL) an
+ * inter-process handle for it; ssk_peer_open maps such a buffer into another process on `device` and enables peer
+ * access, so that kernels there -- ssk_envmap_device / ssk_sweep_render with `out` pointing into the mapping --
+ * write their pixels straight into the owner's HBM over NVLink: the gather happens inside the kernel that computes
+ * the frame, nothing is staged or copied afterwards. */
+int ssk_peer_alloc(int device, size_t bytes, void **ptr, unsigned char handle[SSK_PEER_HANDLE_BYTES]);
+int ssk_peer_open(int device, const unsigned char handle[SSK_PEER_HANDLE_BYTES], void **ptr);
+int ssk_peer_close(int device, void *ptr);
+int ssk_peer_free(int device, void *ptr);
+
+/* BASELINE configs[3] / [4]: n_frames emitters (full property sets, same mode and arith), one equirectangular map
+ * each (pixel convention of ssk_envmap_device) into out[f] (device memory, local or peer-mapped). Emitter contexts
+ * are pooled per (device, mode) and re-parametrised `chunk` at a time (ssk_update_batch); the setup of one chunk
+ * overlaps the kernels of the previous one. wavelengths4: 4 per frame (spectral). Enqueued on `stream`. */
+int ssk_sweep_render(const ssk_params *frames, int n_frames, const char *dataset_dir, int device, int mode,
+                     int width, int height, const float *wavelengths4, float *const *out, int chunk, void *stream);
+void ssk_sweep_release(void);      /* destroys the pooled contexts */
+
+/* The optional NCCL gather of the north star. libnccl.so.2 is loaded at run time (the copy already in the process
+ * if there is one). The 128-byte id comes from ssk_comm_unique_id on one rank and reaches the others through any
+ * host channel. ssk_comm_gather_frames: frames first .. first + count - 1 of every rank's list (ssk_shard_frames
+ * order; `local` holds exactly those) to their final place in `full` on `root`, one grouped ncclSend / ncclRecv
+ * launch. ssk_sweep_render_gather_nccl: the sweep with that gather running on a second stream, double-buffered
+ * against the next chunk's kernels (staging = 2 * chunk frames). */
+typedef struct ssk_comm ssk_comm;
+int  ssk_comm_unique_id(unsigned char id[SSK_COMM_ID_BYTES]);
+int  ssk_comm_create(const unsigned char id[SSK_COMM_ID_BYTES], int rank, int world, int device, ssk_comm **out);
+void ssk_comm_destroy(ssk_comm *c);
+int  ssk_comm_version(void);
+int  ssk_comm_gather_frames(ssk_comm *c, const float *local, size_t frame_floats, int n_frames, int shard_mode, int first,
+                            int count, float *full, int root, void *stream);
+int  ssk_sweep_render_gather_nccl(ssk_comm *c, const ssk_params *frames, int n_frames_total, int shard_mode,
+                                  const char *dataset_dir, int mode, int width, int height, const float *wavelengths4,
+                                  float *staging, float *full, int root, int chunk, void *stream);
+
+/* One process, N GPUs: a context per device built from the same properties, one host thread per device inside each
+ * call. Query batches are split with ssk_shard_ray_range (align 4); sweeps with ssk_shard_frames. For a gathered
+ * sweep every out[f] lives on one GPU and the others store into it through peer access (enabled at creation). */
+typedef struct ssk_group ssk_group;
+int  ssk_group_create(const int *devices, int n_devices, const ssk_params *p, const char *dataset_dir, int mode, ssk_group **out);
+void ssk_group_destroy(ssk_group *g);
+int  ssk_group_size(const ssk_group *g);
+ssk_ctx *ssk_group_context(const ssk_group *g, int i);
+int  ssk_group_update(ssk_group *g, const ssk_params *p);
+int  ssk_group_eval_host(const ssk_group *g, const float *const wi[3], const float *const wavelengths[4], size_t n,
+                         float *const out[4]);
+int  ssk_group_sample_direction_host(const ssk_group *g, const float *const u[2], const float *const wavelengths[4], size_t n,
+                                     float *const d[3], float *pdf, float *const weight[4]);
+int  ssk_group_sweep(const ssk_group *g, const ssk_params *frames, int n_frames, int shard_mode, int width, int height,
+                     const float *wavelengths4, float *const *out, int chunk);
+
 /* Test hook: out[i] = a[i] / b[i] computed with the reciprocal-based division the kernels use for
  * per-emitter constant divisors (device pointers); the tests compare it with IEEE division. */
 int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t n, void *stream);
+
+/* Measurement aid: the time the bare transfers of a *_host call take with nothing else in the way -- h2d_bytes from
+ * pinned host memory on one stream while d2h_bytes go back on another, in pieces of piece_bytes (0 = one copy per
+ * direction), best of `reps` after a warm-up. bench.py reports the *_host entry points against this ceiling. */
+int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds);
 
 /* Number of kernel launches issued through this library since load (bench bookkeeping). */
 uint64_t ssk_launch_count(void);

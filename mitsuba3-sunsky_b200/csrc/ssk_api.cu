@@ -534,7 +534,24 @@ bool is_pinned(const void *p) {
     return at.type == cudaMemoryTypeHost;
 }
 
+/// Planes k = 0..n-1 start at equal byte distances (views of one (n, N) array): one strided copy moves all of them
+template <typename P> bool equally_spaced(P *const *planes, int n, ptrdiff_t *stride_bytes) {
+    if (n < 2) { *stride_bytes = 0; return n == 1; }
+    const ptrdiff_t d = reinterpret_cast<const char *>(planes[1]) - reinterpret_cast<const char *>(planes[0]);
+    if (d <= 0) return false;
+    for (int k = 2; k < n; ++k)
+        if (reinterpret_cast<const char *>(planes[k]) - reinterpret_cast<const char *>(planes[k - 1]) != d) return false;
+    *stride_bytes = d;
+    return true;
+}
+
 /// Generic pipeline: `n_in` input planes, `n_out` output planes, `launch(dev_in[], dev_out[], m, stream)`.
+/// The batch moves in chunks over `active` slots, each slot a stream with its own device staging: H2D, kernel and
+/// D2H of one chunk are ordered on the slot's stream, chunks of different slots overlap (the two copy engines run
+/// H2D of one chunk while another chunk's results go back). Pinned caller buffers (the drop-in case: Dr.Jit and
+/// torch hand over pinned or device memory) need no host-side synchronisation until the end; planes that are views
+/// of one array travel as ONE strided copy per chunk and direction (cudaMemcpy2DAsync, rows = planes) instead of one
+/// copy per plane. Pageable buffers go through the slot's pinned staging with a host memcpy on either side.
 template <typename Launch>
 int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *const *out, int n_out, size_t n,
                   Launch &&launch) {
@@ -547,6 +564,10 @@ int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *c
     bool pin_in = true, pin_out = true;
     for (int k = 0; k < n_in; ++k) pin_in = pin_in && is_pinned(in[k]);
     for (int k = 0; k < n_out; ++k) pin_out = pin_out && is_pinned(out[k]);
+    static const bool no_2d = getenv("SSK_HOST_NO_2D") != nullptr;
+    ptrdiff_t in_stride = 0, out_stride = 0;
+    const bool in_2d = !no_2d && pin_in && n_in > 1 && equally_spaced(in, n_in, &in_stride);
+    const bool out_2d = !no_2d && pin_out && n_out > 1 && equally_spaced(out, n_out, &out_stride);
     const size_t n_chunks = (n + chunk - 1) / chunk;
     // pending[i]: chunk index whose results still sit in staging slot i (pageable outputs only)
     std::vector<long long> pending(Staging::kStreams, -1);
@@ -562,28 +583,38 @@ int host_pipeline(const ssk_ctx *ctx, const float *const *in, int n_in, float *c
         pending[slot] = -1;
         return SSK_OK;
     };
+    const bool host_sync = !(pin_in && pin_out);          // pinned on both sides: stream order is all the ordering needed
     for (size_t ci = 0; ci < n_chunks; ++ci) {
         int slot = (int) (ci % n_slots);
-        if (int rc = drain(slot)) return rc;
+        if (host_sync) if (int rc = drain(slot)) return rc;
         size_t off = ci * chunk, m = std::min(chunk, n - off);
         cudaStream_t s = st.stream[slot];
         const float *din[16]; float *dout[16];
-        for (int k = 0; k < n_in; ++k) {
-            float *dst = st.dev[slot] + (size_t) k * chunk;
-            const float *src = in[k] + off;
-            if (!pin_in) {
-                float *stage = st.pinned[slot] + (size_t) k * chunk;
-                memcpy(stage, src, m * sizeof(float));
-                src = stage;
-            }
-            SSK_CUDA(cudaMemcpyAsync(dst, src, m * sizeof(float), cudaMemcpyHostToDevice, s));
-            din[k] = dst;
-        }
+        for (int k = 0; k < n_in; ++k) din[k] = st.dev[slot] + (size_t) k * chunk;
         for (int k = 0; k < n_out; ++k) dout[k] = st.dev[slot] + (size_t) (n_in + k) * chunk;
+        if (in_2d) {
+            SSK_CUDA(cudaMemcpy2DAsync(st.dev[slot], chunk * sizeof(float), in[0] + off, (size_t) in_stride,
+                                       m * sizeof(float), n_in, cudaMemcpyHostToDevice, s));
+        } else {
+            for (int k = 0; k < n_in; ++k) {
+                const float *src = in[k] + off;
+                if (!pin_in) {
+                    float *stage = st.pinned[slot] + (size_t) k * chunk;
+                    memcpy(stage, src, m * sizeof(float));
+                    src = stage;
+                }
+                SSK_CUDA(cudaMemcpyAsync(const_cast<float *>(din[k]), src, m * sizeof(float), cudaMemcpyHostToDevice, s));
+            }
+        }
         if (int rc = launch(din, dout, m, s)) return rc;
-        for (int k = 0; k < n_out; ++k) {
-            float *dst = pin_out ? out[k] + off : st.pinned[slot] + (size_t) (n_in + k) * chunk;
-            SSK_CUDA(cudaMemcpyAsync(dst, dout[k], m * sizeof(float), cudaMemcpyDeviceToHost, s));
+        if (out_2d) {
+            SSK_CUDA(cudaMemcpy2DAsync(out[0] + off, (size_t) out_stride, dout[0], chunk * sizeof(float),
+                                       m * sizeof(float), n_out, cudaMemcpyDeviceToHost, s));
+        } else {
+            for (int k = 0; k < n_out; ++k) {
+                float *dst = pin_out ? out[k] + off : st.pinned[slot] + (size_t) (n_in + k) * chunk;
+                SSK_CUDA(cudaMemcpyAsync(dst, dout[k], m * sizeof(float), cudaMemcpyDeviceToHost, s));
+            }
         }
         pending[slot] = (long long) ci;
     }
@@ -882,6 +913,40 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
     fdiv_by_kernel<<<1184, 256, 0, (cudaStream_t) stream>>>(a, b, out, n);
     g_launches++;
     SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
+int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds) {
+    if (!best_seconds || reps < 1) return fail(SSK_ERR_INVALID, "bad argument");
+    DeviceGuard dg; if (int rc = dg.enter(device)) return rc;
+    char *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
+    cudaStream_t s0 = nullptr, s1 = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
+    auto cleanup = [&] {
+        if (h_in) cudaFreeHost(h_in); if (h_out) cudaFreeHost(h_out); if (d_in) cudaFree(d_in); if (d_out) cudaFree(d_out);
+        if (s0) cudaStreamDestroy(s0); if (s1) cudaStreamDestroy(s1);
+        if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); if (e2) cudaEventDestroy(e2);
+    };
+    struct Final { decltype(cleanup) &f; ~Final() { f(); } } fin{ cleanup };
+    if (h2d_bytes) { SSK_CUDA(cudaMallocHost(&h_in, h2d_bytes)); SSK_CUDA(cudaMalloc(&d_in, h2d_bytes)); memset(h_in, 1, h2d_bytes); }
+    if (d2h_bytes) { SSK_CUDA(cudaMallocHost(&h_out, d2h_bytes)); SSK_CUDA(cudaMalloc(&d_out, d2h_bytes)); SSK_CUDA(cudaMemset(d_out, 2, d2h_bytes)); }
+    SSK_CUDA(cudaStreamCreateWithFlags(&s0, cudaStreamNonBlocking));
+    SSK_CUDA(cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking));
+    SSK_CUDA(cudaEventCreate(&e0)); SSK_CUDA(cudaEventCreate(&e1)); SSK_CUDA(cudaEventCreate(&e2));
+    if (!piece_bytes) piece_bytes = std::max(h2d_bytes, d2h_bytes);
+    double best = 1e30;
+    for (int r = 0; r < reps + 1; ++r) {                       // first pass is a warm-up
+        SSK_CUDA(cudaDeviceSynchronize());
+        auto t0 = std::chrono::steady_clock::now();
+        for (size_t o = 0; o < h2d_bytes; o += piece_bytes)
+            SSK_CUDA(cudaMemcpyAsync(d_in + o, h_in + o, std::min(piece_bytes, h2d_bytes - o), cudaMemcpyHostToDevice, s0));
+        for (size_t o = 0; o < d2h_bytes; o += piece_bytes)
+            SSK_CUDA(cudaMemcpyAsync(h_out + o, d_out + o, std::min(piece_bytes, d2h_bytes - o), cudaMemcpyDeviceToHost, s1));
+        SSK_CUDA(cudaStreamSynchronize(s0)); SSK_CUDA(cudaStreamSynchronize(s1));
+        double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (r > 0) best = std::min(best, dt);
+    }
+    *best_seconds = best;
     return SSK_OK;
 }
 

@@ -76,13 +76,42 @@ SYMBOLS = {
     "ssk_pdf_direction_host": (C.c_int, [CTX, FPP, C.c_size_t, FP]),
     "ssk_sample_direction_host": (C.c_int, [CTX, FPP, FPP, FPP, C.c_size_t, FPP, FP, FPP, FPP, FP]),
     "ssk_launch_count": (C.c_uint64, []),
+    "ssk_host_copy_ceiling": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
     "ssk_debug_fdiv_by_device": (C.c_int, [FP, FP, FP, C.c_size_t, C.c_void_p]),
     "ssk_sun_coordinates": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                       C.c_float, C.c_float, FP]),
     "ssk_array_from_file": (C.c_int, [C.c_char_p, C.c_int, FP, C.c_size_t, C.POINTER(C.c_size_t),
                                       C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "ssk_array_to_file": (C.c_int, [C.c_char_p, FP, C.POINTER(C.c_size_t), C.c_size_t, C.c_int]),
+    # ---- multi-GPU
+    "ssk_multi_last_error": (C.c_char_p, []),
+    "ssk_shard_ray_range": (C.c_int, [C.c_size_t, C.c_int, C.c_int, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "ssk_shard_frames": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "ssk_peer_alloc": (C.c_int, [C.c_int, C.c_size_t, C.POINTER(C.c_void_p), C.c_char_p]),
+    "ssk_peer_open": (C.c_int, [C.c_int, C.c_char_p, C.POINTER(C.c_void_p)]),
+    "ssk_peer_close": (C.c_int, [C.c_int, C.c_void_p]),
+    "ssk_peer_free": (C.c_int, [C.c_int, C.c_void_p]),
+    "ssk_sweep_render": (C.c_int, [C.POINTER(Params), C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, FP, FPP,
+                                   C.c_int, C.c_void_p]),
+    "ssk_sweep_release": (None, []),
+    "ssk_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "ssk_comm_create": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "ssk_comm_destroy": (None, [C.c_void_p]),
+    "ssk_comm_version": (C.c_int, []),
+    "ssk_comm_gather_frames": (C.c_int, [C.c_void_p, FP, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, FP, C.c_int, C.c_void_p]),
+    "ssk_sweep_render_gather_nccl": (C.c_int, [C.c_void_p, C.POINTER(Params), C.c_int, C.c_int, C.c_char_p, C.c_int, C.c_int,
+                                               C.c_int, FP, FP, FP, C.c_int, C.c_int, C.c_void_p]),
+    "ssk_group_create": (C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(Params), C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "ssk_group_destroy": (None, [C.c_void_p]),
+    "ssk_group_size": (C.c_int, [C.c_void_p]),
+    "ssk_group_context": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "ssk_group_update": (C.c_int, [C.c_void_p, C.POINTER(Params)]),
+    "ssk_group_eval_host": (C.c_int, [C.c_void_p, FPP, FPP, C.c_size_t, FPP]),
+    "ssk_group_sample_direction_host": (C.c_int, [C.c_void_p, FPP, FPP, C.c_size_t, FPP, FP, FPP]),
+    "ssk_group_sweep": (C.c_int, [C.c_void_p, C.POINTER(Params), C.c_int, C.c_int, C.c_int, C.c_int, FP, FPP, C.c_int]),
 }
+SHARD_BLOCKED, SHARD_ROUND_ROBIN = 0, 1
+PEER_HANDLE_BYTES, COMM_ID_BYTES = 64, 128
 # not in the public header: test hook for the pixel -> direction convention of ssk_envmap_device
 EXTRA_SYMBOLS = {
     "ssk_envmap_directions_device": (C.c_int, [CTX, C.c_int, C.c_int, FPP, C.c_void_p]),

@@ -20,34 +20,23 @@ def world():
 
 
 def ray_range(n, rank, world_size, align=4):
-    """Contiguous [begin, end) of an n-ray batch for `rank`. Boundaries are multiples of `align` rays so that
-    every shard's planes stay 16-byte aligned (128-bit kernel variant); the last rank takes the ragged tail.
-    Shards differ by at most `align` rays; empty shards (n < world_size * align) are legal."""
-    if world_size < 1 or not (0 <= rank < world_size):
-        raise ValueError(f"bad rank {rank} for world size {world_size}")
+    """Contiguous [begin, end) of an n-ray batch for `rank` (ssk_shard_ray_range). Boundaries are multiples of
+    `align` rays so that every shard's planes stay 16-byte aligned (128-bit kernel variant); the last rank takes the
+    ragged tail. Shards differ by at most `align` rays; empty shards (n < world_size * align) are legal."""
+    from . import multi
     if n < 0 or align < 1:
         raise ValueError("n must be >= 0 and align >= 1")
-    units = n // align                       # whole aligned groups
-    base, extra = divmod(units, world_size)
-    begin_u = rank * base + min(rank, extra)
-    end_u = begin_u + base + (1 if rank < extra else 0)
-    begin, end = begin_u * align, end_u * align
-    if rank == world_size - 1:
-        end = n
-    return begin, end
+    return multi.ray_range(n, rank, world_size, align)
 
 
 def frames_for_rank(n_frames, rank, world_size, mode="round_robin"):
-    """Frame / map indices rendered by `rank`. round_robin: f % world == rank (config 5: an animation stays
-    load-balanced however long it is); blocked: consecutive maps (config 4: 256 maps, 32 per GPU)."""
-    if world_size < 1 or not (0 <= rank < world_size):
-        raise ValueError(f"bad rank {rank} for world size {world_size}")
-    if mode == "round_robin":
-        return list(range(rank, n_frames, world_size))
-    if mode == "blocked":
-        b, e = ray_range(n_frames, rank, world_size, align=1)
-        return list(range(b, e))
-    raise ValueError("mode must be 'round_robin' or 'blocked'")
+    """Frame / map indices rendered by `rank` (ssk_shard_frames). round_robin: f % world == rank (config 5: an
+    animation stays load-balanced however long it is); blocked: consecutive maps (config 4: 256 maps, 32 per GPU)."""
+    from . import multi
+    if mode not in ("round_robin", "blocked"):
+        raise ValueError("mode must be 'round_robin' or 'blocked'")
+    return multi.frames_for_rank(n_frames, rank, world_size,
+                                 multi.SHARD_ROUND_ROBIN if mode == "round_robin" else multi.SHARD_BLOCKED)
 
 
 def owner_of_frame(f, n_frames, world_size, mode="round_robin"):

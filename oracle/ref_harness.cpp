@@ -223,7 +223,8 @@ struct RefBase {
     virtual void update(const ssk_ref_params &p) = 0;
     virtual void state(ssk_ref_state &s) const = 0;
     virtual void set_scene(const float *bmin, const float *bmax) = 0;
-    virtual void eval(size_t n, const float *wi, const float *wav, float *out) const = 0;
+    /// planes are `stride` floats apart (stride >= n): threads work in place on slices of the caller's arrays
+    virtual void eval(size_t n, const float *wi, const float *wav, float *out, size_t stride = 0) const = 0;
     virtual void sample_direction(size_t n, const float *u, const float *itp, const float *wav, float *d,
                                   float *pdf, float *weight, float *p, float *dist) const = 0;
     virtual void pdf_direction(size_t n, const float *d, float *pdf) const = 0;
@@ -398,14 +399,15 @@ template <typename Float, typename Spectrum> struct RefImpl final : RefBase {
         return w;
     }
 
-    void eval(size_t n, const float *wi, const float *wav, float *out) const override {
+    void eval(size_t n, const float *wi, const float *wav, float *out, size_t stride) const override {
+        const size_t S = stride ? stride : n;
+        SurfaceInteraction3f si = dr::zeros<SurfaceInteraction3f>();
         for (size_t off = 0; off < n; off += Chunk) {
             size_t m = std::min(Chunk, n - off);
-            SurfaceInteraction3f si = dr::zeros<SurfaceInteraction3f>();
-            si.wi = Vector3f(load_f<Float>(wi, off, m), load_f<Float>(wi + n, off, m), load_f<Float>(wi + 2 * n, off, m));
-            si.wavelengths = load_wav(wav, n, off, m);
+            si.wi = Vector3f(load_f<Float>(wi, off, m), load_f<Float>(wi + S, off, m), load_f<Float>(wi + 2 * S, off, m));
+            si.wavelengths = load_wav(wav, S, off, m);
             Spectrum r = em->eval(si, Mask(true));
-            for (int c = 0; c < C; ++c) store_f<Float>(out + c * n, off, m, r[c]);
+            for (int c = 0; c < C; ++c) store_f<Float>(out + c * S, off, m, r[c]);
         }
     }
 
@@ -533,14 +535,10 @@ int ssk_ref_eval(void *h, size_t n, const float *wi, const float *wav, float *ou
     int C = r->channels();
     return guarded([&] {
         if (threads <= 1) { r->eval(n, wi, wav, out); return; }
-        // threads work on private contiguous copies so that the SoA stride stays per-slice
+        // static partition; every thread reads and writes its slice of the caller's planes in place
+        (void) C;
         parallel_ranges(n, threads, [&](size_t b, size_t e) {
-            size_t m = e - b;
-            std::vector<float> in(3 * m), wv(wav ? 4 * m : 0), o((size_t) C * m);
-            for (int c = 0; c < 3; ++c) memcpy(&in[c * m], wi + c * n + b, m * 4);
-            if (wav) for (int c = 0; c < 4; ++c) memcpy(&wv[c * m], wav + c * n + b, m * 4);
-            r->eval(m, in.data(), wav ? wv.data() : nullptr, o.data());
-            for (int c = 0; c < C; ++c) memcpy(out + c * n + b, &o[c * m], m * 4);
+            r->eval(e - b, wi + b, wav ? wav + b : nullptr, out + b, n);
         });
     });
 }
