@@ -302,6 +302,10 @@ uint64_t ssk_launch_count(void);
 /* compute_sun_coordinates (sunsky.h:283-374): date/time/location -> local sun direction */
 int ssk_sun_coordinates(int year, int month, int day, float hour, float minute, float second,
                         float latitude, float longitude, float timezone, float out_dir[3]);
+/* dr::normalize as the constructor applies it to the sun_direction property (sunsky.cpp:922), same rounding.
+ * parameters_changed() does NOT normalise (the reference works on m_sun_dir as stored), so a caller that feeds a raw
+ * property to ssk_update and wants constructor semantics normalises it with this first; ssk_sweep_render does. */
+int ssk_normalize_direction(const float in[3], float out[3]);
 /* array_from_file (sunsky.h:515-561): reads a dataset as fp32. *count receives the element count;
  * shape (nullable) receives up to 8 dims, *ndim their number. `out` may be NULL to query sizes. */
 int ssk_array_from_file(const char *path, int file_is_f64, float *out, size_t capacity, size_t *count,

@@ -223,11 +223,32 @@ int need_device(const ssk_ctx *ctx, DeviceGuard &dg) {
 const HotBlock &hot(const ssk_ctx *ctx) { return ctx->E.block; }
 bool fast(const ssk_ctx *ctx) { return ctx->E.block.arith == kFast; }
 
+/// spectral eval with the inputs staged by the TMA (every input plane 16-byte aligned). Opt-in (SSK_EVAL_TMA=1):
+/// measured on B200 it runs at 53.4-54.0 Gevals/s against 54.7 for the register-prefetch kernel -- the ring itself
+/// sustains 6.5 TB/s on this 7-in / 4-out plane pattern (profiles/ubench/stream_probe.cu), but the kernel is bound by
+/// its dependency chains at ~62-66 % issue utilisation, not by its loads (profiles/r2_summary.md)
+template <int A>
+int launch_eval_spec_tma(const ssk_ctx *ctx, const Planes3 &i3, const Planes4 &w4, float *const out[4], size_t n,
+                         float dir_sign, cudaStream_t s) {
+    int per_sm = 0;
+    SSK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, eval_spec_tma_kernel<A>, kThreads, 0));
+    if (per_sm < 1) per_sm = 1;
+    const size_t tiles = (n + kThreads - 1) / kThreads;
+    const int grid = (int) std::max<size_t>(1, std::min(tiles, (size_t) ctx->sm_count * per_sm));
+    OutPlanes4 o4 = { out[0], out[1], out[2], out[3] };
+    eval_spec_tma_kernel<A><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, w4, o4, n, dir_sign);
+    return SSK_OK;
+}
+
 template <int A, int R>
 int launch_eval_t(const ssk_ctx *ctx, bool spectral, const Planes3 &i3, const Planes4 &w4, float *const out[4], size_t n,
                   float dir_sign, cudaStream_t s) {
     int grid = 1;
     if (spectral) {
+        static const bool use_tma = getenv("SSK_EVAL_TMA") != nullptr;
+        if (R == 1 && use_tma && aligned16(i3.x) && aligned16(i3.y) && aligned16(i3.z) && aligned16(w4.a) && aligned16(w4.b) &&
+            aligned16(w4.c) && aligned16(w4.d))
+            return launch_eval_spec_tma<A>(ctx, i3, w4, out, n, dir_sign, s);
         OutPlanes4 o4 = { out[0], out[1], out[2], out[3] };
         if (int rc = occupancy_grid(ctx, eval_spec_kernel<A, R>, n, &grid, R)) return rc;
         eval_spec_kernel<A, R><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, i3, w4, o4, n, dir_sign);
@@ -1122,6 +1143,13 @@ int ssk_sun_coordinates(int year, int month, int day, float hour, float minute, 
     Location loc = { latitude, longitude, timezone };
     Vec3 v = sun_coordinates(dt, loc);
     out_dir[0] = v.x; out_dir[1] = v.y; out_dir[2] = v.z;
+    return SSK_OK;
+}
+
+int ssk_normalize_direction(const float in[3], float out[3]) {
+    if (!in || !out) return fail(SSK_ERR_INVALID, "null argument");
+    Vec3 v = normalize_sun_direction({ in[0], in[1], in[2] });
+    out[0] = v.x; out[1] = v.y; out[2] = v.z;
     return SSK_OK;
 }
 

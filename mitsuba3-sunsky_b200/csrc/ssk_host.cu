@@ -31,6 +31,13 @@ void validate_params(const ssk_params &p, bool spectral) {
     }
 }
 
+/// dr::normalize on a ScalarVector3f (sunsky.cpp:922): v * rsqrt(sum(v * v)); the 3-wide horizontal sum adds
+/// (x^2 + z^2) + y^2 (drjit/packet_sse42.h:1659-1666) and a scalar rsqrt is 1 / sqrt (drjit/array_utils.h:213-219)
+Vec3 normalize_sun_direction(const Vec3 &v) {
+    float inv = 1.f / sqrtf((v.x * v.x + v.z * v.z) + v.y * v.y);
+    return { v.x * inv, v.y * inv, v.z * inv };
+}
+
 static void mat3_from_4x4(const float *m16, float *m9) {
     for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) m9[r * 3 + c] = m16[r * 4 + c];
 }
@@ -162,11 +169,7 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
     } else {
         Vec3 v = { p.sun_direction[0], p.sun_direction[1], p.sun_direction[2] };
         if (!(p.flags & SSK_FLAG_SUN_DIR_NORMALIZED) && from_constructor) {
-            // dr::normalize on a ScalarVector3f (sunsky.cpp:922): v * rsqrt(sum(v * v)); the 3-wide horizontal sum
-            // adds (x^2 + z^2) + y^2 (drjit/packet_sse42.h:1659-1666) and a scalar rsqrt is 1 / sqrt
-            // (drjit/array_utils.h:213-219)
-            float inv = 1.f / sqrtf((v.x * v.x + v.z * v.z) + v.y * v.y);
-            v = { v.x * inv, v.y * inv, v.z * inv };
+            v = normalize_sun_direction(v);
         }
         E.sun_dir_world = v;
         local_sun = xform(B.to_local, v);
@@ -212,9 +215,18 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
         const float *A = &E.sky_params[c * 9];
         const double log2e = 1.4426950408889634074;
         const double norm = E.spectral ? 1.0 : 1.0 / 106.7502593994140625;
-        const float fast[kFastCoefs] = { A[0], A[1], A[2], A[3], (float) ((double) A[4] * log2e),
+        // c1 coefficients per SSK_C1_MODE (c1_fast in ssk_model.cuh)
+#if SSK_C1_MODE == 0
+        const float t0 = A[0], t1 = A[1], t11 = 0.f;
+#elif SSK_C1_MODE == 1
+        const float t0 = A[0], t1 = (float) ((double) A[1] * log2e), t11 = 0.f;
+#else
+        const float t0 = A[0] < 0.f ? -1.f : (A[0] > 0.f ? 1.f : 0.f), t1 = A[1],
+                    t11 = A[0] != 0.f ? (float) log(fabs((double) A[0])) : -1e30f;
+#endif
+        const float fast[kFastCoefs] = { t0, t1, A[2], A[3], (float) ((double) A[4] * log2e),
                                          A[5], A[6], A[7], 1.f + A[8] * A[8], 2.f * A[8],
-                                         (float) ((double) E.sky_radiance[c] * (double) p.sky_scale * norm) };
+                                         (float) ((double) E.sky_radiance[c] * (double) p.sky_scale * norm), t11 };
         for (int k = 0; k < kFastCoefs; ++k) B.sky_fast[k][c] = fast[k];
     }
     for (int c = C; c < kChanPad; ++c) B.sky_fast[8][c] = 1.f;      // pad channels: keep the -3/2 power finite

@@ -281,6 +281,7 @@ struct HostEmitter {
 };
 
 void validate_params(const ssk_params &p, bool spectral);
+Vec3 normalize_sun_direction(const Vec3 &v);
 /// Computes the hemisphere integral of the sky and the cone integral of the sun per channel (x Jacobian) for an
 /// emitter whose block is complete except for the sampling weight; empty = quadrature_host
 using QuadratureFn = std::function<void(const HostEmitter &E, float sky_rad[11], float sun_rad[11])>;

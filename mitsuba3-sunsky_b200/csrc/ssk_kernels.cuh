@@ -48,6 +48,9 @@ constexpr int kThreads = 256;
 #ifndef SSK_SPECX_MINB
 #define SSK_SPECX_MINB 1
 #endif
+#ifndef SSK_SPECT_MINB
+#define SSK_SPECT_MINB 3           /* TMA-staged FAST spectral eval: resident CTAs per SM (4 = 64 registers, 8 bytes of spill) */
+#endif
 
 /// Copy the emitter block from global to shared memory (16-byte accesses) and, for FAST spectral
 /// kernels, build the bin-pair table of eval_spec (build_pair_table's layout). Ends with a barrier.
@@ -57,9 +60,9 @@ __device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const 
     for (int i = threadIdx.x; i < (int) (sizeof(HotBlock) / 16); i += blockDim.x) d[i] = __ldg(s + i);
     if (pairs)
         for (int i = threadIdx.x; i < kPairTable; i += blockDim.x) {
-            int c = i % kChanPad;
-            const float *row = &src->sky_fast[0][0] + (i - c);
-            pairs[i] = make_float2(__ldg(row + c), c + 1 < kChanPad ? __ldg(row + c + 1) : 0.f);
+            int c = i % kChanPad, k = i / kChanPad;
+            const float *row = &src->sky_fast[k][0];
+            pairs[pair_index(k, c)] = make_float2(__ldg(row + c), c + 1 < kChanPad ? __ldg(row + c + 1) : 0.f);
         }
     __syncthreads();
 }
@@ -213,6 +216,120 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
             setk<R>(o0, k, o[0]); setk<R>(o1, k, o[1]); setk<R>(o2, k, o[2]); setk<R>(o3, k, o[3]);
         }
         storer<R>(out.a, i, n, o0); storer<R>(out.b, i, n, o1); storer<R>(out.c, i, n, o2); storer<R>(out.d, i, n, o3);
+    }
+}
+
+// ---- TMA-staged input tiles ------------------------------------------------------------------------------------
+// Round-2 profile of eval_spec_kernel (profiles/r2_summary.md): the register-held software prefetch of the 7 input
+// planes spilled (80 registers at 3 CTAs / SM) and the spill store of a just-requested value waits for the load --
+// 34 % of all stall samples sat on one `STL` with long_scoreboard, and 28 IADD3 per ray went into 64-bit plane
+// addressing. Here the planes of a 256-ray tile are brought in by the TMA instead: one thread issues one 1 KB
+// cp.async.bulk per plane into a 3-stage shared-memory ring, completion is signalled on an mbarrier, the consumers
+// read their element with a fixed-offset LDS and release the stage with an mbarrier arrive. No registers are tied
+// up by data in flight, nothing stalls on a load, and the per-thread global address arithmetic of the inputs is gone.
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile("{\n"
+                 ".reg .pred p;\n"
+                 "SSK_WAIT:\n"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+                 "@p bra SSK_DONE;\n"
+                 "bra SSK_WAIT;\n"
+                 "SSK_DONE:\n"
+                 "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+/// 1-D bulk copy global -> shared (16-byte aligned on both sides, size a multiple of 16), completion on `bar`
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+constexpr int kTmaStages = 3;
+constexpr int kWarps = kThreads / 32;
+/// Ring of input tiles: P planes x kThreads floats per stage, one `full` mbarrier per stage. A stage is refilled by
+/// whichever warp releases it LAST (a shared-memory counter, one atomic per warp and tile): nobody ever waits for a
+/// stage to become free, and the ~100 instructions of issuing P bulk copies are paid by one warp in eight per tile.
+/// (Measured alternatives, profiles/r2_summary.md: thread 0 as fixed producer behind an `empty` mbarrier made every
+/// consumer spin whenever warp 0 ran late; one pipeline per warp cost +48 % instructions in copy issue.)
+template <int P> struct TileRing {
+    float data[kTmaStages][P][kThreads];
+    uint64_t full[kTmaStages];
+    int released[kTmaStages];
+};
+/// Issued by ONE thread: planes src[p] + tile * kThreads -> stage `s`
+template <int P> __device__ __forceinline__ void tile_issue(TileRing<P> &ring, int s, const float *const (&src)[P], size_t tile) {
+    mbar_expect_tx(&ring.full[s], P * kThreads * (uint32_t) sizeof(float));
+#pragma unroll
+    for (int p = 0; p < P; ++p)
+        tma_load_1d(&ring.data[s][p][0], src[p] + tile * kThreads, kThreads * (uint32_t) sizeof(float), &ring.full[s]);
+}
+template <int P> __device__ __forceinline__ void ring_init(TileRing<P> &ring) {
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kTmaStages; ++s) { mbar_init(&ring.full[s], 1); ring.released[s] = 0; }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+}
+/// Called by every thread after it has read its element of stage `s`: the last warp to get here refills the stage
+/// with tile `next` (if there is one)
+template <int P> __device__ __forceinline__ void ring_release(TileRing<P> &ring, int s, const float *const (&src)[P], size_t next, size_t n_tiles) {
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) {
+        __threadfence_block();
+        if (atomicAdd(&ring.released[s], 1) == kWarps - 1) {
+            ring.released[s] = 0;
+            __threadfence_block();
+            if (next < n_tiles) tile_issue(ring, s, src, next);
+        }
+    }
+}
+
+/// eval / eval_direction, spectral, one ray per thread, inputs through the TMA ring. Planes must be 16-byte
+/// aligned (the launch wrapper checks); the rays past the last full 256-ray tile are read with plain loads.
+template <int A>
+__global__ void __launch_bounds__(kThreads, A == kFast ? SSK_SPECT_MINB : 2)
+eval_spec_tma_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
+                     OutPlanes4 out, size_t n, float dir_sign) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
+    __shared__ __align__(128) TileRing<7> ring;
+    const float *const src[7] = { in.x, in.y, in.z, wav.a, wav.b, wav.c, wav.d };
+    const size_t n_tiles = n / kThreads;
+    ring_init(ring);
+    stage_block(&S, A == kFast ? pairs : nullptr, blk);          // ends with __syncthreads(): barriers are initialised
+    const float *sun_rad = blk->sun_rad;
+    if (threadIdx.x == 0)
+        for (int j = 0; j < kTmaStages; ++j) {
+            size_t t = (size_t) blockIdx.x + (size_t) j * gridDim.x;
+            if (t < n_tiles) tile_issue(ring, j, src, t);
+        }
+    uint32_t k = 0;
+    for (size_t t = blockIdx.x; t < n_tiles; t += gridDim.x, ++k) {
+        const int s = (int) (k % kTmaStages);
+        mbar_wait(&ring.full[s], (k / kTmaStages) & 1u);
+        const float (*d)[kThreads] = ring.data[s];
+        Vec3 wi = { dir_sign * d[0][threadIdx.x], dir_sign * d[1][threadIdx.x], dir_sign * d[2][threadIdx.x] };
+        float wl[4] = { d[3][threadIdx.x], d[4][threadIdx.x], d[5][threadIdx.x], d[6][threadIdx.x] }, o[4];
+        ring_release(ring, s, src, t + (size_t) kTmaStages * gridDim.x, n_tiles);
+        eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
+        const size_t i = t * kThreads + threadIdx.x;
+        __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]); __stcs(out.d + i, o[3]);
+    }
+    // ragged tail (n % 256 rays): the CTA whose turn the next tile would be
+    const size_t i = n_tiles * kThreads + threadIdx.x;
+    if (blockIdx.x == n_tiles % gridDim.x && i < n) {
+        Vec3 wi = { dir_sign * __ldcs(in.x + i), dir_sign * __ldcs(in.y + i), dir_sign * __ldcs(in.z + i) };
+        float wl[4] = { __ldcs(wav.a + i), __ldcs(wav.b + i), __ldcs(wav.c + i), __ldcs(wav.d + i) }, o[4];
+        eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
+        __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]); __stcs(out.d + i, o[3]);
     }
 }
 

@@ -26,7 +26,24 @@ constexpr int kSkyParams = 9;       // NB_SKY_PARAMS (sunsky.h:37)
 constexpr int kLd = 6;              // NB_SUN_LD_PARAMS (sunsky.h:44)
 constexpr int kMaxChannels = 11;    // NB_WAVELENGTHS (sunsky.h:20)
 constexpr int kChanPad = kMaxChannels + 1;
-constexpr int kFastCoefs = 11;      // A0, A1, A2, A3, A4 log2e, A5, A6, A7, 1 + A8^2, 2 A8, radiance x scale
+// FAST-mode coefficient table, per channel: c1 coefficients (T0, T1, T11: see c1_fast), A2, A3, A4 log2e, A5, A6, A7,
+// 1 + A8^2, 2 A8, radiance x scale
+constexpr int kFastCoefs = 12;
+
+// How FAST mode evaluates c1 = 1 + A0 exp(A1 / (cos(theta) + 0.01)), which cancels to ~0.1 towards the zenith:
+//   0  the reference's exp polynomial with a cheaper range reduction (fexp): 24 instructions per bin pair
+//   1  MUFU ex2 on a pre-scaled exponent, guarded: |c1| < 1/16 |A0 e| (error amplification > 16) -> reference path
+//   2  u = A1 s + ln|A0|; c1 = -expm1(u) by a degree-6 polynomial where A0 < 0 and |u| < 1/4 (no cancellation at
+//      all: the small quantity is computed directly), 1 + sgn(A0) 2^(u log2 e) on the MUFU elsewhere (c1 >= 0.22
+//      there, amplification < 5). Select, not branch. No fallback needed.
+#ifndef SSK_C1_MODE
+#define SSK_C1_MODE 1
+#endif
+// FAST spectral coefficient table in shared memory as 128-bit rows {T_2q(bin), T_2q(bin+1), T_2q+1(bin), T_2q+1(bin+1)}:
+// 6 LDS.128 per wavelength instead of 11 LDS.64
+#ifndef SSK_QUAD_TABLE
+#define SSK_QUAD_TABLE 1
+#endif
 
 enum { kExact = 0, kFast = 1 };
 
@@ -152,6 +169,58 @@ SSK_HD float2 render_sky_2(const HotBlock &P, int ch, const RayTerms &r) {
 }
 
 
+/// c1 of FAST mode on a pair (SSK_C1_MODE above). T0, T1, T11 per mode:
+///   0: A0, A1, -            1: A0, A1 log2(e), -            2: sgn(A0), A1, ln|A0| (-1e30 for A0 == 0)
+/// `s` = 1 / (cos(theta) + 0.01) on both elements (bin pair) or per element (ray pair).
+constexpr float kC1Guard = 0.0625f;
+SSK_HD float2 c1_fast_2(float2 T0, float2 T1, float2 T11, float2 s, bool &ok) {
+#if SSK_C1_MODE == 0
+    (void) T11;
+    return add2x(mul2(T0, fexp_2(mul2(T1, s), ok)), splat2(1.f));
+#elif SSK_C1_MODE == 1
+    (void) T11;
+    float2 a = mul2(T1, s);
+    float2 p = mul2(T0, f2(hw_ex2(a.x), hw_ex2(a.y)));
+    float2 c1 = add2(p, splat2(1.f));
+    ok = fabsf(c1.x) >= kC1Guard * fabsf(p.x) && fabsf(c1.y) >= kC1Guard * fabsf(p.y);
+    return c1;
+#else
+    ok = true;
+    float2 u = fma2(T1, s, T11);
+    float2 q = fma2(u, splat2(1.f / 720.f), splat2(1.f / 120.f));
+    q = fma2(q, u, splat2(1.f / 24.f));
+    q = fma2(q, u, splat2(1.f / 6.f));
+    q = fma2(q, u, splat2(0.5f));
+    q = fma2(q, u, splat2(1.f));
+    float2 small = mul2(neg2(u), q);                              // -expm1(u)
+    float2 a = mul2s(u, SSK_INV_LOG_TWO);
+    float2 big = fma2(T0, f2(hw_ex2(a.x), hw_ex2(a.y)), splat2(1.f));
+    return f2((T0.x < 0.f && fabsf(u.x) < 0.25f) ? small.x : big.x, (T0.y < 0.f && fabsf(u.y) < 0.25f) ? small.y : big.y);
+#endif
+}
+SSK_HD float c1_fast(float T0, float T1, float T11, float s, bool &ok) {
+#if SSK_C1_MODE == 0
+    (void) T11;
+    return T0 * fexp(T1 * s, ok) + 1.f;
+#elif SSK_C1_MODE == 1
+    (void) T11;
+    float p = T0 * hw_ex2(T1 * s), c1 = p + 1.f;
+    ok = fabsf(c1) >= kC1Guard * fabsf(p);
+    return c1;
+#else
+    ok = true;
+    float u = fmaf(T1, s, T11);
+    float q = fmaf(u, 1.f / 720.f, 1.f / 120.f);
+    q = fmaf(q, u, 1.f / 24.f);
+    q = fmaf(q, u, 1.f / 6.f);
+    q = fmaf(q, u, 0.5f);
+    q = fmaf(q, u, 1.f);
+    float small = -u * q;
+    float big = fmaf(T0, hw_ex2(u * SSK_INV_LOG_TWO), 1.f);
+    return (T0 < 0.f && fabsf(u) < 0.25f) ? small : big;
+#endif
+}
+
 /// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
 /// lane-dependent channels); the radiance scale T[10] folds sky_scale and, in RGB mode, the CIE-Y
 /// normalisation. What is approximated and what is not follows the conditioning of the formula:
@@ -170,7 +239,7 @@ constexpr float kCancel = 0.125f;
 ///   c2 = fma chain T2 + T3 2^(T4 gamma) + T5 cos^2(gamma) + T6 chi + T7 sqrt(cos(theta)), s2 its |.| twin
 SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool &ok) {
     bool ok_e;
-    float c1 = T[0] * fexp(T[1] * r.inv_denom_c1, ok_e) + 1.f;
+    float c1 = c1_fast(T[0], T[1], T[11], r.inv_denom_c1, ok_e);
     float t = T[8] - T[9] * r.cos_gamma;
     float rs = hw_rsqrt(t);
     float chi = (rs * rs * rs) * r.one_plus_cg2;
@@ -190,7 +259,7 @@ SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool
 /// T[k] = { coefficient k of channel a, of channel b }. ok = neither element cancelled.
 SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, bool &ok) {
     bool ok_e;
-    float2 c1 = add2x(mul2(T[0], fexp_2(mul2s(T[1], r.inv_denom_c1), ok_e)), splat2(1.f));
+    float2 c1 = c1_fast_2(T[0], T[1], T[11], splat2(r.inv_denom_c1), ok_e);
     float2 t = subp2(T[8], mul2s(T[9], r.cos_gamma));
     float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
     float2 chi = mul2s(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
@@ -403,7 +472,7 @@ SSK_HD float2 render_sky_p(const HotBlock &P, int ch, const RayTermsP &r) {
 /// sky_channel_fast for one channel and two rays (see sky_channel_fast_2 for what is approximated)
 SSK_HD float2 sky_channel_fast_p(const float T[kFastCoefs], const RayTermsP &r, bool &ok0, bool &ok1) {
     bool ok_e;
-    float2 c1 = add2x(mul2s(fexp_2(mul2s(r.inv_denom_c1, T[1]), ok_e), T[0]), splat2(1.f));
+    float2 c1 = c1_fast_2(splat2(T[0]), splat2(T[1]), splat2(T[11]), r.inv_denom_c1, ok_e);
     float2 t = subp2(splat2(T[8]), mul2s(r.cos_gamma, T[9]));
     float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
     float2 chi = mul2(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
@@ -508,11 +577,21 @@ SSK_HD float sun_spec_term(const HotBlock &U, const HotBlock &S, const float *su
 /// between, in one 64-bit load. For a given k the 11 bins span 88 bytes, so whatever bins the lanes of a warp
 /// ask for, the load is a single conflict-free wavefront (a row-per-bin layout read with 128-bit loads was
 /// measured at 2.2x the ideal wavefront count and became the bottleneck: profiles/r1_summary.md).
+/// With SSK_QUAD_TABLE the same pairs are interleaved two coefficients at a time, so that one 128-bit load returns
+/// the pairs of coefficients 2q and 2q + 1: pairs[((k / 2) * kChanPad + bin) * 2 + (k & 1)]. For a given q the 11 bins
+/// span 176 bytes: two lanes of a quarter-warp collide only when their bins differ by exactly 8.
 constexpr int kPairTable = kFastCoefs * kChanPad;
+SSK_HD int pair_index(int k, int bin) {
+#if SSK_QUAD_TABLE
+    return ((k >> 1) * kChanPad + bin) * 2 + (k & 1);
+#else
+    return k * kChanPad + bin;
+#endif
+}
 SSK_HD void build_pair_table(const HotBlock &B, float2 *pairs) {
     for (int k = 0; k < kFastCoefs; ++k)
         for (int c = 0; c < kChanPad; ++c)
-            pairs[k * kChanPad + c] = f2(B.sky_fast[k][c], c + 1 < kChanPad ? B.sky_fast[k][c + 1] : 0.f);
+            pairs[pair_index(k, c)] = f2(B.sky_fast[k][c], c + 1 < kChanPad ? B.sky_fast[k][c + 1] : 0.f);
 }
 
 /// Sky radiance of the 4 wavelengths with the reference sequence (FAST mode's fallback for cancelling lanes)
@@ -570,8 +649,17 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
         valid[w] = b.valid;
         if (A == kFast) {
             float2 T[kFastCoefs];
+#if SSK_QUAD_TABLE
+            const float4 *quads = reinterpret_cast<const float4 *>(pairs);
+#pragma unroll
+            for (int q = 0; q < kFastCoefs / 2; ++q) {
+                float4 v = quads[q * kChanPad + b.lo];
+                T[2 * q] = f2(v.x, v.y); T[2 * q + 1] = f2(v.z, v.w);
+            }
+#else
 #pragma unroll
             for (int k = 0; k < kFastCoefs; ++k) T[k] = pairs[k * kChanPad + b.lo];
+#endif
             bool ok_w;
             float2 sk = sky_channel_fast_2(T, g.r, ok_w);
             ok = ok && ok_w;

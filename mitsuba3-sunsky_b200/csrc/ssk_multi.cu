@@ -203,8 +203,14 @@ int ssk_sweep_render(const ssk_params *frames, int n_frames, const char *dataset
         // the chunk's own setup quadrature (its stream has the highest priority and overlaps the queued maps)
         const int have = (int) pool->ctx.size();
         const int upd = std::min(have, m);
-        if (upd > 0)
-            if (int rc = ssk_update_batch(pool->ctx.data(), frames + s, upd)) return mfail(rc, ssk_last_error());
+        if (upd > 0) {
+            // a frame is a full property set: constructor semantics, i.e. the sun direction is normalised
+            // (parameters_changed() alone would take it as stored)
+            std::vector<ssk_params> fp(frames + s, frames + s + upd);
+            for (auto &q : fp)
+                if (!q.use_record && !(q.flags & SSK_FLAG_SUN_DIR_NORMALIZED)) ssk_normalize_direction(q.sun_direction, q.sun_direction);
+            if (int rc = ssk_update_batch(pool->ctx.data(), fp.data(), upd)) return mfail(rc, ssk_last_error());
+        }
         for (int i = upd; i < m; ++i) {
             ssk_ctx *c = nullptr;
             if (int rc = ssk_create(frames + s + i, dataset_dir, device, mode, &c)) return mfail(rc, ssk_last_error());
