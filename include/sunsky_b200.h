@@ -164,14 +164,18 @@ int ssk_sample_direction_device(const ssk_ctx *ctx, const float *const u[2], con
                                 const float *const wavelengths[4], size_t n, float *const d[3], float *pdf,
                                 float *const weight[4], float *const p[3], float *dist, void *stream);
 
-/* Forward derivative of eval() along a tangent of the Differentiable parameters `turbidity` and `albedo`
- * (src/emitters/sunsky.cpp:222-225; sunsky-testing/traversal_test.py:94-144 drives it with dr.forward_from):
- *   out = d eval / d turbidity * d_turbidity + sum_c d eval / d albedo[c] * d_albedo[c]
- * d_albedo has 0, 1 (same tangent for every channel) or n_channels (3 RGB / 11 spectral bins) entries. Planes as
- * ssk_eval_device. The derivative is the one the reference's AD sees: the interpolated state is piecewise linear
- * in both parameters and the sampling weight / TGMM are not part of eval(). Calls on one context must be ordered
- * on `stream` (the context owns one tangent block). */
-int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo,
+/* Forward derivative of eval() along a tangent of the Differentiable parameters `turbidity`, `albedo` and
+ * `sun_direction` (traverse(), src/emitters/sunsky.cpp:222-237; sunsky-testing/traversal_test.py:94-144 drives it
+ * with dr.forward_from):
+ *   out = d eval/d turbidity * d_turbidity + sum_c d eval/d albedo[c] * d_albedo[c] + sum_i d eval/d sun_direction[i] * d_sun_direction[i]
+ * d_albedo has 0, 1 (same tangent for every channel) or n_channels (3 RGB / 11 spectral bins) entries; d_sun_direction
+ * is NULL or 3 floats (world space; emitters built from a sun direction only). Planes as ssk_eval_device. The
+ * derivative is the one forward-mode AD of the reference's code produces: the interpolated state is piecewise linear
+ * in turbidity and albedo and a quintic Bezier in the sun elevation; gamma = unit_angle(sun, wo) and cos(psi) are
+ * differentiated as written; masks, bin and segment indices, the sampling weight and the TGMM (not part of eval())
+ * carry no tangent. The tangent block travels as a kernel parameter: calls on one context may be issued
+ * concurrently. Independent oracle: oracle/jvp_oracle.py (fp64 dual numbers), tests/test_parity_gpu.py. */
+int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo, const float *d_sun_direction,
                         const float *const wi[3], const float *const wav[4], size_t n, float *const out[4], void *stream);
 
 /* sample_wavelengths(si, sample) (src/emitters/sunsky.cpp:463-480).

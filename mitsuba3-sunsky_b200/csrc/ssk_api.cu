@@ -52,7 +52,6 @@ struct ssk_ctx {
     EmitterBlock *ring[kBlockRing] = {};
     cudaEvent_t used[kBlockRing] = {};               // recorded on the launch stream after every launch on ring[i]
     int cur = 0;
-    mutable TangentBlock *d_tangent = nullptr;       // eval_jvp: lazily allocated, rewritten by every call
     int sm_count = 0;
     mutable Staging st;
 };
@@ -826,7 +825,6 @@ void ssk_destroy(ssk_ctx *ctx) {
             if (ctx->st.pinned[i]) cudaFreeHost(ctx->st.pinned[i]);
             if (ctx->st.dev[i]) cudaFree(ctx->st.dev[i]);
         }
-        if (ctx->d_tangent) cudaFree(ctx->d_tangent);
     }
     delete ctx;
 }
@@ -1054,7 +1052,7 @@ int ssk_sample_direction_host(const ssk_ctx *ctx, const float *const u[2], const
     });
 }
 
-int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo,
+int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_albedo, int n_d_albedo, const float *d_sun_direction,
                         const float *const wi[3], const float *const wav[4], size_t n, float *const out[4], void *stream) {
     DeviceGuard dg; if (int rc = need_device(ctx, dg)) return rc;
     const bool spectral = ctx->mode == SSK_MODE_SPECTRAL;
@@ -1062,6 +1060,8 @@ int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_al
     if (n_d_albedo != 0 && n_d_albedo != 1 && n_d_albedo != ctx->E.n_channels)
         return fail(SSK_ERR_INVALID, "d_albedo needs 0, 1 or n_channels (3 RGB / 11 spectral) entries");
     if (n_d_albedo && !d_albedo) return fail(SSK_ERR_INVALID, "null d_albedo");
+    if (d_sun_direction && ctx->E.active_record)
+        return fail(SSK_ERR_INVALID, "sun_direction is not a parameter of an emitter built from a date / location record");
     if (n == 0) return SSK_OK;                     // empty batches carry null planes
     if (!wi || !out || !wi[0] || !wi[1] || !wi[2]) return fail(SSK_ERR_INVALID, "null direction / output planes");
     for (int c = 0; c < C; ++c) if (!out[c]) return fail(SSK_ERR_INVALID, "null output plane");
@@ -1069,11 +1069,9 @@ int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_al
         return fail(SSK_ERR_INVALID, "spectral mode needs 4 wavelength planes");
     return guarded([&]() -> int {
         cudaStream_t s = (cudaStream_t) stream;
-        TangentBlock T;
-        state_tangent(ctx->E, d_turbidity, d_albedo, n_d_albedo, T);
-        if (!ctx->d_tangent) SSK_CUDA(cudaMalloc(&ctx->d_tangent, sizeof(TangentBlock)));
-        // pageable source: the copy is staged before the call returns, so the stack block may go out of scope
-        SSK_CUDA(cudaMemcpyAsync(ctx->d_tangent, &T, sizeof(T), cudaMemcpyHostToDevice, s));
+        // the tangent block is a kernel parameter: built here, copied into the launch, nothing shared between calls
+        static thread_local TangentBlock T;
+        state_tangent(ctx->E, d_turbidity, d_albedo, n_d_albedo, d_sun_direction, T);
         Planes3 i3 = { wi[0], wi[1], wi[2] };
         Planes4 w4 = { nullptr, nullptr, nullptr, nullptr };
         if (spectral) w4 = { wav[0], wav[1], wav[2], wav[3] };
@@ -1081,7 +1079,7 @@ int ssk_eval_jvp_device(const ssk_ctx *ctx, float d_turbidity, const float *d_al
         int grid = 1;
         auto launch = [&](auto kernel) -> int {
             if (int rc = occupancy_grid(ctx, kernel, n, &grid, 1)) return rc;
-            kernel<<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_tangent, i3, w4, o4, n);
+            kernel<<<grid, kThreads, 0, s>>>(hot(ctx), T, ctx->d_block, i3, w4, o4, n);
             return SSK_OK;
         };
         int rc = fast(ctx) ? (spectral ? launch(eval_jvp_kernel<kFast, true>) : launch(eval_jvp_kernel<kFast, false>))

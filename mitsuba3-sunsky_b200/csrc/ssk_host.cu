@@ -412,12 +412,73 @@ void estimate_sky_sun_ratio(HostEmitter &E, const float sky_rad[11], const float
     }
 }
 
+/// d compute_radiance_params / d eta (sunsky.h:157-231): only the Bezier weights C_i x^i (1 - x)^(5 - i) depend on the
+/// sun elevation (x = cbrt(2 eta / pi)); the turbidity and albedo lerps that follow are linear. fp64.
+static void radiance_params_deta(const std::vector<float> &dataset, const float *albedo, int n_channels, float turbidity,
+                                 float eta, std::vector<double> &out) {
+    const uint32_t dataset_size = (uint32_t) dataset.size();
+    const uint32_t t_block = dataset_size / 10, a_block = t_block / 2, result_size = a_block / 6,
+                   nb_params = result_size / (uint32_t) n_channels;
+    out.assign(result_size, 0.0);
+    if (!(eta > 0.f && eta <= SSK_HALF_PI)) return;
+    const double x = cbrt(2.0 / 3.14159265358979323846 * (double) eta);
+    if (x < 1e-6) return;
+    const double dx = (2.0 / 3.14159265358979323846) / (3.0 * x * x);
+    const double coefs[6] = { 1, 5, 10, 10, 5, 1 };
+    double dw[6];
+    for (int i = 0; i < 6; ++i) {
+        const double a = i ? i * pow(x, i - 1) * pow(1.0 - x, 5 - i) : 0.0;
+        const double b = i < 5 ? (5 - i) * pow(x, i) * pow(1.0 - x, 4 - i) : 0.0;
+        dw[i] = coefs[i] * (a - b) * dx;
+    }
+    uint32_t t_high = (uint32_t) (int32_t) floorf(turbidity), t_low = t_high - 1;
+    const double t_rem = (double) turbidity - (double) t_high;
+    auto bez = [&](uint32_t t_idx, uint32_t a_idx, uint32_t i) {
+        if (t_idx >= 10) return 0.0;
+        double acc = 0.0;
+        for (int c = 0; c < 6; ++c) acc += dw[c] * (double) dataset[t_idx * t_block + a_idx * a_block + c * result_size + i];
+        return acc;
+    };
+    for (uint32_t i = 0; i < result_size; ++i) {
+        const double lo = bez(t_low, 0, i) + (bez(t_high, 0, i) - bez(t_low, 0, i)) * t_rem,
+                     hi = bez(t_low, 1, i) + (bez(t_high, 1, i) - bez(t_low, 1, i)) * t_rem;
+        out[i] = lo + (hi - lo) * (double) albedo[i / nb_params];
+    }
+}
+
 /// State tangent for the direction (d_turbidity, d_albedo[]): the interpolated state is linear in turbidity inside a
 /// slab [t, t+1] and linear in each channel's albedo (sunsky.h:157-231 for the sky, :403-419 for the sun), so the
 /// exact derivative is a difference of states rebuilt at the slab ends / at albedo 0 and 1.
-void state_tangent(const HostEmitter &E, float d_turbidity, const float *d_albedo, int n_d_albedo, TangentBlock &T) {
+void state_tangent(const HostEmitter &E, float d_turbidity, const float *d_albedo, int n_d_albedo, const float *d_sun_direction,
+                   TangentBlock &T) {
     memset(&T, 0, sizeof(T));
     const int C = E.n_channels;
+    if (d_sun_direction && (d_sun_direction[0] != 0.f || d_sun_direction[1] != 0.f || d_sun_direction[2] != 0.f)) {
+        // local sun direction v = to_world^-1 sun_dir (linear), theta = unit_angle_z(v) differentiated as written
+        // (drjit/sphere.h:73-81), eta = pi/2 - theta, then the Bezier weights of both sky tables
+        const EmitterBlock &B = E.block;
+        Vec3 dv = xform(B.to_local, Vec3{ d_sun_direction[0], d_sun_direction[1], d_sun_direction[2] });
+        T.d_sun_n[0] = dv.x; T.d_sun_n[1] = dv.y; T.d_sun_n[2] = dv.z;
+        const double vx = B.sun_n[0], vy = B.sun_n[1], vz = B.sun_n[2], sg = vz >= 0.0 ? 1.0 : -1.0;
+        const double D2 = vx * vx + vy * vy + (vz - sg) * (vz - sg);
+        double d_eta = 0.0;
+        if (D2 > 0.0) {
+            const double D = sqrt(D2), dD = (vx * dv.x + vy * dv.y + (vz - sg) * dv.z) / D;
+            d_eta = -sg * dD / sqrt(std::max(1.0 - 0.25 * D2, 1e-300));
+        }
+        if (d_eta != 0.0) {
+            float albedo[11];
+            for (int c = 0; c < C; ++c) albedo[c] = E.params.n_albedo == 1 ? E.params.albedo[0] : E.params.albedo[c];
+            const float eta = SSK_HALF_PI - E.sun_angles[1];
+            std::vector<double> dp, dr;
+            radiance_params_deta(E.data->sky_params, albedo, C, E.params.turbidity, eta, dp);
+            radiance_params_deta(E.data->sky_rad, albedo, C, E.params.turbidity, eta, dr);
+            for (int c = 0; c < C; ++c) {
+                for (int k = 0; k < kSkyParams; ++k) T.sky_params[k][c] += (float) (d_eta * dp[c * 9 + k]);
+                T.sky_rad[c] += (float) (d_eta * dr[c]);
+            }
+        }
+    }
     auto rebuilt = [&](float turbidity, float albedo) {
         HostEmitter H = E;
         ssk_params p = E.params;

@@ -293,6 +293,7 @@ void estimate_sky_sun_ratio(HostEmitter &E, const float sky_rad[11], const float
 std::shared_ptr<const Datasets> datasets_for(const std::string &dir, bool spectral);   // process-wide cache
 const std::vector<float> &gauss_legendre_200();     // 200 nodes followed by 200 weights
 void set_ray_pdf_scale(HotBlock &B);
-void state_tangent(const HostEmitter &E, float d_turbidity, const float *d_albedo, int n_d_albedo, TangentBlock &T);
+void state_tangent(const HostEmitter &E, float d_turbidity, const float *d_albedo, int n_d_albedo, const float *d_sun_direction,
+                   TangentBlock &T);
 
 } // namespace ssk

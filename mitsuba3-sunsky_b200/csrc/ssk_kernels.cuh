@@ -741,22 +741,34 @@ setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int
     if (lane == 0) partial[blockIdx.x] = acc;
 }
 
-// ---- forward derivative of eval (turbidity / albedo tangents) ----------------------------------------------
+// ---- forward derivative of eval (turbidity / albedo / sun-direction tangents) -----------------------------------
+/// The 14 KB tangent block travels as a kernel parameter (sm_70+ takes up to 32 KB): nothing to allocate, copy or
+/// race on between calls. Spectral lanes index the sky coefficients and their tangent with their own wavelength bin;
+/// from the parameter bank that serialises per distinct channel, so both are copied to shared memory first.
 template <int A, bool Spectral>
 __global__ void __launch_bounds__(kThreads)
-eval_jvp_kernel(const __grid_constant__ HotBlock U, const TangentBlock *__restrict__ tangent, Planes3 in, Planes4 wav,
-                OutPlanes4 out, size_t n) {
-    const TangentBlock &T = *tangent;              // 14 KB, L1 / L2 resident; indexed per channel
+eval_jvp_kernel(const __grid_constant__ HotBlock U, const __grid_constant__ TangentBlock T, const EmitterBlock *__restrict__ blk,
+                Planes3 in, Planes4 wav, OutPlanes4 out, size_t n) {
+    __shared__ SkyCoefs SP, ST;
+    if (Spectral) {
+        for (int i = threadIdx.x; i < (int) (sizeof(SkyCoefs) / 4); i += blockDim.x) {
+            const int row = i / kChanPad, c = i % kChanPad;
+            if (row < kSkyParams) { SP.sky_params[row][c] = U.sky_params[row][c]; ST.sky_params[row][c] = T.sky_params[row][c]; }
+            else                  { SP.sky_rad[c] = U.sky_rad[c];                 ST.sky_rad[c] = T.sky_rad[c]; }
+        }
+        __syncthreads();
+    }
+    const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x;
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         Vec3 wi = { __ldcs(in.x + i), __ldcs(in.y + i), __ldcs(in.z + i) };
         float o[4] = { 0.f, 0.f, 0.f, 0.f };
         if (Spectral) {
             const float wl[4] = { __ldcs(wav.a + i), __ldcs(wav.b + i), __ldcs(wav.c + i), __ldcs(wav.d + i) };
-            eval_spec_jvp<A>(U, T, wi, wl, o);
+            eval_spec_jvp<A>(U, SP, ST, T, sun_rad, wi, wl, o);
             __stcs(out.d + i, o[3]);
         } else {
-            eval_rgb_jvp<A>(U, T, wi, o);
+            eval_rgb_jvp<A>(U, T, sun_rad, wi, o);
         }
         __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]);
     }

@@ -914,19 +914,41 @@ template <int A> SSK_HD DirSample sample_dir(const HotBlock &U, const HotBlock &
     return r;
 }
 
-// ---- forward derivative of eval() w.r.t. the differentiable scalar parameters ---------------------------
-// turbidity and albedo are flagged Differentiable (sunsky.cpp:222-225) and enter eval() only through the
-// interpolated state (sky coefficients, mean radiance, sun table), which is piecewise linear in both
-// (sunsky.h:157-231, 403-419). The host builds the state tangent for a direction (d_turbidity, d_albedo[]) as
-// differences of interpolated states; the kernel pushes it through the radiance formula analytically.
+// ---- forward derivative of eval() w.r.t. the Differentiable parameters ------------------------------------
+// traverse() flags turbidity, albedo and sun_direction as Differentiable (sunsky.cpp:222-237). They enter eval()
+//   * through the interpolated state: sky coefficients and mean radiance (piecewise linear in turbidity and albedo,
+//     quintic Bezier in x = cbrt(2 eta / pi) of the sun elevation eta, sunsky.h:157-231) and the sun table (linear in
+//     turbidity, :403-419): the host builds that tangent (state_tangent, ssk_host.cu);
+//   * sun_direction also directly, through gamma = unit_angle(sun, wo) in render_sky and through cos(psi) in the
+//     sun-disc term: the kernel differentiates those formulas as written (what forward-mode AD does; masks, bin and
+//     segment indices are constants).
+// The independent oracle is oracle/jvp_oracle.py (fp64 dual numbers).
 struct TangentBlock {
     float sky_params[kSkyParams][kChanPad];
     float sky_rad[kChanPad];
+    float d_sun_n[4];                                 // tangent of the local sun direction (m_local_sun_frame.n)
     float sun_rad[kSunSegments * 3 * 4 * kLd];
 };
-/// d render_sky(ch) for the state tangent T (product rule over sunsky.cpp:538-555). A = kFast: MUFU ex2 / rsq /
-/// rcp for the transcendentals (the derivative has no bit-level reference to match)
-template <int A> SSK_HD float render_sky_jvp(const HotBlock &P, const TangentBlock &T, int ch, const RayTerms &r) {
+/// The per-channel sky part of a HotBlock or a TangentBlock (same member layout as the head of both): what the
+/// spectral derivative indexes with a per-lane channel, so the kernel keeps a shared-memory copy of each
+struct SkyCoefs {
+    float sky_params[kSkyParams][kChanPad];
+    float sky_rad[kChanPad];
+};
+/// d gamma for the tangent dn of the sun direction: unit_angle (drjit/sphere.h:53-59) differentiated as written
+SSK_HD float unit_angle_jvp(const Vec3 &n, const Vec3 &wo, const float dn[3]) {
+    const float dot = dot3(n, wo), sg = dot >= 0.f ? 1.f : -1.f;
+    const float dx = wo.x - sg * n.x, dy = wo.y - sg * n.y, dz = wo.z - sg * n.z;
+    const float D2 = dx * dx + dy * dy + dz * dz;
+    if (!(D2 > 0.f)) return 0.f;
+    const float D = sqrtf(D2);
+    const float dD = -sg * (dx * dn[0] + dy * dn[1] + dz * dn[2]) / D;
+    return sg * dD / sqrtf(fmaxf(1.f - 0.25f * D2, 1e-30f));
+}
+/// d render_sky(ch) for the state tangent T and the angle tangent dgamma (product rule over sunsky.cpp:538-555).
+/// A = kFast: MUFU ex2 / rsq for the transcendentals (the derivative has no bit-level reference to match)
+template <int A, class PB, class TB>
+SSK_HD float render_sky_jvp(const PB &P, const TB &T, int ch, const RayTerms &r, float dgamma, float sin_gamma) {
     float A0 = P.sky_params[0][ch], A1 = P.sky_params[1][ch], A2 = P.sky_params[2][ch], A3 = P.sky_params[3][ch],
           A4 = P.sky_params[4][ch], A5 = P.sky_params[5][ch], A6 = P.sky_params[6][ch], A7 = P.sky_params[7][ch],
           A8 = P.sky_params[8][ch], L = P.sky_rad[ch];
@@ -937,45 +959,70 @@ template <int A> SSK_HD float render_sky_jvp(const HotBlock &P, const TangentBlo
     float e1 = A == kFast ? hw_ex2(A1 * r.inv_denom_c1 * kLog2e) : dexp(A1 * r.inv_denom_c1);
     float c1 = 1.f + A0 * e1, dc1 = d0 * e1 + A0 * e1 * (d1 * r.inv_denom_c1);
     float arg = 1.f + A8 * A8 - 2.f * A8 * r.cos_gamma;
-    float chi, chi_over_arg;
-    if (A == kFast) { float rs = hw_rsqrt(arg); chi = r.one_plus_cg2 * (rs * rs * rs); chi_over_arg = chi * (rs * rs); }
-    else { chi = fdiv(r.one_plus_cg2, dpow15(arg)); chi_over_arg = fdiv(chi, arg); }
-    float dchi = -1.5f * chi_over_arg * ((2.f * A8 - 2.f * r.cos_gamma) * d8);
+    float chi, chi_over_arg, inv_pow;
+    if (A == kFast) { float rs = hw_rsqrt(arg); inv_pow = rs * rs * rs; chi = r.one_plus_cg2 * inv_pow; chi_over_arg = chi * (rs * rs); }
+    else { float pw = dpow15(arg); inv_pow = fdiv(1.f, pw); chi = fdiv(r.one_plus_cg2, pw); chi_over_arg = fdiv(chi, arg); }
+    const float dcg = -sin_gamma * dgamma, dcg2 = 2.f * r.cos_gamma * dcg;
+    float darg = (2.f * A8 - 2.f * r.cos_gamma) * d8 - 2.f * A8 * dcg;
+    float dchi = dcg2 * inv_pow - 1.5f * chi_over_arg * darg;
     float e4 = A == kFast ? hw_ex2(A4 * r.gamma * kLog2e) : dexp(A4 * r.gamma);
     float c2 = A2 + A3 * e4 + A5 * r.cos_gamma_sqr + A6 * chi + A7 * r.sqrt_cos_theta;
-    float dc2 = d2 + d3 * e4 + A3 * e4 * (r.gamma * d4) + d5 * r.cos_gamma_sqr + d6 * chi + A6 * dchi + d7 * r.sqrt_cos_theta;
+    float dc2 = d2 + d3 * e4 + A3 * e4 * (r.gamma * d4 + A4 * dgamma) + d5 * r.cos_gamma_sqr + A5 * dcg2 + d6 * chi + A6 * dchi +
+                d7 * r.sqrt_cos_theta;
     return (dc1 * c2 + c1 * dc2) * L + c1 * c2 * dL;
 }
-/// d eval, RGB (mirrors eval_rgb; the sun term is linear in its table)
-template <int A> SSK_HD void eval_rgb_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &wi, float out[3]) {
+/// Powers of cos(psi) and their tangents for the sun-disc term: cj[j] = c^j, dcj[j] = j c^(j-1) dc with
+/// c = sqrt(1 - sin^2(gamma) / sin^2(half aperture)) (sunsky.h:384-392)
+SSK_HD void cos_psi_powers_jvp(const HotBlock &U, float gamma, float sin_gamma, float cos_gamma, float dgamma, float cj[6], float dcj[6]) {
+    const float c = cos_psi(U, gamma);
+    const float dc = c > 0.f ? -U.ar2 * sin_gamma * cos_gamma * dgamma / c : 0.f;
+    powers6(c, cj);
+    dcj[0] = 0.f;
+    for (int j = 1; j < 6; ++j) dcj[j] = (float) j * cj[j - 1] * dc;
+}
+/// d eval, RGB (mirrors eval_rgb). sun_rad: the primal sun table (for the cos(psi) tangent); T.sun_rad: its tangent
+template <int A> SSK_HD void eval_rgb_jvp(const HotBlock &U, const TangentBlock &T, const float *sun_rad, const Vec3 &wi, float out[3]) {
     EvalGeom g = eval_geom<kExact>(U, wi, true);
     out[0] = out[1] = out[2] = 0.f;
     if (!g.active) return;
-    float xk[4], cj[6];
+    Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
+    Vec3 wo = xform(U.to_local, Vec3{ -wi.x, -wi.y, -wi.z });
+    const float dgamma = unit_angle_jvp(n, wo, T.d_sun_n), sg = dsin(g.r.gamma);
+    float xk[4], cj[6], dcj[6];
     SunSeg s = { 0, 0.f };
-    if (g.hit_sun) { s = sun_segment(g.r.cos_theta); powers4(s.x, xk); powers6(cos_psi(U, g.r.gamma), cj); }
+    if (g.hit_sun) { s = sun_segment(g.r.cos_theta); powers4(s.x, xk); cos_psi_powers_jvp(U, g.r.gamma, sg, g.r.cos_gamma, dgamma, cj, dcj); }
     for (int c = 0; c < 3; ++c) {
-        double res = (double) (U.sky_scale * render_sky_jvp<A>(U, T, c, g.r));
-        if (g.hit_sun) res += (double) (U.sun_scale * render_sun_rgb(T.sun_rad, c, s, xk, cj) * U.area_ratio) * 467.069280386;
+        double res = (double) (U.sky_scale * render_sky_jvp<A>(U, T, c, g.r, dgamma, sg));
+        if (g.hit_sun) {
+            float dsun = render_sun_rgb(T.sun_rad, c, s, xk, cj) + render_sun_rgb(sun_rad, c, s, xk, dcj);
+            res += (double) (U.sun_scale * dsun * U.area_ratio) * 467.069280386;
+        }
         out[c] = (float) (res * (1.0 / 106.7502593994140625));
     }
 }
-/// d eval, spectral (mirrors eval_spec)
-template <int A> SSK_HD void eval_spec_jvp(const HotBlock &U, const TangentBlock &T, const Vec3 &wi, const float wav[4], float out[4]) {
+/// d eval, spectral (mirrors eval_spec). P / TS: the sky coefficients and their tangent, indexed by a per-lane channel
+/// (the kernel passes shared-memory copies; U and T themselves work too)
+template <int A, class PB, class TB>
+SSK_HD void eval_spec_jvp(const HotBlock &U, const PB &P, const TB &TS, const TangentBlock &T, const float *sun_rad,
+                          const Vec3 &wi, const float wav[4], float out[4]) {
     EvalGeom g = eval_geom<kExact>(U, wi, true);
     out[0] = out[1] = out[2] = out[3] = 0.f;
     if (!g.active) return;
-    float xk[4], cj[6];
+    Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
+    Vec3 wo = xform(U.to_local, Vec3{ -wi.x, -wi.y, -wi.z });
+    const float dgamma = unit_angle_jvp(n, wo, T.d_sun_n), sg = dsin(g.r.gamma);
+    float xk[4], cj[6], dcj[6];
     SunSeg s = { 0, 0.f };
-    if (g.hit_sun) { s = sun_segment(g.r.cos_theta); powers4(s.x, xk); powers6(cos_psi(U, g.r.gamma), cj); }
+    if (g.hit_sun) { s = sun_segment(g.r.cos_theta); powers4(s.x, xk); cos_psi_powers_jvp(U, g.r.gamma, sg, g.r.cos_gamma, dgamma, cj, dcj); }
     for (int w = 0; w < 4; ++w) {
         Bin b = wavelength_bin(wav[w]);
         if (!b.valid) continue;
         const int hi = b.lo + 1;                   // channel 11 is the zero pad (see HotBlock)
-        float d = U.sky_scale * lerp(render_sky_jvp<A>(U, T, b.lo, g.r), render_sky_jvp<A>(U, T, hi, g.r), b.f);
+        float d = U.sky_scale * lerp(render_sky_jvp<A>(P, TS, b.lo, g.r, dgamma, sg), render_sky_jvp<A>(P, TS, hi, g.r, dgamma, sg), b.f);
         if (g.hit_sun) {
-            float lo_v = render_sun_spec(T.sun_rad, b.lo, s, xk), hi_v = hi < kMaxChannels ? render_sun_spec(T.sun_rad, hi, s, xk) : 0.f;
-            d += U.sun_scale * lerp(lo_v, hi_v, b.f) * sun_ld(U, b.lo, hi, b.f, cj) * U.area_ratio;
+            float t_lo = render_sun_spec(T.sun_rad, b.lo, s, xk), t_hi = hi < kMaxChannels ? render_sun_spec(T.sun_rad, hi, s, xk) : 0.f;
+            float p_lo = render_sun_spec(sun_rad, b.lo, s, xk), p_hi = hi < kMaxChannels ? render_sun_spec(sun_rad, hi, s, xk) : 0.f;
+            d += U.sun_scale * (lerp(t_lo, t_hi, b.f) * sun_ld(U, b.lo, hi, b.f, cj) + lerp(p_lo, p_hi, b.f) * sun_ld(U, b.lo, hi, b.f, dcj)) * U.area_ratio;
         }
         out[w] = d;
     }

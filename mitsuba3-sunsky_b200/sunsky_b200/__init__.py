@@ -320,10 +320,11 @@ class SunskyEmitter:
         return (d, pdf, wgt, op, dist) if want_p else (d, pdf, wgt)
 
 
-    def eval_jvp(self, wi, wavelengths=None, d_turbidity=0.0, d_albedo=None):
-        """Forward derivative of eval() along (d_turbidity, d_albedo): what dr.forward_from(params['turbidity'] /
-        params['albedo']) gives on plugin.eval(si) (sunsky.cpp:222-225, sunsky-testing/traversal_test.py:94-144).
-        d_albedo: None, a scalar, or one tangent per channel (3 RGB / 11 spectral bins). Device tensors only."""
+    def eval_jvp(self, wi, wavelengths=None, d_turbidity=0.0, d_albedo=None, d_sun_direction=None):
+        """Forward derivative of eval() along (d_turbidity, d_albedo, d_sun_direction): what dr.forward_from(params[...])
+        gives on plugin.eval(si) (sunsky.cpp:222-237, sunsky-testing/traversal_test.py:94-144).
+        d_albedo: None, a scalar, or one tangent per channel (3 RGB / 11 spectral bins); d_sun_direction: None or 3
+        floats (world space). Device tensors only."""
         import torch
         if not _is_torch(wi):
             raise TypeError("eval_jvp takes CUDA tensors (float32, plane-major)")
@@ -339,8 +340,10 @@ class SunskyEmitter:
         da = np.zeros(0, np.float32) if d_albedo is None else np.ascontiguousarray(d_albedo, dtype=np.float32).reshape(-1)
         out = torch.empty((self.channels, n), dtype=torch.float32, device=wi.device)
         o_pp, _ = self._pp_t(out, self.channels, "out")
+        ds = None if d_sun_direction is None else np.ascontiguousarray(d_sun_direction, dtype=np.float32).reshape(3)
         _check(self._L.ssk_eval_jvp_device(self._ctx, float(d_turbidity), da.ctypes.data_as(_capi.FP) if da.size else None,
-                                           int(da.size), d_pp, w_pp, n, o_pp, self._stream()))
+                                           int(da.size), None if ds is None else ds.ctypes.data_as(_capi.FP), d_pp, w_pp, n,
+                                           o_pp, self._stream()))
         return out
 
     def sample_wavelengths(self, wi, sample=None):

@@ -65,7 +65,7 @@ SYMBOLS = {
     "ssk_eval_direction_device": (C.c_int, [CTX, FPP, FPP, C.c_size_t, FPP, C.c_void_p]),
     "ssk_pdf_direction_device": (C.c_int, [CTX, FPP, C.c_size_t, FP, C.c_void_p]),
     "ssk_sample_direction_device": (C.c_int, [CTX, FPP, FPP, FPP, C.c_size_t, FPP, FP, FPP, FPP, FP, C.c_void_p]),
-    "ssk_eval_jvp_device": (C.c_int, [CTX, C.c_float, FP, C.c_int, FPP, FPP, C.c_size_t, FPP, C.c_void_p]),
+    "ssk_eval_jvp_device": (C.c_int, [CTX, C.c_float, FP, C.c_int, FP, FPP, FPP, C.c_size_t, FPP, C.c_void_p]),
     "ssk_sample_wavelengths_device": (C.c_int, [CTX, FPP, FP, C.c_size_t, FPP, FPP, C.c_void_p]),
     "ssk_sample_ray_device": (C.c_int, [CTX, FP, FPP, FPP, C.c_size_t, FPP, FPP, FPP, FPP, C.c_void_p]),
     "ssk_sample_wavelengths_host": (C.c_int, [CTX, FPP, FP, C.c_size_t, FPP, FPP]),

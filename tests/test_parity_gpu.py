@@ -640,6 +640,54 @@ def test_eval_jvp_matches_finite_differences(ssk, spectral, arith):
     assert e.eval_jvp(wi[:, :0].contiguous(), wav[:, :0].contiguous() if spectral else None, d_turbidity=1.0).shape[1] == 0
 
 
+JVP_CASES = [(False, 3.4, 0.3, 30.0), (True, 6.7, 0.55, 50.2), (False, 9.2, 0.9, 8.0), (True, 1.6, 0.1, 75.0),
+             (False, 6.0, 0.5, 50.2), (True, 10.0, 0.0, 20.0)]
+
+
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+@pytest.mark.parametrize("spectral,t,a,eta", JVP_CASES)
+def test_eval_jvp_matches_the_dual_number_oracle(ssk, spectral, t, a, eta, arith):
+    """eval_jvp against oracle/jvp_oracle.py: the reference's formulas on fp64 forward-mode dual numbers (pinned to
+    the reference library in tests/test_jvp_oracle_cpu.py). Covers the three Differentiable parameters of traverse()
+    (sunsky.cpp:222-237) -- turbidity, albedo per channel, sun_direction -- alone and combined, sky lanes and lanes
+    inside the sun disc. Tolerance: 2e-5 of the largest derivative on sky lanes (fp32 kernel vs fp64 oracle; measured
+    <= 9e-6), 5e-4 relative on sun-disc lanes away from the disc edge (where d cos(psi) is unbounded)."""
+    import torch
+    import jvp_oracle
+    from sunsky_b200 import _capi
+    rng = np.random.default_rng(5)
+    sd = np.array(common.sun_dir_from_elevation(eta, 0.9), np.float32)
+    e = ssk.SunskyEmitter(spectral=spectral, arith=arith, turbidity=t, albedo=a, sun_direction=list(sd))
+    st = e.state()
+    sdn = np.array(st.sun_dir_world, np.float64)
+    wo = np.concatenate([common.hemisphere_dirs(4096, rng), common.around(sdn, 0.2, 256, rng)], axis=1).astype(np.float32)
+    n = wo.shape[1]
+    wav = (330.0 + 380.0 * rng.random((4, n), dtype=np.float32)).astype(np.float32) if spectral else None
+    wi_t = torch.from_numpy(np.ascontiguousarray(-wo)).cuda()
+    wav_t = torch.from_numpy(wav).cuda() if spectral else None
+    C = 11 if spectral else 3
+    o = jvp_oracle.JvpOracle(_capi.DATASET_DIR, spectral)
+    for d_t, d_a, d_s in ((1.0, None, None), (0.0, rng.normal(size=C).astype(np.float32), None),
+                          (0.0, None, rng.normal(size=3).astype(np.float32)),
+                          (0.7, rng.normal(size=C).astype(np.float32), rng.normal(size=3).astype(np.float32))):
+        got = e.eval_jvp(wi_t, wav_t, d_turbidity=d_t, d_albedo=d_a, d_sun_direction=d_s).double().cpu().numpy()
+        val, tan, hit = o.eval_jvp(t, a, sdn, wo, wav, d_turbidity=d_t, d_albedo=d_a, d_sun_dir=d_s, area_ratio=st.area_ratio)
+        assert hit.sum() >= 128 and (~hit).sum() >= 4000
+        scale = np.abs(tan[:, ~hit]).max()
+        assert np.abs(got - tan)[:, ~hit].max() <= 2e-5 * scale, (d_t, d_a is not None, d_s is not None)
+        # sun-disc lanes: relative, away from the edge (cos(psi) > 0.3  <=>  sin(gamma) < 0.954 sin(half aperture))
+        cosg = (wo.astype(np.float64) * sdn[:, None]).sum(0)
+        inner = hit & (np.sqrt(np.maximum(1 - cosg * cosg, 0)) < 0.95 * np.sin(np.radians(0.5358 / 2)))
+        big = np.abs(tan) > 1e-3 * np.abs(tan[:, inner]).max()
+        m = big & inner[None, :]
+        assert m.sum() > 100
+        assert (np.abs(got - tan)[m] / np.abs(tan[m])).max() <= 5e-4, (d_t, d_a is not None, d_s is not None)
+    # an emitter built from a date / location record has no sun_direction parameter (sunsky.cpp:226-238)
+    rec = ssk.SunskyEmitter(spectral=spectral, hour=11.0)
+    with pytest.raises(ssk.SunskyError):
+        rec.eval_jvp(wi_t, wav_t, d_sun_direction=[0.0, 0.1, 0.0])
+
+
 # ---- environment maps and sweeps (BASELINE configs[3], configs[4]) ----------------------------------------
 
 @pytest.mark.parametrize("spectral", [False, True])
