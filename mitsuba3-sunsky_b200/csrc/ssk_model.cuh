@@ -39,10 +39,11 @@ constexpr int kFastCoefs = 12;
 #ifndef SSK_C1_MODE
 #define SSK_C1_MODE 1
 #endif
-// FAST spectral coefficient table in shared memory as 128-bit rows {T_2q(bin), T_2q(bin+1), T_2q+1(bin), T_2q+1(bin+1)}:
-// 6 LDS.128 per wavelength instead of 11 LDS.64
+// 1: FAST spectral coefficient table in shared memory as 128-bit rows {T_2q(bin), T_2q(bin+1), T_2q+1(bin), T_2q+1(bin+1)},
+// 6 LDS.128 per wavelength instead of 12 LDS.64. Measured SLOWER (spectral eval 54.9 vs 65.0 Gevals/s with c1 mode 1):
+// lanes of a quarter-warp whose bins differ by 8 collide, and the kernel is latency-bound on exactly these loads.
 #ifndef SSK_QUAD_TABLE
-#define SSK_QUAD_TABLE 1
+#define SSK_QUAD_TABLE 0
 #endif
 
 enum { kExact = 0, kFast = 1 };
@@ -299,14 +300,21 @@ SSK_HD void powers6(float c, float *p) {
 
 /// render_sun, RGB branch (sunsky.cpp:597-611). The 24 coefficients of a (segment, channel) pair are
 /// contiguous and 16-byte aligned: six 128-bit loads.
+/// Global = false: the table is not in global memory (the tangent block of eval_jvp is a kernel parameter)
+template <bool Global = true>
 SSK_HD float render_sun_rgb(const float *sun_rad, int ch, const SunSeg &s, const float *xk, const float *cj) {
     const float *S = sun_rad + s.pos * (3 * 4 * kLd) + ch * (4 * kLd);
     float c[4 * kLd];
 #if defined(__CUDA_ARCH__)
+    if (Global) {
 #pragma unroll
-    for (int q = 0; q < 6; ++q) {
-        float4 v = __ldg(reinterpret_cast<const float4 *>(S) + q);
-        c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+        for (int q = 0; q < 6; ++q) {
+            float4 v = __ldg(reinterpret_cast<const float4 *>(S) + q);
+            c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4 * kLd; ++q) c[q] = S[q];
     }
 #else
     for (int q = 0; q < 4 * kLd; ++q) c[q] = S[q];
@@ -320,10 +328,11 @@ SSK_HD float render_sun_rgb(const float *sun_rad, int ch, const SunSeg &s, const
     return acc;
 }
 /// render_sun, spectral branch (sunsky.cpp:590-596): one 128-bit load per (segment, wavelength bin)
+template <bool Global = true>
 SSK_HD float render_sun_spec(const float *sun_rad, int ch, const SunSeg &s, const float *xk) {
     const float *S = sun_rad + s.pos * (kMaxChannels * 4) + ch * 4;
 #if defined(__CUDA_ARCH__)
-    float4 v = __ldg(reinterpret_cast<const float4 *>(S));
+    float4 v = Global ? __ldg(reinterpret_cast<const float4 *>(S)) : make_float4(S[0], S[1], S[2], S[3]);
     const float c[4] = { v.x, v.y, v.z, v.w };
 #else
     const float c[4] = { S[0], S[1], S[2], S[3] };
@@ -994,7 +1003,7 @@ template <int A> SSK_HD void eval_rgb_jvp(const HotBlock &U, const TangentBlock 
     for (int c = 0; c < 3; ++c) {
         double res = (double) (U.sky_scale * render_sky_jvp<A>(U, T, c, g.r, dgamma, sg));
         if (g.hit_sun) {
-            float dsun = render_sun_rgb(T.sun_rad, c, s, xk, cj) + render_sun_rgb(sun_rad, c, s, xk, dcj);
+            float dsun = render_sun_rgb<false>(T.sun_rad, c, s, xk, cj) + render_sun_rgb(sun_rad, c, s, xk, dcj);
             res += (double) (U.sun_scale * dsun * U.area_ratio) * 467.069280386;
         }
         out[c] = (float) (res * (1.0 / 106.7502593994140625));
@@ -1020,7 +1029,7 @@ SSK_HD void eval_spec_jvp(const HotBlock &U, const PB &P, const TB &TS, const Ta
         const int hi = b.lo + 1;                   // channel 11 is the zero pad (see HotBlock)
         float d = U.sky_scale * lerp(render_sky_jvp<A>(P, TS, b.lo, g.r, dgamma, sg), render_sky_jvp<A>(P, TS, hi, g.r, dgamma, sg), b.f);
         if (g.hit_sun) {
-            float t_lo = render_sun_spec(T.sun_rad, b.lo, s, xk), t_hi = hi < kMaxChannels ? render_sun_spec(T.sun_rad, hi, s, xk) : 0.f;
+            float t_lo = render_sun_spec<false>(T.sun_rad, b.lo, s, xk), t_hi = hi < kMaxChannels ? render_sun_spec<false>(T.sun_rad, hi, s, xk) : 0.f;
             float p_lo = render_sun_spec(sun_rad, b.lo, s, xk), p_hi = hi < kMaxChannels ? render_sun_spec(sun_rad, hi, s, xk) : 0.f;
             d += U.sun_scale * (lerp(t_lo, t_hi, b.f) * sun_ld(U, b.lo, hi, b.f, cj) + lerp(p_lo, p_hi, b.f) * sun_ld(U, b.lo, hi, b.f, dcj)) * U.area_ratio;
         }

@@ -651,7 +651,9 @@ def test_eval_jvp_matches_the_dual_number_oracle(ssk, spectral, t, a, eta, arith
     the reference library in tests/test_jvp_oracle_cpu.py). Covers the three Differentiable parameters of traverse()
     (sunsky.cpp:222-237) -- turbidity, albedo per channel, sun_direction -- alone and combined, sky lanes and lanes
     inside the sun disc. Tolerance: 2e-5 of the largest derivative on sky lanes (fp32 kernel vs fp64 oracle; measured
-    <= 9e-6), 5e-4 relative on sun-disc lanes away from the disc edge (where d cos(psi) is unbounded)."""
+    <= 9e-6); 3e-3 relative on sun-disc lanes away from the disc edge (where d cos(psi) is unbounded): the sun
+    polynomial multiplies 1e13-sized coefficients that cancel, so ANY fp32 evaluation -- the reference's included, see
+    test04's 1.6e-3 against the fp64 .spd spectra -- carries ~1e-3 of noise in the value and in its derivative."""
     import torch
     import jvp_oracle
     from sunsky_b200 import _capi
@@ -681,7 +683,7 @@ def test_eval_jvp_matches_the_dual_number_oracle(ssk, spectral, t, a, eta, arith
         big = np.abs(tan) > 1e-3 * np.abs(tan[:, inner]).max()
         m = big & inner[None, :]
         assert m.sum() > 100
-        assert (np.abs(got - tan)[m] / np.abs(tan[m])).max() <= 5e-4, (d_t, d_a is not None, d_s is not None)
+        assert (np.abs(got - tan)[m] / np.abs(tan[m])).max() <= 3e-3, (d_t, d_a is not None, d_s is not None)
     # an emitter built from a date / location record has no sun_direction parameter (sunsky.cpp:226-238)
     rec = ssk.SunskyEmitter(spectral=spectral, hour=11.0)
     with pytest.raises(ssk.SunskyError):
