@@ -126,22 +126,8 @@ def emitter_kwargs():
 
 
 def configs1_inputs(n, device, rank=0):
-    """SURVEY.md 8(d) cfg 2: generator j of PCG32(size = 2n) gives one float; (u1, u2) = (float[2i], float[2i + 1]);
-    cos(theta) = u1, phi = 2 pi u2, wo = (sin cos, sin sin, cos), si.wi = -wo; wavelengths = 360 + 360 *
-    sample_shifted<4>(u3) with u3 from the next block of n generators (core/math.h:408-431). Ranks use disjoint
-    stream blocks. Returns (wi (3, n), wo (3, n), wavelengths (4, n)) as torch tensors on `device`."""
-    import torch
     from sunsky_b200 import pcg32
-    base = rank * 3 * n
-    u = pcg32.point2_pairs(n, stream_offset=base, device=device)
-    u3 = pcg32.floats(n, 1, stream_offset=base + 2 * n, device=device)[0]
-    ct = u[0]; st = torch.sqrt(torch.clamp(1 - ct * ct, min=0)); ph = (2 * np.pi) * u[1]
-    wo = torch.stack([st * torch.cos(ph), st * torch.sin(ph), ct]).contiguous()
-    shifted = u3[None, :] + torch.arange(4, device=device, dtype=torch.float32)[:, None] / 4
-    shifted = torch.where(shifted >= 1, shifted - 1, shifted)
-    # 360 + 360 * (1 - 2^-24) rounds to 720.0f, where the reference gathers one bin past its tables (SURVEY.md C4)
-    wav = (360.0 + 360.0 * shifted).clamp_(max=719.99).contiguous()
-    return (-wo).contiguous(), wo, wav
+    return pcg32.configs1_inputs(n, device, rank)
 
 
 def cpu_rate(r, wi, wav, threads, n, repeat=1):

@@ -306,6 +306,11 @@ uint64_t ssk_launch_count(void);
 /* compute_sun_coordinates (sunsky.h:283-374): date/time/location -> local sun direction */
 int ssk_sun_coordinates(int year, int month, int day, float hour, float minute, float second,
                         float latitude, float longitude, float timezone, float out_dir[3]);
+/* mi.hosek_sun_rad (src/render/python/sunsky_v.cpp:19 = arhosekskymodel_solar_radiance_internal2,
+ * include/mitsuba/render/sunsky/ArHosekSkyModel.c:686-786): direct solar radiance of the original fp64 Hosek-Wilkie
+ * model at one wavelength [nm], solar elevation [rad] and angle gamma from the disc centre [rad], evaluated on the
+ * shipped fp64 tables (sun_spec_rad.bin, sun_spec_ld.bin). Host, fp64; 0 outside 320..720 nm or turbidity 1..10. */
+int ssk_hosek_sun_rad(const char *dataset_dir, double turbidity, double wavelength, double elevation, double gamma, double *out);
 /* dr::normalize as the constructor applies it to the sun_direction property (sunsky.cpp:922), same rounding.
  * parameters_changed() does NOT normalise (the reference works on m_sun_dir as stored), so a caller that feeds a raw
  * property to ssk_update and wants constructor semantics normalises it with this first; ssk_sweep_render does. */

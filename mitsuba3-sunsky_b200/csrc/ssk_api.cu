@@ -1144,6 +1144,66 @@ int ssk_sun_coordinates(int year, int month, int day, float hour, float minute, 
     return SSK_OK;
 }
 
+/// fp64 payload of a dataset file (the files are fp64 on disk; the plugin itself keeps them in fp32)
+static std::vector<double> read_dataset_f64(const std::string &path, size_t expect) {
+    FILE *f = fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("\"" + path + "\": file does not exist!");
+    char tag[4] = { 0, 0, 0, 0 }; uint32_t version; uint64_t ndim = 0, count = 1;
+    bool ok = fread(tag, 1, 3, f) == 3 && fread(&version, 4, 1, f) == 1 && fread(&ndim, 8, 1, f) == 1 && ndim > 0 && ndim <= 8;
+    for (uint64_t i = 0; ok && i < ndim; ++i) { uint64_t d; ok = fread(&d, 8, 1, f) == 1; count *= d; }
+    std::vector<double> v(ok && count == expect ? count : 0);
+    ok = ok && count == expect && fread(v.data(), 8, count, f) == count;
+    fclose(f);
+    if (!ok) throw std::runtime_error(path + ": truncated or unexpected dataset file");
+    return v;
+}
+
+int ssk_hosek_sun_rad(const char *dataset_dir, double turbidity, double wavelength, double elevation, double gamma, double *out) {
+    if (!dataset_dir || !out) return fail(SSK_ERR_INVALID, "null argument");
+    return guarded([&]() -> int {
+        // arhosekskymodel_solar_radiance_internal2 (ArHosekSkyModel.c:686-786) on the shipped tables:
+        // sun_spec_rad.bin = solarDatasets as [turbidity][segment][lambda][power of x], sun_spec_ld.bin = limbDarkeningDatasets
+        static std::mutex mu;
+        static std::string dir;
+        static std::vector<double> rad, ld;
+        std::lock_guard<std::mutex> lock(mu);
+        if (dir != dataset_dir || rad.empty()) {
+            std::string d = dataset_dir; if (!d.empty() && d.back() != '/') d += '/';
+            rad = read_dataset_f64(d + "sun_spec_rad.bin", 10 * 45 * 11 * 4);
+            ld = read_dataset_f64(d + "sun_spec_ld.bin", 66);
+            dir = dataset_dir;
+        }
+        *out = 0.0;
+        if (!(wavelength >= 320.0 && wavelength <= 720.0 && turbidity >= 1.0 && turbidity <= 10.0)) return SSK_OK;
+        int turb_low = (int) turbidity - 1;
+        double turb_frac = turbidity - (double) (turb_low + 1);
+        if (turb_low == 9) { turb_low = 8; turb_frac = 1.0; }
+        int wl_low = (int) ((wavelength - 320.0) / 40.0);
+        double wl_frac = fmod(wavelength, 40.0) / 40.0;
+        if (wl_low == 10) { wl_low = 9; wl_frac = 1.0; }
+        auto sr = [&](int t, int wl) {                       // arhosekskymodel_sr_internal (:656-684)
+            const double pi = 3.14159265358979323846;
+            int pos = (int) (pow(2.0 * elevation / pi, 1.0 / 3.0) * 45);
+            if (pos > 44) pos = 44;
+            const double break_x = pow((double) pos / 45.0, 3.0) * (pi * 0.5), x = elevation - break_x;
+            const double *c = &rad[(((size_t) t * 45 + pos) * 11 + wl) * 4];
+            double res = 0.0, x_exp = 1.0;
+            for (int i = 0; i < 4; ++i) { res += x_exp * c[i]; x_exp *= x; }
+            return res;
+        };
+        double direct = (1.0 - turb_frac) * ((1.0 - wl_frac) * sr(turb_low, wl_low) + wl_frac * sr(turb_low, wl_low + 1)) +
+                        turb_frac * ((1.0 - wl_frac) * sr(turb_low + 1, wl_low) + wl_frac * sr(turb_low + 1, wl_low + 1));
+        double c[6];
+        for (int i = 0; i < 6; ++i) c[i] = (1.0 - wl_frac) * ld[wl_low * 6 + i] + wl_frac * ld[(wl_low + 1) * 6 + i];
+        const double sol = sin(0.5358 / 2.0 * (3.14159265358979323846 / 180.0)), ar2 = 1 / (sol * sol), sg = sin(gamma);
+        double sc2 = 1.0 - ar2 * sg * sg;
+        if (sc2 < 0.0) sc2 = 0.0;
+        const double sc = sqrt(sc2);
+        *out = direct * (c[0] + c[1] * sc + c[2] * pow(sc, 2.0) + c[3] * pow(sc, 3.0) + c[4] * pow(sc, 4.0) + c[5] * pow(sc, 5.0));
+        return SSK_OK;
+    });
+}
+
 int ssk_normalize_direction(const float in[3], float out[3]) {
     if (!in || !out) return fail(SSK_ERR_INVALID, "null argument");
     Vec3 v = normalize_sun_direction({ in[0], in[1], in[2] });

@@ -19,7 +19,7 @@ from . import _capi
 from ._capi import (MODE_RGB, MODE_SPECTRAL, FLAG_SUN_DIR_NORMALIZED, FLAG_TO_LOCAL_GIVEN, ARITH_EXACT, ARITH_FAST, DATASET_DIR,
                     Params, State)
 
-__all__ = ["SunskyEmitter", "SunskyError", "sun_coordinates", "array_from_file", "array_to_file",
+__all__ = ["SunskyEmitter", "SunskyError", "sun_coordinates", "hosek_sun_rad", "array_from_file", "array_to_file",
            "launch_count", "MODE_RGB", "MODE_SPECTRAL"]
 
 
@@ -483,6 +483,15 @@ def sun_coordinates(year, month, day, hour, minute, second, latitude, longitude,
     _check(_capi.lib().ssk_sun_coordinates(year, month, day, hour, minute, second, latitude, longitude, timezone,
                                            out.ctypes.data_as(_capi.FP)))
     return out
+
+
+def hosek_sun_rad(turbidity, wavelength, elevation, gamma, dataset_dir=None):
+    """`mi.hosek_sun_rad` (src/render/python/sunsky_v.cpp:19): direct solar radiance of the original fp64
+    Hosek-Wilkie model."""
+    out = C.c_double()
+    _check(_capi.lib().ssk_hosek_sun_rad((dataset_dir or DATASET_DIR).encode(), float(turbidity), float(wavelength),
+                                         float(elevation), float(gamma), C.byref(out)))
+    return out.value
 
 
 def array_from_file(path, file_is_f64=True):

@@ -81,6 +81,7 @@ SYMBOLS = {
     "ssk_sun_coordinates": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                       C.c_float, C.c_float, FP]),
     "ssk_normalize_direction": (C.c_int, [FP, FP]),
+    "ssk_hosek_sun_rad": (C.c_int, [C.c_char_p, C.c_double, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]),
     "ssk_array_from_file": (C.c_int, [C.c_char_p, C.c_int, FP, C.c_size_t, C.POINTER(C.c_size_t),
                                       C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "ssk_array_to_file": (C.c_int, [C.c_char_p, FP, C.POINTER(C.c_size_t), C.c_size_t, C.c_int]),

@@ -40,5 +40,9 @@ $CXX $FLAGS -mavx2 $INC "$HERE/ref_harness.cpp" -o "$OUT/libsunsky_ref.so" &
 P1=$!
 $CXX $FLAGS -mavx2 -mavx512f -mavx512vl -mavx512dq -mavx512bw -mavx512cd $INC "$HERE/ref_harness.cpp" -o "$OUT/libsunsky_ref_avx512.so" &
 P2=$!
-wait $P1; wait $P2
+# second oracle: the original fp64 Hosek-Wilkie model (mi.hosek_sun_rad), see oracle/hosek_harness.cpp
+$CXX -std=c++17 -O2 -fPIC -shared -mavx2 -mfma -ffp-contract=off -fno-strict-aliasing -w \
+    -I $REF -I $REF/ext/drjit/include -I $REF/ext/drjit/ext/drjit-core/include "$HERE/hosek_harness.cpp" -o "$OUT/libhosek_ref.so" &
+P3=$!
+wait $P1; wait $P2; wait $P3
 echo "built $OUT/libsunsky_ref.so $OUT/libsunsky_ref_avx512.so"

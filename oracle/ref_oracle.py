@@ -285,6 +285,25 @@ def invert4(m):
     return out.reshape(4, 4)
 
 
+_hosek = None
+
+
+def hosek_sun_rad(turbidity, wavelength, elevation, gamma):
+    """mi.hosek_sun_rad of the reference: the original fp64 Hosek-Wilkie model compiled in place
+    (oracle/hosek_harness.cpp -> oracle/_ref/libhosek_ref.so). The second, independent oracle of SURVEY.md 8(c)."""
+    global _hosek
+    if _hosek is None:
+        H = C.CDLL(os.path.join(_HERE, "_ref", "libhosek_ref.so"))
+        H.ssk_ref_hosek_sun_rad.restype = C.c_double
+        H.ssk_ref_hosek_sun_rad.argtypes = [C.c_double] * 4
+        _hosek = H
+    return _hosek.ssk_ref_hosek_sun_rad(turbidity, wavelength, elevation, gamma)
+
+
+def hosek_available():
+    return os.path.exists(os.path.join(_HERE, "_ref", "libhosek_ref.so"))
+
+
 def pcg32_floats(n, stream_offset=0):
     out = np.empty(n, np.float32)
     lib().ssk_ref_pcg32_floats(n, stream_offset, _fp(out))

@@ -106,3 +106,37 @@ def test_packet_flavour_tracks_the_parity_flavour(ref, name, isa):
     assert common.bit_equal(d, g["s_d"]) and common.bit_equal(pdf, g["s_pdf"])
     # threaded driver = single-threaded driver
     assert common.bit_equal(r.eval(-g["wo"], wav, threads=3), a)
+
+
+def test_hosek_sun_rad_matches_the_fp64_model_and_the_spd_fixtures(ssk, ref, refdata):
+    """ssk_hosek_sun_rad (the library's mi.hosek_sun_rad) against the reference's ArHosekSkyModel.c compiled in place
+    (second oracle, fp64) over a (turbidity, wavelength, elevation, gamma) grid, and against the 80 shipped .spd
+    spectra, which are output of that model (fp64 restatement within 2.4e-8)."""
+    if not ref.hosek_available():
+        pytest.skip("oracle/_ref/libhosek_ref.so not built")
+    rng = np.random.default_rng(3)
+    worst = 0.0
+    for _ in range(4000):
+        t, wl = rng.uniform(1, 10), rng.uniform(315, 725)
+        el, g = rng.uniform(1e-4, np.pi / 2), rng.uniform(0, 0.006)
+        a, b = ssk.hosek_sun_rad(t, wl, el, g), ref.hosek_sun_rad(t, wl, el, g)
+        assert (a == 0) == (b == 0)
+        if b != 0:
+            worst = max(worst, abs(a - b) / abs(b))
+    assert worst < 1e-12, worst
+    for t, wl in ((10.0, 500.0), (3.0, 720.0), (1.0, 320.0), (0.5, 500.0), (3.0, 319.0)):        # edges and out of range
+        assert ssk.hosek_sun_rad(t, wl, 0.7, 0.001) == pytest.approx(ref.hosek_sun_rad(t, wl, 0.7, 0.001), rel=1e-12, abs=0)
+    wavelengths = refdata["sun_wavelengths"]
+    turbs = np.linspace(1, 10, 5); etas = np.linspace(1e-4, np.pi / 2 - 1e-4, 4)
+    gammas = np.linspace(0, rs.SUN_HALF_APERTURE_ANGLE - 1e-4, 4)
+    worst = 0.0
+    for i, t in enumerate(turbs):
+        for j, eta in enumerate(etas):
+            for k, g in enumerate(gammas):
+                got = np.array([ssk.hosek_sun_rad(t, wl, eta, g) for wl in wavelengths])
+                want = refdata["sun_spectra"][i, j, k]
+                assert np.array_equal(got == 0, want == 0)
+                nz = want != 0
+                if nz.any():
+                    worst = max(worst, float((np.abs(got[nz] - want[nz]) / want[nz]).max()))
+    assert worst < 1e-6, worst          # the .spd files carry 8 significant digits
