@@ -6,7 +6,7 @@
 // It is meant for the cuda_* variants: a Dr.Jit CUDA array already is one device plane per component, so every
 // Emitter call maps 1:1 onto one C-ABI entry point of include/sunsky_b200.h, enqueued on Dr.Jit's own stream.
 // The same source also instantiates for CPU array types whose `.data()` is host memory (it then uses the *_host
-// entry points); that is what tests/test_adapter_cpu.py type-checks against the reference's headers.
+// entry points); that is what tests/test_host_cpu.py::test_adapter_plugin_type_checks type-checks against the reference's headers.
 //
 // Member-by-member correspondence (reference: src/emitters/sunsky.cpp):
 //   constructor / init_from_props  :162-218, :889-948   -> ssk_params + ssk_create

@@ -550,44 +550,48 @@ __device__ __forceinline__ void gst2(float *p, size_t ia, size_t ib, bool two, f
 template <int A, bool Spectral, bool Weight = true>
 __global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
 sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    // Round 2: every WARP sorts and processes its own 512-sample tile (ballots + __syncwarp only). The CTA-wide
+    // version spent 23 % of its stall samples at __syncthreads: with w ~ 0.5 the first four warps of a CTA always
+    // got TGMM samples and the last four sun-cone samples, and the tile took as long as the slower technique.
     __shared__ __align__(16) HotBlock S;
     __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
-    __shared__ __align__(8) float tu0[kTile], tu1[kTile];
-    __shared__ unsigned short perm[kTile];
-    __shared__ int wcount[kThreads / 32][2];
+    __shared__ __align__(8) float tu0_all[kThreads / 32][kTile], tu1_all[kThreads / 32][kTile];
+    __shared__ unsigned short perm_all[kThreads / 32][kTile];
     stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
-    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float *tu0 = tu0_all[warp], *tu1 = tu1_all[warp];
+    unsigned short *perm = perm_all[warp];
     const unsigned lt = (1u << lane) - 1u;
     const size_t n_tiles = (n + kTile - 1) / kTile;
-    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const size_t warps_total = (size_t) gridDim.x * (kThreads / 32);
+    for (size_t tile = (size_t) blockIdx.x * (kThreads / 32) + warp; tile < n_tiles; tile += warps_total) {
         const size_t base = tile * kTile;
         const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
-        // 1. stage the tile's samples (coalesced 64-bit loads) and classify
-        const int l0 = 2 * t, l1 = 2 * t + 1;
-        float2 v0 = f2(0.f, 0.f), v1 = f2(0.f, 0.f);
-        if (l1 < valid) { v0 = __ldcs(reinterpret_cast<const float2 *>(a.u0 + base + l0)); v1 = __ldcs(reinterpret_cast<const float2 *>(a.u1 + base + l0)); }
-        else if (l0 < valid) { v0.x = __ldcs(a.u0 + base + l0); v1.x = __ldcs(a.u1 + base + l0); }
-        tu0[l0] = v0.x; tu0[l1] = v0.y; tu1[l0] = v1.x; tu1[l1] = v1.y;
-        const bool ok0 = l0 < valid, ok1 = l1 < valid;
-        const bool sky0 = ok0 && v0.x < U.sky_w, sky1 = ok1 && v0.y < U.sky_w;
-        const unsigned bs0 = __ballot_sync(0xffffffffu, sky0), bs1 = __ballot_sync(0xffffffffu, sky1);
-        const unsigned bn0 = __ballot_sync(0xffffffffu, ok0 && !sky0), bn1 = __ballot_sync(0xffffffffu, ok1 && !sky1);
-        if (lane == 0) { wcount[warp][0] = __popc(bs0) + __popc(bs1); wcount[warp][1] = __popc(bn0) + __popc(bn1); }
-        __syncthreads();
-        // 2. slot of each sample: sky samples first (warp-major), then sun samples
-        int sky_before = 0, sun_before = 0, sky_total = 0;
-#pragma unroll
-        for (int w = 0; w < kThreads / 32; ++w) {
-            const int cs = wcount[w][0], cn = wcount[w][1];
-            if (w < warp) { sky_before += cs; sun_before += cn; }
-            sky_total += cs;
+        // 1. + 2. stage the tile's samples (coalesced 64-bit loads), classify, and give every sample its slot: sky
+        //    samples fill the tile from the front, sun samples from the back (of the valid part)
+        int n_sky = 0, n_sun = 0;
+#pragma unroll 2
+        for (int k = 0; k < kTile / 64; ++k) {
+            const int l0 = 64 * k + 2 * lane, l1 = l0 + 1;
+            float2 v0 = f2(0.f, 0.f), v1 = f2(0.f, 0.f);
+            if (l1 < valid) { v0 = __ldcs(reinterpret_cast<const float2 *>(a.u0 + base + l0)); v1 = __ldcs(reinterpret_cast<const float2 *>(a.u1 + base + l0)); }
+            else if (l0 < valid) { v0.x = __ldcs(a.u0 + base + l0); v1.x = __ldcs(a.u1 + base + l0); }
+            *reinterpret_cast<float2 *>(tu0 + l0) = v0; *reinterpret_cast<float2 *>(tu1 + l0) = v1;
+            const bool ok0 = l0 < valid, ok1 = l1 < valid;
+            const bool sky0 = ok0 && v0.x < U.sky_w, sky1 = ok1 && v0.y < U.sky_w;
+            const unsigned bs0 = __ballot_sync(0xffffffffu, sky0), bs1 = __ballot_sync(0xffffffffu, sky1);
+            const unsigned bn0 = __ballot_sync(0xffffffffu, ok0 && !sky0), bn1 = __ballot_sync(0xffffffffu, ok1 && !sky1);
+            if (sky0) perm[n_sky + __popc(bs0 & lt)] = (unsigned short) l0;
+            else if (ok0) perm[valid - 1 - (n_sun + __popc(bn0 & lt))] = (unsigned short) l0;
+            if (sky1) perm[n_sky + __popc(bs0) + __popc(bs1 & lt)] = (unsigned short) l1;
+            else if (ok1) perm[valid - 1 - (n_sun + __popc(bn0) + __popc(bn1 & lt))] = (unsigned short) l1;
+            n_sky += __popc(bs0) + __popc(bs1); n_sun += __popc(bn0) + __popc(bn1);
         }
-        if (sky0) perm[sky_before + __popc(bs0 & lt)] = (unsigned short) l0;
-        else if (ok0) perm[sky_total + sun_before + __popc(bn0 & lt)] = (unsigned short) l0;
-        if (sky1) perm[sky_before + __popc(bs0) + __popc(bs1 & lt)] = (unsigned short) l1;
-        else if (ok1) perm[sky_total + sun_before + __popc(bn0) + __popc(bn1 & lt)] = (unsigned short) l1;
-        __syncthreads();
+        __syncwarp();
+#pragma unroll 1
+        for (int k = 0; k < kTile / 64; ++k) {
+        const int l0 = 64 * k + 2 * lane, l1 = l0 + 1;
         // 3. two samples of one technique per thread
         if (l0 < valid) {
             const bool two = l1 < valid;
@@ -638,7 +642,8 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
                 }
             }
         }
-        __syncthreads();               // tu0 / tu1 / perm are rewritten by the next tile
+        }
+        __syncwarp();                  // tu0 / tu1 / perm are rewritten by the next tile
     }
 }
 

@@ -25,7 +25,15 @@ public:
             // nearest bin of the 40 nm grid starting at 320 nm
             UnpolarizedSpectrum r;
             for (size_t c = 0; c < r.size(); ++c) {
-                if constexpr (dr::is_array_v<Float>) {
+                if constexpr (dr::is_jit_v<Float>) {            // JIT arrays (adapter type-check): lanes through a host copy
+                    size_t n = si.wavelengths[c].size();
+                    std::vector<float> tmp(n);
+                    for (size_t l = 0; l < n; ++l) {
+                        int b = (int) ((si.wavelengths[c].entry(l) - 320.f) / 40.f + 0.5f);
+                        tmp[l] = m_values[std::min(std::max(b, 0), (int) m_values.size() - 1)];
+                    }
+                    r[c] = dr::load<Float>(tmp.data(), n);
+                } else if constexpr (dr::is_array_v<Float>) {
                     size_t n = si.wavelengths[c].size();
                     Float v = dr::zeros<Float>(n);
                     for (size_t l = 0; l < n; ++l) {
