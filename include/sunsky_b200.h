@@ -296,8 +296,11 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
 
 /* Measurement aid: the time the bare transfers of a *_host call take with nothing else in the way -- h2d_bytes from
  * pinned host memory on one stream while d2h_bytes go back on another, in pieces of piece_bytes (0 = one copy per
- * direction), best of `reps` after a warm-up. bench.py reports the *_host entry points against this ceiling. */
-int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds);
+ * direction): best and (nullable) mean of `reps` passes after a warm-up. With several GPUs sharing the host's memory
+ * and PCIe root the mean of passes that every rank runs at the same time is the contended ceiling. bench.py reports
+ * the *_host entry points against it. */
+int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds,
+                          double *mean_seconds);
 
 /* Number of kernel launches issued through this library since load (bench bookkeeping). */
 uint64_t ssk_launch_count(void);

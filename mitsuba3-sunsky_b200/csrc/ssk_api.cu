@@ -935,7 +935,8 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
     return SSK_OK;
 }
 
-int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds) {
+int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds,
+                          double *mean_seconds) {
     if (!best_seconds || reps < 1) return fail(SSK_ERR_INVALID, "bad argument");
     DeviceGuard dg; if (int rc = dg.enter(device)) return rc;
     char *h_in = nullptr, *h_out = nullptr, *d_in = nullptr, *d_out = nullptr;
@@ -953,7 +954,7 @@ int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t
     SSK_CUDA(cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking));
     SSK_CUDA(cudaEventCreate(&e0)); SSK_CUDA(cudaEventCreate(&e1)); SSK_CUDA(cudaEventCreate(&e2));
     if (!piece_bytes) piece_bytes = std::max(h2d_bytes, d2h_bytes);
-    double best = 1e30;
+    double best = 1e30, total = 0.0;
     for (int r = 0; r < reps + 1; ++r) {                       // first pass is a warm-up
         SSK_CUDA(cudaDeviceSynchronize());
         auto t0 = std::chrono::steady_clock::now();
@@ -963,9 +964,10 @@ int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t
             SSK_CUDA(cudaMemcpyAsync(h_out + o, d_out + o, std::min(piece_bytes, d2h_bytes - o), cudaMemcpyDeviceToHost, s1));
         SSK_CUDA(cudaStreamSynchronize(s0)); SSK_CUDA(cudaStreamSynchronize(s1));
         double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-        if (r > 0) best = std::min(best, dt);
+        if (r > 0) { best = std::min(best, dt); total += dt; }
     }
     *best_seconds = best;
+    if (mean_seconds) *mean_seconds = total / reps;
     return SSK_OK;
 }
 

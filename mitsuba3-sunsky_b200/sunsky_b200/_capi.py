@@ -76,7 +76,8 @@ SYMBOLS = {
     "ssk_pdf_direction_host": (C.c_int, [CTX, FPP, C.c_size_t, FP]),
     "ssk_sample_direction_host": (C.c_int, [CTX, FPP, FPP, FPP, C.c_size_t, FPP, FP, FPP, FPP, FP]),
     "ssk_launch_count": (C.c_uint64, []),
-    "ssk_host_copy_ceiling": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
+    "ssk_host_copy_ceiling": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.POINTER(C.c_double),
+                                      C.POINTER(C.c_double)]),
     "ssk_debug_fdiv_by_device": (C.c_int, [FP, FP, FP, C.c_size_t, C.c_void_p]),
     "ssk_sun_coordinates": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                       C.c_float, C.c_float, FP]),
