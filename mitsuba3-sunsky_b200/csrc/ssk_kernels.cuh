@@ -54,11 +54,17 @@ constexpr int kThreads = 256;
 
 /// Copy the emitter block from global to shared memory (16-byte accesses) and, for FAST spectral
 /// kernels, build the bin-pair table of eval_spec (build_pair_table's layout). Ends with a barrier.
-__device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const EmitterBlock *src) {
+__device__ __forceinline__ void stage_block(HotBlock *dst, float2 *pairs, const EmitterBlock *src, bool exact_pairs = false) {
     const uint4 *s = reinterpret_cast<const uint4 *>(src);
     uint4 *d = reinterpret_cast<uint4 *>(dst);
     for (int i = threadIdx.x; i < (int) (sizeof(HotBlock) / 16); i += blockDim.x) d[i] = __ldg(s + i);
-    if (pairs)
+    if (pairs && exact_pairs) {                    // EXACT spectral kernels: build_exact_pair_table's layout
+        for (int i = threadIdx.x; i < kExactPairTable; i += blockDim.x) {
+            int c = i % kChanPad, k = i / kChanPad;
+            const float *row = k < kSkyParams ? &src->sky_params[k][0] : &src->sky_rad[0];
+            pairs[i] = make_float2(__ldg(row + c), c + 1 < kChanPad ? __ldg(row + c + 1) : 0.f);
+        }
+    } else if (pairs)
         for (int i = threadIdx.x; i < kPairTable; i += blockDim.x) {
             int c = i % kChanPad, k = i / kChanPad;
             const float *row = &src->sky_fast[k][0];
@@ -178,8 +184,8 @@ __global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? SSK_SPECF_M
 eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
                  OutPlanes4 out, size_t n, float dir_sign) {
     __shared__ __align__(16) HotBlock S;
-    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
-    stage_block(&S, A == kFast ? pairs : nullptr, blk);
+    __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : kExactPairTable];
+    stage_block(&S, pairs, blk, A == kExact);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
     if (R == 1 && A == kFast && SSK_EVAL_PREFETCH == 1) {
@@ -199,7 +205,7 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
                 nx = __ldcs(in.x + j); ny = __ldcs(in.y + j); nz = __ldcs(in.z + j);
                 na = __ldcs(wav.a + j); nb = __ldcs(wav.b + j); nc = __ldcs(wav.c + j); nd = __ldcs(wav.d + j);
             }
-            eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
+            eval_spec<A, A == kExact>(U, S, pairs, sun_rad, wi, wl, true, o);
             __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]); __stcs(out.d + i, o[3]);
         }
         return;
@@ -212,7 +218,7 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
         for (int k = 0; k < R; ++k) {
             Vec3 wi = { dir_sign * getk<R>(x, k), dir_sign * getk<R>(y, k), dir_sign * getk<R>(z, k) };
             float wl[4] = { getk<R>(w0, k), getk<R>(w1, k), getk<R>(w2, k), getk<R>(w3, k) }, o[4];
-            eval_spec<A>(U, S, pairs, sun_rad, wi, wl, true, o);
+            eval_spec<A, A == kExact>(U, S, pairs, sun_rad, wi, wl, true, o);
             setk<R>(o0, k, o[0]); setk<R>(o1, k, o[1]); setk<R>(o2, k, o[2]); setk<R>(o3, k, o[3]);
         }
         storer<R>(out.a, i, n, o0); storer<R>(out.b, i, n, o1); storer<R>(out.c, i, n, o2); storer<R>(out.d, i, n, o3);
@@ -547,6 +553,16 @@ __device__ __forceinline__ void gst2(float *p, size_t ia, size_t ib, bool two, f
     __stcs(p + ia, v.x);
     if (two) __stcs(p + ib, v.y);
 }
+// Two implementations, bit-identical results. SSK_SORT_PER_WARP = 0 (default): the CTA sorts a 512-sample tile
+// (three __syncthreads per tile). = 1: every warp sorts its own 512-sample tile (ballots and __syncwarp only). ncu of
+// the CTA version showed 23 % of stall samples at the barriers, but without them the warps of an SM drift apart and
+// the two techniques' code paths (65 KB of SASS) thrash the instruction cache: `no_inst` becomes the top stall (29 %)
+// and the kernel is 4 % SLOWER (20.9 vs 21.7 Gsamples/s, profiles/r2_summary.md). The barriers were acting as a
+// phase lock that keeps the instruction working set small.
+#ifndef SSK_SORT_PER_WARP
+#define SSK_SORT_PER_WARP 0
+#endif
+#if SSK_SORT_PER_WARP
 template <int A, bool Spectral, bool Weight = true>
 __global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
 sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
@@ -646,6 +662,104 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
         __syncwarp();                  // tu0 / tu1 / perm are rewritten by the next tile
     }
 }
+
+#else
+template <int A, bool Spectral, bool Weight = true>
+__global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
+sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
+    __shared__ __align__(16) HotBlock S;
+    __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
+    __shared__ __align__(8) float tu0[kTile], tu1[kTile];
+    __shared__ unsigned short perm[kTile];
+    __shared__ int wcount[kThreads / 32][2];
+    stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
+    const float *sun_rad = blk->sun_rad;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const size_t n_tiles = (n + kTile - 1) / kTile;
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const size_t base = tile * kTile;
+        const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
+        // 1. stage the tile's samples (coalesced 64-bit loads) and classify
+        const int l0 = 2 * t, l1 = 2 * t + 1;
+        float2 v0 = f2(0.f, 0.f), v1 = f2(0.f, 0.f);
+        if (l1 < valid) { v0 = __ldcs(reinterpret_cast<const float2 *>(a.u0 + base + l0)); v1 = __ldcs(reinterpret_cast<const float2 *>(a.u1 + base + l0)); }
+        else if (l0 < valid) { v0.x = __ldcs(a.u0 + base + l0); v1.x = __ldcs(a.u1 + base + l0); }
+        tu0[l0] = v0.x; tu0[l1] = v0.y; tu1[l0] = v1.x; tu1[l1] = v1.y;
+        const bool ok0 = l0 < valid, ok1 = l1 < valid;
+        const bool sky0 = ok0 && v0.x < U.sky_w, sky1 = ok1 && v0.y < U.sky_w;
+        const unsigned bs0 = __ballot_sync(0xffffffffu, sky0), bs1 = __ballot_sync(0xffffffffu, sky1);
+        const unsigned bn0 = __ballot_sync(0xffffffffu, ok0 && !sky0), bn1 = __ballot_sync(0xffffffffu, ok1 && !sky1);
+        if (lane == 0) { wcount[warp][0] = __popc(bs0) + __popc(bs1); wcount[warp][1] = __popc(bn0) + __popc(bn1); }
+        __syncthreads();
+        // 2. slot of each sample: sky samples first (warp-major), then sun samples
+        int sky_before = 0, sun_before = 0, sky_total = 0;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) {
+            const int cs = wcount[w][0], cn = wcount[w][1];
+            if (w < warp) { sky_before += cs; sun_before += cn; }
+            sky_total += cs;
+        }
+        if (sky0) perm[sky_before + __popc(bs0 & lt)] = (unsigned short) l0;
+        else if (ok0) perm[sky_total + sun_before + __popc(bn0 & lt)] = (unsigned short) l0;
+        if (sky1) perm[sky_before + __popc(bs0) + __popc(bs1 & lt)] = (unsigned short) l1;
+        else if (ok1) perm[sky_total + sun_before + __popc(bn0) + __popc(bn1 & lt)] = (unsigned short) l1;
+        __syncthreads();
+        // 3. two samples of one technique per thread
+        if (l0 < valid) {
+            const bool two = l1 < valid;
+            const int la = perm[l0], lb = two ? perm[l1] : la;
+            const size_t ia = base + la, ib = base + lb;
+            DirSampleP s = sample_dir_p<A>(U, S, f2(tu0[la], two ? tu0[lb] : 0.5f), f2(tu1[la], two ? tu1[lb] : 0.5f));
+            gst2(a.dx, ia, ib, two, s.d_world.x); gst2(a.dy, ia, ib, two, s.d_world.y); gst2(a.dz, ia, ib, two, s.d_world.z);
+            gst2(a.pdf, ia, ib, two, s.pdf);
+            // first pass: weight plane 0 keeps, per SLOT of the sorted tile, the sample it holds and its `active`
+            // flag, so that weight_spec_sorted_kernel walks the samples in the same technique order
+            if (!Weight) {
+                __stcs(a.q0 + base + l0, __int_as_float(la | (s.active0 ? kTile : 0)));
+                if (two) __stcs(a.q0 + base + l1, __int_as_float(lb | (s.active1 ? kTile : 0)));
+            }
+            float2 e[4];
+            if (Weight) {
+            if (Spectral) {
+                float2 w0 = gld2(a.w0, ia, ib, two, 0.f), w1 = gld2(a.w1, ia, ib, two, 0.f), w2 = gld2(a.w2, ia, ib, two, 0.f),
+                       w3 = gld2(a.w3, ia, ib, two, 0.f);
+                float ea[4], eb[4];
+                const float wa[4] = { w0.x, w1.x, w2.x, w3.x }, wb[4] = { w0.y, w1.y, w2.y, w3.y };
+                eval_spec<A>(U, S, pairs, sun_rad, Vec3{ -s.d_world.x.x, -s.d_world.y.x, -s.d_world.z.x }, wa, s.active0, ea);
+                eval_spec<A>(U, S, pairs, sun_rad, Vec3{ -s.d_world.x.y, -s.d_world.y.y, -s.d_world.z.y }, wb, s.active1 && two, eb);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) e[c] = f2(ea[c], eb[c]);
+            } else {
+                Vec3p wi = { neg2(s.d_world.x), neg2(s.d_world.y), neg2(s.d_world.z) };
+                eval_rgb_p<A>(U, sun_rad, wi, s.active0, s.active1 && two, e);
+            }
+            const float2 inv_pdf = A == kFast ? f2(hw_rcp(s.pdf.x), hw_rcp(s.pdf.y)) : f2(fdiv(1.f, s.pdf.x), fdiv(1.f, s.pdf.y));
+#pragma unroll
+            for (int c = 0; c < (Spectral ? 4 : 3); ++c) {
+                float2 w = mul2(e[c], inv_pdf);
+                w = f2((fabsf(w.x) < INFINITY) ? w.x : 0.f, (fabsf(w.y) < INFINITY) ? w.y : 0.f);
+                gst2(c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3, ia, ib, two, w);
+            }
+            }
+            if (a.ox || a.dist) {          // bounding-sphere bookkeeping (sunsky.cpp:415-421), as sample_pair_kernel
+                float2 px = f2(0.f, 0.f), py = px, pz = px;
+                if (a.px) { px = gld2(a.px, ia, ib, two, 0.f); py = gld2(a.py, ia, ib, two, 0.f); pz = gld2(a.pz, ia, ib, two, 0.f); }
+                Vec3p rel = { add2s(px, -U.bs_center[0]), add2s(py, -U.bs_center[1]), add2s(pz, -U.bs_center[2]) };
+                float2 nr = sqrt2(sqnorm3_p(rel));
+                float2 dd = mul2s(f2(fmaxf(U.bs_radius, nr.x), fmaxf(U.bs_radius, nr.y)), 2.f);
+                if (a.dist) gst2(a.dist, ia, ib, two, dd);
+                if (a.ox) {
+                    gst2(a.ox, ia, ib, two, fma2(s.d_world.x, dd, px)); gst2(a.oy, ia, ib, two, fma2(s.d_world.y, dd, py));
+                    gst2(a.oz, ia, ib, two, fma2(s.d_world.z, dd, pz));
+                }
+            }
+        }
+        __syncthreads();               // tu0 / tu1 / perm are rewritten by the next tile
+    }
+}
+
+#endif
 
 /// Second pass after sample_sorted_kernel<A,false,false>: the tile's samples in technique order (sky samples in the
 /// low slots, sun-cone samples -- all inside the sun disc -- in the high ones), thread t takes slots t and

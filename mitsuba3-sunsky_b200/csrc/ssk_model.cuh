@@ -222,6 +222,33 @@ SSK_HD float c1_fast(float T0, float T1, float T11, float s, bool &ok) {
 #endif
 }
 
+/// render_sky_2 with the coefficient pairs {A_k(ch), A_k(ch + 1)} read as ONE 64-bit value each from a pair table
+/// (EXACT spectral kernels, exact_pair_index): 10 loads per wavelength instead of 20 scalar ones plus their address
+/// arithmetic. Same operations in the same order as render_sky_2(P, ch, r).
+constexpr int kExactPairRows = kSkyParams + 1;           // 9 coefficients + mean radiance
+constexpr int kExactPairTable = kExactPairRows * kChanPad;
+SSK_HD float2 render_sky_2(const float2 *xp, int ch, const RayTerms &r) {
+    float2 A0 = xp[0 * kChanPad + ch], A1 = xp[1 * kChanPad + ch], A2 = xp[2 * kChanPad + ch], A3 = xp[3 * kChanPad + ch],
+           A4 = xp[4 * kChanPad + ch], A5 = xp[5 * kChanPad + ch], A6 = xp[6 * kChanPad + ch], A7 = xp[7 * kChanPad + ch],
+           A8 = xp[8 * kChanPad + ch], L = xp[9 * kChanPad + ch];
+    float2 c1 = add2x(mul2(A0, dexp_2(mul2s(A1, r.inv_denom_c1))), splat2(1.f));
+    float2 arg = add2x(neg2(mul2s(mul2s(A8, 2.f), r.cos_gamma)), add2x(mul2(A8, A8), splat2(1.f)));
+    float2 pw = dpow15_2(arg);
+    float2 chi = f2(fdiv(r.one_plus_cg2, pw.x), fdiv(r.one_plus_cg2, pw.y));
+    float2 c2 = add2x(mul2(A3, dexp_2(mul2s(A4, r.gamma))), A2);
+    c2 = add2x(mul2s(A5, r.cos_gamma_sqr), c2);
+    c2 = add2x(mul2(A6, chi), c2);
+    c2 = add2x(mul2s(A7, r.sqrt_cos_theta), c2);
+    return mul2(mul2(c1, c2), L);
+}
+SSK_HD void build_exact_pair_table(const HotBlock &B, float2 *xp) {
+    for (int k = 0; k < kExactPairRows; ++k)
+        for (int c = 0; c < kChanPad; ++c) {
+            const float *row = k < kSkyParams ? B.sky_params[k] : B.sky_rad;
+            xp[k * kChanPad + c] = f2(row[c], c + 1 < kChanPad ? row[c + 1] : 0.f);
+        }
+}
+
 /// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
 /// lane-dependent channels); the radiance scale T[10] folds sky_scale and, in RGB mode, the CIE-Y
 /// normalisation. What is approximated and what is not follows the conditioning of the formula:
@@ -646,7 +673,7 @@ SSK_COLD float4 add_sun_spec_cold(const HotBlock &U, const HotBlock &S, const fl
 /// wavelength are evaluated as one float2 pair. FAST mode reads `pairs` (build_pair_table); lanes where a
 /// channel cancels redo all four wavelengths with the reference sequence, sun-disc lanes add the sun term,
 /// both behind one call per ray.
-template <int A>
+template <int A, bool ExactPairs = false>
 SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs, const float *sun_rad,
                       const Vec3 &wi, const float wav[4], bool active_in, float out[4]) {
     EvalGeom g = eval_geom<A>(U, wi, active_in);
@@ -674,7 +701,8 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
             ok = ok && ok_w;
             out[w] = lerp(sk.x, sk.y, b.f);
         } else {
-            float2 sk = render_sky_2(S, b.lo, g.r);
+            // EXACT: with ExactPairs the kernel staged build_exact_pair_table's table in `pairs`
+            float2 sk = ExactPairs ? render_sky_2(pairs, b.lo, g.r) : render_sky_2(S, b.lo, g.r);
             out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
         }
     }

@@ -651,7 +651,7 @@ def test_eval_jvp_matches_the_dual_number_oracle(ssk, spectral, t, a, eta, arith
     the reference library in tests/test_jvp_oracle_cpu.py). Covers the three Differentiable parameters of traverse()
     (sunsky.cpp:222-237) -- turbidity, albedo per channel, sun_direction -- alone and combined, sky lanes and lanes
     inside the sun disc. Tolerance: 2e-5 of the largest derivative on sky lanes (fp32 kernel vs fp64 oracle; measured
-    <= 9e-6); 3e-3 relative on sun-disc lanes away from the disc edge (where d cos(psi) is unbounded): the sun
+    <= 9e-6); 1e-3 relative (floored at a tenth of the largest derivative) on sun-disc lanes away from the disc edge (where d cos(psi) is unbounded): the sun
     polynomial multiplies 1e13-sized coefficients that cancel, so ANY fp32 evaluation -- the reference's included, see
     test04's 1.6e-3 against the fp64 .spd spectra -- carries ~1e-3 of noise in the value and in its derivative."""
     import torch
@@ -680,10 +680,12 @@ def test_eval_jvp_matches_the_dual_number_oracle(ssk, spectral, t, a, eta, arith
         # sun-disc lanes: relative, away from the edge (cos(psi) > 0.3  <=>  sin(gamma) < 0.954 sin(half aperture))
         cosg = (wo.astype(np.float64) * sdn[:, None]).sum(0)
         inner = hit & (np.sqrt(np.maximum(1 - cosg * cosg, 0)) < 0.95 * np.sin(np.radians(0.5358 / 2)))
-        big = np.abs(tan) > 1e-3 * np.abs(tan[:, inner]).max()
-        m = big & inner[None, :]
+        m = np.broadcast_to(inner[None, :], tan.shape)
         assert m.sum() > 100
-        assert (np.abs(got - tan)[m] / np.abs(tan[m])).max() <= 3e-3, (d_t, d_a is not None, d_s is not None)
+        # relative to the lane's own derivative, but not below a tenth of the largest one: in the combined tangent the
+        # turbidity and sun-direction parts can cancel, and the noise of each part does not
+        floor = 0.1 * np.abs(tan[m]).max()
+        assert (np.abs(got - tan)[m] / np.maximum(np.abs(tan[m]), floor)).max() <= 1e-3, (d_t, d_a is not None, d_s is not None)
     # an emitter built from a date / location record has no sun_direction parameter (sunsky.cpp:226-238)
     rec = ssk.SunskyEmitter(spectral=spectral, hour=11.0)
     with pytest.raises(ssk.SunskyError):
