@@ -127,6 +127,21 @@ int ssk_update(ssk_ctx *ctx, const ssk_params *p);
  * synchronisation (0.14 ms per emitter one by one; see DESIGN.md for the batched figure). On failure no context is
  * modified. */
 int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n);
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). Same result as
+ * ssk_update_batch -- every context ends in exactly the state n ssk_update calls produce -- but the call makes no
+ * cudaMalloc / cudaMallocHost / cudaFree and creates no stream: the scratch of the setup quadrature (node values of
+ * the two 200 x 200 integrands, chain partials, Gauss-Legendre table) lives in one file-scope `static __device__`
+ * array of SSK_NOALLOC_MAX_EMITTERS x 4.125 MiB (+ 2 KiB) that every GPU which loads the library holds until the
+ * process exits; kernels and copies run on the default stream and the call returns when the blocks are on the
+ * device. n > SSK_NOALLOC_MAX_EMITTERS is rejected with SSK_ERR_INVALID (split the batch), so are contexts without
+ * a device. All calls share the one array per GPU and it keeps the previous call's contents (the partial sums are
+ * cleared at the start of every call, the node values are overwritten in full): calls on one device serialise on a
+ * mutex inside the library, and nothing else may use the array -- two processes' worth of calls cannot overlap on
+ * the GPU because each process has its own copy. Contexts must exist already (ssk_create allocates). On failure no
+ * context is modified. */
+#define SSK_NOALLOC_MAX_EMITTERS 2
+int ssk_update_batch_noalloc(ssk_ctx *const *ctxs, const ssk_params *params, int n);
 
 /* set_scene(): bounding sphere from the scene bbox; NULL pointers = invalid bbox (:287-301). */
 int ssk_set_scene(ssk_ctx *ctx, const float *bbox_min, const float *bbox_max);

@@ -787,6 +787,109 @@ int ssk_update_batch(ssk_ctx *const *ctxs, const ssk_params *params, int n) {
     });
 }
 
+// ---- parameters_changed without any CUDA allocation (no counterpart in the reference) ----------
+// The setup quadrature needs scratch: per emitter the node values of both integrands (chain-major, kEmitterStride
+// floats), the chain partials, and the Gauss-Legendre table. ssk_update / ssk_update_batch keep these in lazily
+// cudaMalloc'ed buffers; this variant keeps them in ONE file-scope device array of fixed size, resident on every GPU
+// that loads the library until the process exits:
+//   [ kNoAllocMaxEmitters x kEmitterStride | kNoAllocMaxEmitters x kMaxChains partials (padded) | 2 x kQuadN table ]
+constexpr int kNoAllocMaxEmitters = SSK_NOALLOC_MAX_EMITTERS;
+constexpr size_t kNoAllocPartialOff = (size_t) kNoAllocMaxEmitters * kEmitterStride;
+constexpr size_t kNoAllocPartialLen = ((size_t) kNoAllocMaxEmitters * kMaxChains + 63) / 64 * 64;      // keeps the table 256-byte aligned
+constexpr size_t kNoAllocTableOff = kNoAllocPartialOff + kNoAllocPartialLen;
+constexpr size_t kNoAllocFloats = kNoAllocTableOff + 2 * kQuadN;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+
+struct NoAllocDevice {      // one per device: the array's address ON THAT DEVICE (the symbol itself is a host-side stand-in)
+    float *ptr = nullptr;
+    std::mutex mu;          // calls on one device serialise here; calls that overlap on the GPU would race on the array
+};
+NoAllocDevice g_noalloc[kMaxDevices];
+
+/// Address of the scratch array on `device` (current device on entry); the first call per device also puts the
+/// Gauss-Legendre table into its region. No allocation: cudaGetSymbolAddress only resolves the module's symbol.
+int noalloc_scratch(int device, float **out) {
+    NoAllocDevice &d = g_noalloc[device];
+    if (!d.ptr) {
+        float *p = nullptr;
+        SSK_CUDA(cudaGetSymbolAddress((void **) &p, g_noalloc_scratch));
+        if (!p) return fail(SSK_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the no-alloc scratch array");
+        SSK_CUDA(cudaMemcpy(p + kNoAllocTableOff, gauss_legendre_200().data(), 2 * kQuadN * sizeof(float), cudaMemcpyHostToDevice));
+        d.ptr = p;
+    }
+    *out = d.ptr;
+    return SSK_OK;
+}
+
+/// quadrature_device_batch on the static scratch, default stream, synchronous copies into stack buffers
+int quadrature_device_noalloc(ssk_ctx *const *ctxs, int n, float (*sky_rad)[11], float (*sun_rad)[11]) {
+    const int device = ctxs[0]->device;
+    if (device >= kMaxDevices) return fail(SSK_ERR_UNSUPPORTED, "device ordinal too large");
+    std::lock_guard<std::mutex> lock(g_noalloc[device].mu);
+    DeviceGuard dg; if (int rc = dg.enter(device)) return rc;
+    float *base = nullptr;
+    if (int rc = noalloc_scratch(device, &base)) return rc;
+    float *d_buf = base, *d_partial = base + kNoAllocPartialOff, *d_gl = base + kNoAllocTableOff;
+    const int C = ctxs[0]->E.n_channels, nchains = 2 * C * kQuadChunks;
+    // the array keeps the previous call's contents: the partials start from zero so that a launch that failed to run
+    // cannot hand back the last call's sums (the node values are overwritten in full for every chain that is read)
+    SSK_CUDA(cudaMemsetAsync(d_partial, 0, kNoAllocPartialLen * sizeof(float), 0));
+    for (int e = 0; e < n; ++e) {
+        ssk_ctx *ctx = ctxs[e];
+        SSK_CUDA(cudaMemcpyAsync(ctx->d_block, &ctx->E.block, sizeof(EmitterBlock), cudaMemcpyHostToDevice, 0));
+        setup_quadrature_kernel<<<(2 * kQuadNodes + kThreads - 1) / kThreads, kThreads>>>(
+            ctx->E.block, ctx->d_block, d_gl, d_buf + (size_t) e * kEmitterStride, C);
+    }
+    setup_sum_kernel<<<n * nchains, 32>>>(d_buf, d_partial, nchains, kEmitterStride);
+    g_launches += n + 1;
+    SSK_CUDA(cudaGetLastError());
+    float h_partial[kNoAllocMaxEmitters * kMaxChains];
+    SSK_CUDA(cudaMemcpy(h_partial, d_partial, (size_t) n * nchains * sizeof(float), cudaMemcpyDeviceToHost));
+    for (int e = 0; e < n; ++e)
+        for (int which = 0; which < 2; ++which) {
+            const float J = which == 0 ? quad_sky_jacobian() : quad_sun_jacobian(ctxs[e]->E.block);
+            for (int c = 0; c < C; ++c) {
+                float total = 0.f;                   // llvm_block_sum: partials added in chunk order
+                for (int k = 0; k < kQuadChunks; ++k) total = total + h_partial[e * nchains + (which * C + c) * kQuadChunks + k];
+                (which == 0 ? sky_rad : sun_rad)[e][c] = total * J;
+            }
+        }
+    return SSK_OK;
+}
+
+int ssk_update_batch_noalloc(ssk_ctx *const *ctxs, const ssk_params *params, int n) {
+    if (n < 0 || (n > 0 && (!ctxs || !params))) return fail(SSK_ERR_INVALID, "null argument");
+    if (n == 0) return SSK_OK;
+    if (n > kNoAllocMaxEmitters)
+        return fail(SSK_ERR_INVALID, "ssk_update_batch_noalloc: " + std::to_string(n) + " emitters exceed the fixed scratch of SSK_NOALLOC_MAX_EMITTERS = " +
+                                     std::to_string(kNoAllocMaxEmitters) + " per call; split the batch or use ssk_update_batch");
+    for (int i = 0; i < n; ++i) {
+        if (!ctxs[i]) return fail(SSK_ERR_INVALID, "null context");
+        if (ctxs[i]->device != ctxs[0]->device || ctxs[i]->mode != ctxs[0]->mode)
+            return fail(SSK_ERR_INVALID, "ssk_update_batch_noalloc: contexts must share one device and one mode");
+        for (int j = 0; j < i; ++j)
+            if (ctxs[j] == ctxs[i]) return fail(SSK_ERR_INVALID, "ssk_update_batch_noalloc: a context appears twice");
+    }
+    if (ctxs[0]->device < 0 || !ctxs[0]->d_block)
+        return fail(SSK_ERR_CUDA, "ssk_update_batch_noalloc: context has no CUDA device (the setup kernels have no CPU fallback here)");
+    return guarded([&]() -> int {
+        HostEmitter backup[kNoAllocMaxEmitters];
+        int cur0[kNoAllocMaxEmitters];
+        for (int i = 0; i < n; ++i) { backup[i] = ctxs[i]->E; cur0[i] = ctxs[i]->cur; }
+        auto rollback = [&] { for (int i = 0; i < n; ++i) { ctxs[i]->E = backup[i]; ctxs[i]->cur = cur0[i]; ctxs[i]->d_block = ctxs[i]->ring[cur0[i]]; } };
+        for (int i = 0; i < n; ++i) if (int rc = rotate_block(ctxs[i])) { rollback(); return rc; }
+        try {
+            for (int i = 0; i < n; ++i) build_emitter_pre(ctxs[i]->E, params[i], false);
+            float sky[kNoAllocMaxEmitters][11], sun[kNoAllocMaxEmitters][11];
+            if (int rc = quadrature_device_noalloc(ctxs, n, sky, sun)) { rollback(); return rc; }
+            for (int i = 0; i < n; ++i) build_emitter_post(ctxs[i]->E, sky[i], sun[i]);
+        } catch (...) { rollback(); throw; }
+        for (int i = 0; i < n; ++i)
+            if (int rc = upload_block(ctxs[i])) return rc;
+        return SSK_OK;
+    });
+}
+
 int ssk_set_scene(ssk_ctx *ctx, const float *bmin, const float *bmax) {
     if (!ctx) return fail(SSK_ERR_INVALID, "null context");
     // set_scene (sunsky.cpp:287-301); math::RayEpsilon<float> = 89.40697e-6 (Epsilon * 1500)

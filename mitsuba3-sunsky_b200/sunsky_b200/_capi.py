@@ -55,6 +55,7 @@ SYMBOLS = {
     "ssk_create": (C.c_int, [C.POINTER(Params), C.c_char_p, C.c_int, C.c_int, C.POINTER(CTX)]),
     "ssk_update": (C.c_int, [CTX, C.POINTER(Params)]),
     "ssk_update_batch": (C.c_int, [C.POINTER(CTX), C.POINTER(Params), C.c_int]),
+    "ssk_update_batch_noalloc": (C.c_int, [C.POINTER(CTX), C.POINTER(Params), C.c_int]),
     "ssk_set_scene": (C.c_int, [CTX, FP, FP]),
     "ssk_destroy": (None, [CTX]),
     "ssk_get_state": (C.c_int, [CTX, C.POINTER(State)]),
