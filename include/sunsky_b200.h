@@ -308,6 +308,10 @@ int  ssk_group_sweep(const ssk_group *g, const ssk_params *frames, int n_frames,
 /* Test hook: out[i] = a[i] / b[i] computed with the reciprocal-based division the kernels use for
  * per-emitter constant divisors (device pointers); the tests compare it with IEEE division. */
 int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t n, void *stream);
+/* Test hook for EXACT mode's guarded shortcuts, each beside the sequence it replaces (device pointers, n even):
+ * op 0 / 1: normal-range division a / b by reciprocal refinement / IEEE division; op 2 / 3: exp(a) without / with the
+ * range selects; op 4 / 5: pow(a, 1.5) without / with the special cases. b may be NULL for op >= 2. */
+int ssk_debug_math_device(int op, const float *a, const float *b, float *out, size_t n, void *stream);
 
 /* Measurement aid: the time the bare transfers of a *_host call take with nothing else in the way -- h2d_bytes from
  * pinned host memory on one stream while d2h_bytes go back on another, in pieces of piece_bytes (0 = one copy per

@@ -1038,6 +1038,15 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
     return SSK_OK;
 }
 
+int ssk_debug_math_device(int op, const float *a, const float *b, float *out, size_t n, void *stream) {
+    if (!a || !out || op < 0 || op > 5 || (op < 2 && !b) || (n & 1)) return fail(SSK_ERR_INVALID, "bad argument");
+    if (n == 0) return SSK_OK;
+    math_probe_kernel<<<1184, 256, 0, (cudaStream_t) stream>>>(op, a, b, out, n);
+    g_launches++;
+    SSK_CUDA(cudaGetLastError());
+    return SSK_OK;
+}
+
 int ssk_host_copy_ceiling(int device, size_t h2d_bytes, size_t d2h_bytes, size_t piece_bytes, int reps, double *best_seconds,
                           double *mean_seconds) {
     if (!best_seconds || reps < 1) return fail(SSK_ERR_INVALID, "bad argument");

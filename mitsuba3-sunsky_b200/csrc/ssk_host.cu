@@ -230,6 +230,19 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
         for (int k = 0; k < kFastCoefs; ++k) B.sky_fast[k][c] = fast[k];
     }
     for (int c = C; c < kChanPad; ++c) B.sky_fast[8][c] = 1.f;      // pad channels: keep the -3/2 power finite
+    // EXACT mode's per-ray guard (HotBlock::exact_lim_s): written so that a NaN anywhere disables it
+    {
+        float m1 = 0.f, m4 = 0.f;
+        bool pow_ok = true;
+        for (int c = 0; c < C; ++c) {
+            const float *A = &E.sky_params[c * 9];
+            m1 = fmaxf(m1, A[1]); m4 = fmaxf(m4, fabsf(A[4]));        // c1: only positive exponents are bounded by the guard
+            const double a8 = fabs((double) A[8]), lo = (1.0 - a8) * (1.0 - a8), hi = (1.0 + a8) * (1.0 + a8);
+            pow_ok = pow_ok && lo >= 0x1p-39 && hi <= 0x1p39 && fabsf(A[1]) <= 1e20f && A[4] == A[4] && fabsf(A[0]) <= 1e20f;
+        }
+        B.exact_lim_s = pow_ok ? (m1 > 0.f ? 86.f / m1 : INFINITY) : -1.f;
+        B.exact_lim_gamma = pow_ok ? (m4 > 0.f ? 86.f / m4 : INFINITY) : -1.f;
+    }
     // --- sun radiance table and limb darkening (:191-195 / 274)
     E.sun_radiance.resize(E.data->sun_rad.size() / 10);
     sun_params(E.data->sun_rad, p.turbidity, E.sun_radiance.data());

@@ -48,6 +48,11 @@ constexpr int kThreads = 256;
 #ifndef SSK_SPECX_MINB
 #define SSK_SPECX_MINB 1
 #endif
+// EXACT spectral eval, one ray per thread: 3 CTAs per SM (79 registers, no spills); left to the compiler it takes 89
+// registers and drops to 2 CTAs, which measured 5 % slower
+#ifndef SSK_SPECX1_MINB
+#define SSK_SPECX1_MINB 3
+#endif
 #ifndef SSK_SPECT_MINB
 #define SSK_SPECT_MINB 3           /* TMA-staged FAST spectral eval: resident CTAs per SM (4 = 64 registers, 8 bytes of spill) */
 #endif
@@ -180,7 +185,7 @@ eval_rgb_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
 
 /// eval / eval_direction, spectral (4 wavelengths per ray)
 template <int A, int R>
-__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? SSK_SPECF_MINB : SSK_SPECX_MINB)
+__global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? SSK_SPECF_MINB : (R == 1 ? SSK_SPECX1_MINB : SSK_SPECX_MINB))
 eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, Planes3 in, Planes4 wav,
                  OutPlanes4 out, size_t n, float dir_sign) {
     __shared__ __align__(16) HotBlock S;
@@ -1087,6 +1092,24 @@ __global__ void envmap_dirs_kernel(float *dx, float *dy, float *dz, int width, i
 __global__ void fdiv_by_kernel(const float *a, const float *b, float *out, size_t n) {
     for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t) gridDim.x * blockDim.x)
         out[i] = fdiv_by(a[i], b[i], fdiv(1.f, b[i]));
+}
+
+/// Test hook for the guarded shortcuts of EXACT mode, each next to the sequence it replaces (bit-compared by the tests):
+///   op 0 / 1: fdiv_normal_2(a, b) / IEEE a / b      op 2 / 3: dexp_2<true>(a) / dexp(a)
+///   op 4 / 5: dpow15_2_safe(a) / dpow15(a)
+__global__ void math_probe_kernel(int op, const float *a, const float *b, float *out, size_t n) {
+    for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i + 1 < n; i += (size_t) gridDim.x * blockDim.x * 2) {
+        float2 x = f2(a[i], a[i + 1]), y = b ? f2(b[i], b[i + 1]) : splat2(1.f), r;
+        switch (op) {
+            case 0: r = fdiv_normal_2(x, y); break;
+            case 1: r = f2(fdiv(x.x, y.x), fdiv(x.y, y.y)); break;
+            case 2: r = dexp_2<true>(x); break;
+            case 3: r = f2(dexp(x.x), dexp(x.y)); break;
+            case 4: r = dpow15_2_safe(x); break;
+            default: r = f2(dpow15(x.x), dpow15(x.y)); break;
+        }
+        out[i] = r.x; out[i + 1] = r.y;
+    }
 }
 
 } // namespace ssk

@@ -86,7 +86,13 @@ struct HotBlock {
     float bs_center[3], bs_radius;
     int32_t spectral;
     int32_t arith;
-    int32_t pad_[4];
+    // EXACT mode's per-ray guard (eval_spec / render_sky_2<true>): a ray with 0 <= 1 / (cos(theta) + 0.01) <= exact_lim_s
+    // and gamma <= exact_lim_gamma keeps every exponential argument of every channel below 86 and, for the gamma
+    // term, above -86 (no overflow / underflow select can apply, results normal; the c1 exponent is clamped from
+    // below, see render_sky_2), and the host has checked |A0| <= 1e20 and that 1 + A8^2 - 2 A8 cos(gamma) stays in
+    // [2^-39, 2^39] for every channel (no special case of pow, quotient by it normal). Both -1 when that fails.
+    float exact_lim_s, exact_lim_gamma;
+    int32_t pad_[2];
     // --- wavelength importance sampling: ContinuousDistribution over [360, 720] nm, 10 nodes
     //     (sunsky.cpp:869-881, distr_1d.h:286-593); RGB emitters leave it zeroed
     float wl_pdf[10], wl_cdf[10];                    // unnormalised node densities, cumulative trapezoid sums (9 used)
@@ -227,15 +233,23 @@ SSK_HD float c1_fast(float T0, float T1, float T11, float s, bool &ok) {
 /// arithmetic. Same operations in the same order as render_sky_2(P, ch, r).
 constexpr int kExactPairRows = kSkyParams + 1;           // 9 coefficients + mean radiance
 constexpr int kExactPairTable = kExactPairRows * kChanPad;
-SSK_HD float2 render_sky_2(const float2 *xp, int ch, const RayTerms &r) {
+/// Safe = true (HotBlock::exact_lim_*: the ray passed the guard): the exponentials skip their range selects, the power
+/// its special cases, and the two quotients come from fdiv_normal_2. Every value is the one the generic sequence gives.
+template <bool Safe = false> SSK_HD float2 render_sky_2(const float2 *xp, int ch, const RayTerms &r) {
     float2 A0 = xp[0 * kChanPad + ch], A1 = xp[1 * kChanPad + ch], A2 = xp[2 * kChanPad + ch], A3 = xp[3 * kChanPad + ch],
            A4 = xp[4 * kChanPad + ch], A5 = xp[5 * kChanPad + ch], A6 = xp[6 * kChanPad + ch], A7 = xp[7 * kChanPad + ch],
            A8 = xp[8 * kChanPad + ch], L = xp[9 * kChanPad + ch];
-    float2 c1 = add2x(mul2(A0, dexp_2(mul2s(A1, r.inv_denom_c1))), splat2(1.f));
+    // Safe: the exponent is clamped at -80 from below. Below that the exponential is < 2e-35 either way and, with
+    // |A0| <= 1e20 (checked on the host), c1 = 1 + A0 e rounds to exactly 1 in both sequences; without the clamp the
+    // ~1 % of rays next to the horizon would fail the guard and, scattered over the warps, drag a fifth of them
+    // through the generic sequence
+    float2 x1 = mul2s(A1, r.inv_denom_c1);
+    if (Safe) x1 = f2(fmaxf(x1.x, -80.f), fmaxf(x1.y, -80.f));
+    float2 c1 = add2x(mul2(A0, dexp_2<Safe>(x1)), splat2(1.f));
     float2 arg = add2x(neg2(mul2s(mul2s(A8, 2.f), r.cos_gamma)), add2x(mul2(A8, A8), splat2(1.f)));
-    float2 pw = dpow15_2(arg);
-    float2 chi = f2(fdiv(r.one_plus_cg2, pw.x), fdiv(r.one_plus_cg2, pw.y));
-    float2 c2 = add2x(mul2(A3, dexp_2(mul2s(A4, r.gamma))), A2);
+    float2 pw = Safe ? dpow15_2_safe(arg) : dpow15_2(arg);
+    float2 chi = Safe ? fdiv_normal_2(splat2(r.one_plus_cg2), pw) : f2(fdiv(r.one_plus_cg2, pw.x), fdiv(r.one_plus_cg2, pw.y));
+    float2 c2 = add2x(mul2(A3, dexp_2<Safe>(mul2s(A4, r.gamma))), A2);
     c2 = add2x(mul2s(A5, r.cos_gamma_sqr), c2);
     c2 = add2x(mul2(A6, chi), c2);
     c2 = add2x(mul2s(A7, r.sqrt_cos_theta), c2);
@@ -643,6 +657,18 @@ SSK_COLD float4 sky_spec_exact_cold(const HotBlock &U, const HotBlock &S, RayTer
     return make_float4(o[0], o[1], o[2], o[3]);
 }
 
+/// EXACT spectral sky of the 4 wavelengths from the pair table, generic sequence (rays that fail the exact_lim guard)
+SSK_COLD float4 sky_spec_pairs_generic_cold(const HotBlock &U, const float2 *pairs, RayTerms r, float4 wav) {
+    const float wl[4] = { wav.x, wav.y, wav.z, wav.w };
+    float o[4];
+    for (int w = 0; w < 4; ++w) {
+        Bin b = wavelength_bin(wl[w]);
+        float2 sk = render_sky_2<false>(pairs, b.lo, r);
+        o[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
+    }
+    return make_float4(o[0], o[1], o[2], o[3]);
+}
+
 /// Sun-disc lanes of the spectral eval: the sun term of every wavelength on top of `sky` (sunsky.cpp:339-347),
 /// reference op order. `fast`: guard against the sun cancelling the sky (the fitted sun radiance can be
 /// negative for a low sun in a turbid atmosphere); such lanes redo the sky with the reference sequence.
@@ -679,6 +705,10 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
     EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = out[3] = 0.f; return; }
     bool ok = true, valid[4];
+    // EXACT from the pair table: rays inside the guard take the select-free sequence, the others redo the four
+    // wavelengths with the generic one behind a call (same values; see HotBlock::exact_lim_s)
+    const bool safe = A == kExact && ExactPairs && g.r.inv_denom_c1 >= 0.f && g.r.inv_denom_c1 <= U.exact_lim_s &&
+                      fabsf(g.r.gamma) <= U.exact_lim_gamma;
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
         Bin b = wavelength_bin(wav[w]);
@@ -702,11 +732,21 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
             out[w] = lerp(sk.x, sk.y, b.f);
         } else {
             // EXACT: with ExactPairs the kernel staged build_exact_pair_table's table in `pairs`
-            float2 sk = ExactPairs ? render_sky_2(pairs, b.lo, g.r) : render_sky_2(S, b.lo, g.r);
-            out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
+            if (ExactPairs) {
+                // guard failed: the value computed here is discarded below (no branch inside the unrolled loop)
+                float2 sk = render_sky_2<true>(pairs, b.lo, g.r);
+                out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
+            } else {
+                float2 sk = render_sky_2(S, b.lo, g.r);
+                out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
+            }
         }
     }
     const float4 wav4 = make_float4(wav[0], wav[1], wav[2], wav[3]);
+    if (A == kExact && ExactPairs && !safe) {
+        float4 e = sky_spec_pairs_generic_cold(U, pairs, g.r, wav4);
+        out[0] = e.x; out[1] = e.y; out[2] = e.z; out[3] = e.w;
+    }
     if (A == kFast && !ok) {
         float4 e = sky_spec_exact_cold(U, S, g.r, wav4);
         out[0] = e.x; out[1] = e.y; out[2] = e.z; out[3] = e.w;

@@ -80,6 +80,7 @@ SYMBOLS = {
     "ssk_host_copy_ceiling": (C.c_int, [C.c_int, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.POINTER(C.c_double),
                                       C.POINTER(C.c_double)]),
     "ssk_debug_fdiv_by_device": (C.c_int, [FP, FP, FP, C.c_size_t, C.c_void_p]),
+    "ssk_debug_math_device": (C.c_int, [C.c_int, FP, FP, FP, C.c_size_t, C.c_void_p]),
     "ssk_sun_coordinates": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                       C.c_float, C.c_float, FP]),
     "ssk_normalize_direction": (C.c_int, [FP, FP]),

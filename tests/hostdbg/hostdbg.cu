@@ -10,6 +10,11 @@ static const float2 *E_pairs(const HostEmitter &E) {
     build_pair_table(E.block, pairs);
     return pairs;
 }
+static const float2 *E_xpairs(const HostEmitter &E) {
+    static thread_local float2 xp[kExactPairTable];
+    build_exact_pair_table(E.block, xp);
+    return xp;
+}
 extern "C" {
 void *hostdbg_create(const ssk_params *p, const char *dir, int spectral) {
     HostEmitter *E = new HostEmitter();
@@ -26,7 +31,7 @@ void hostdbg_eval(void *h, size_t n, const float *wi, const float *wav, float *o
         Vec3 v = { wi[i], wi[n + i], wi[2 * n + i] };
         if (E.spectral) {
             float w[4] = { wav[i], wav[n + i], wav[2 * n + i], wav[3 * n + i] }, o[4];
-            if (E.block.arith) eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, v, w, true, o); else eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, v, w, true, o);
+            if (E.block.arith) eval_spec<1>(E.block, E.block, E_pairs(E), E.block.sun_rad, v, w, true, o); else if (getenv("HOSTDBG_NOPAIRS")) eval_spec<0>(E.block, E.block, nullptr, E.block.sun_rad, v, w, true, o); else eval_spec<0, true>(E.block, E.block, E_xpairs(E), E.block.sun_rad, v, w, true, o);
             for (int c = 0; c < 4; ++c) out[c * n + i] = o[c];
         } else if (getenv("HOSTDBG_PAIR")) {       // the two-rays-per-thread path of eval_rgb_pair_kernel
             if (i & 1) continue;

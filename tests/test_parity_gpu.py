@@ -389,6 +389,37 @@ def test_division_by_constant_is_ieee(ssk):
     assert worst == 0, f"{worst} quotients differ from IEEE division"
 
 
+def test_exact_mode_shortcuts_are_bit_identical(ssk):
+    """The guarded shortcuts of the EXACT spectral kernel (ssk_math.cuh: fdiv_normal_2, dexp_2<true>, dpow15_2_safe)
+    against the sequences they replace, over the whole range their guards admit (HotBlock::exact_lim_*): quotients of
+    normal operands up to 2^+-64, exp on [-86, 86], pow(x, 1.5) on [2^-39, 2^39]."""
+    import ctypes as C
+    import torch
+    from sunsky_b200 import _capi
+    L = _capi.lib()
+    gen = torch.Generator(device="cuda"); gen.manual_seed(17)
+    n = 1 << 24
+    p = lambda t: C.cast(t.data_ptr(), _capi.FP)
+    def run(op, a, b=None):
+        out = torch.empty_like(a)
+        assert L.ssk_debug_math_device(op, p(a), p(b) if b is not None else None, p(out), n, None) == 0
+        torch.cuda.synchronize()
+        return out.view(torch.int32)
+    def spread(lo_exp, hi_exp):           # mantissas all over the binade, exponents uniform in [lo_exp, hi_exp)
+        e = torch.randint(lo_exp, hi_exp, (n,), device="cuda", generator=gen).float()
+        return (1 + torch.rand(n, device="cuda", generator=gen)) * torch.exp2(e)
+    for trial in range(4):
+        # render_sky's quotient is (1 + cos^2 gamma) / pow(..): numerator in [1, 2], divisor in [2^-60, 2^60]
+        a = 1 + torch.rand(n, device="cuda", generator=gen) if trial < 2 else spread(-64, 64) * (1 - 2 * (torch.rand(n, device="cuda", generator=gen) < .5).float())
+        b = spread(-60, 60) if trial < 2 else spread(-64, 64)
+        assert int((run(0, a, b) != run(1, a, b)).sum()) == 0, "fdiv_normal_2 differs from IEEE division"
+        assert int((run(1, a, b) != (a / b).view(torch.int32)).sum()) == 0
+        x = (torch.rand(n, device="cuda", generator=gen) * 2 - 1) * (86.0 if trial % 2 else 8.0)
+        assert int((run(2, x) != run(3, x)).sum()) == 0, "dexp_2<true> differs from dexp"
+        y = spread(-39, 39) if trial % 2 else 0.001 + 4 * torch.rand(n, device="cuda", generator=gen)
+        assert int((run(4, y) != run(5, y)).sum()) == 0, "dpow15_2_safe differs from dpow15"
+
+
 FAST_GRID = [(t, a, eta) for t in (1.0, 2.3, 3.0, 5.5, 8.0, 10.0) for a in (0.0, 0.3, 1.0) for eta in (0.5, 3.0, 12.0, 30.0, 50.2, 75.0, 89.5)]
 
 
