@@ -156,19 +156,23 @@ SSK_HD float render_sky(const HotBlock &P, int ch, const RayTerms &r) {
 SSK_COLD float render_sky_cold(const HotBlock &P, int ch, RayTerms r) { return render_sky(P, ch, r); }
 /// render_sky for channels ch and ch + 1 at once (the two bins a wavelength falls between): the reference
 /// op order on float2, each element bit-identical to render_sky(). The one IEEE division stays per element.
-SSK_HD float2 render_sky_2(const HotBlock &P, int ch, const RayTerms &r) {
+template <bool Safe = false> SSK_HD float2 render_sky_2(const HotBlock &P, int ch, const RayTerms &r);
+template <bool Safe> SSK_HD float2 render_sky_2(const HotBlock &P, int ch, const RayTerms &r) {
     const float (*A)[kChanPad] = P.sky_params;
     float2 A0 = f2(A[0][ch], A[0][ch + 1]), A1 = f2(A[1][ch], A[1][ch + 1]), A2 = f2(A[2][ch], A[2][ch + 1]),
            A3 = f2(A[3][ch], A[3][ch + 1]), A4 = f2(A[4][ch], A[4][ch + 1]), A5 = f2(A[5][ch], A[5][ch + 1]),
            A6 = f2(A[6][ch], A[6][ch + 1]), A7 = f2(A[7][ch], A[7][ch + 1]), A8 = f2(A[8][ch], A[8][ch + 1]);
     // every product that feeds a sum goes through add2x (see there: ptxas would contract it otherwise)
-    float2 c1 = add2x(mul2(A0, dexp_2(mul2s(A1, r.inv_denom_c1))), splat2(1.f));
+    // Safe: see the pair-table overload below (same guard, same clamp)
+    float2 x1 = mul2s(A1, r.inv_denom_c1);
+    if (Safe) x1 = f2(fmaxf(x1.x, -80.f), fmaxf(x1.y, -80.f));
+    float2 c1 = add2x(mul2(A0, dexp_2<Safe>(x1)), splat2(1.f));
     // 1 + A8 * A8 - 2 * A8 * cos_gamma: ((1 + A8 A8) - ((2 A8) cos_gamma))
     float2 arg = add2x(neg2(mul2s(mul2s(A8, 2.f), r.cos_gamma)), add2x(mul2(A8, A8), splat2(1.f)));
-    float2 pw = dpow15_2(arg);
-    float2 chi = f2(fdiv(r.one_plus_cg2, pw.x), fdiv(r.one_plus_cg2, pw.y));
+    float2 pw = Safe ? dpow15_2_safe(arg) : dpow15_2(arg);
+    float2 chi = Safe ? fdiv_normal_2(splat2(r.one_plus_cg2), pw) : f2(fdiv(r.one_plus_cg2, pw.x), fdiv(r.one_plus_cg2, pw.y));
     // A2 + A3 exp(A4 gamma) + A5 cos^2 + A6 chi + A7 sqrt(cos_theta), summed left to right
-    float2 c2 = add2x(mul2(A3, dexp_2(mul2s(A4, r.gamma))), A2);
+    float2 c2 = add2x(mul2(A3, dexp_2<Safe>(mul2s(A4, r.gamma))), A2);
     c2 = add2x(mul2s(A5, r.cos_gamma_sqr), c2);
     c2 = add2x(mul2(A6, chi), c2);
     c2 = add2x(mul2s(A7, r.sqrt_cos_theta), c2);
@@ -505,15 +509,20 @@ SSK_HD Vec3p xform_p(const float *m, const Vec3p &v) {
              fma2(splat2(m[5]), v.z, fma2(splat2(m[4]), v.y, mul2s(v.x, m[3]))),
              fma2(splat2(m[8]), v.z, fma2(splat2(m[7]), v.y, mul2s(v.x, m[6]))) };
 }
-/// render_sky for one channel and two rays, reference op order (see render_sky)
-SSK_HD float2 render_sky_p(const HotBlock &P, int ch, const RayTermsP &r) {
+/// render_sky for one channel and two rays, reference op order (see render_sky). Safe = true: both rays passed the
+/// guard of HotBlock::exact_lim_* (or are inactive and discarded): select-free exp / pow, quotients by fdiv_normal_2,
+/// c1 exponent clamped from below (render_sky_2 explains why that keeps every bit)
+template <bool Safe = false> SSK_HD float2 render_sky_p(const HotBlock &P, int ch, const RayTermsP &r) {
     float A0 = P.sky_params[0][ch], A1 = P.sky_params[1][ch], A2 = P.sky_params[2][ch],
           A3 = P.sky_params[3][ch], A4 = P.sky_params[4][ch], A5 = P.sky_params[5][ch],
           A6 = P.sky_params[6][ch], A7 = P.sky_params[7][ch], A8 = P.sky_params[8][ch];
-    float2 c1 = add2x(mul2s(dexp_2(mul2s(r.inv_denom_c1, A1)), A0), splat2(1.f));
+    float2 x1 = mul2s(r.inv_denom_c1, A1);
+    if (Safe) x1 = f2(fmaxf(x1.x, -80.f), fmaxf(x1.y, -80.f));
+    float2 c1 = add2x(mul2s(dexp_2<Safe>(x1), A0), splat2(1.f));
     const float k1 = 1.f + A8 * A8, k2 = 2.f * A8;          // the same for every lane: uniform scalars
-    float2 chi = fdiv2(r.one_plus_cg2, dpow15_2(subp2(splat2(k1), mul2s(r.cos_gamma, k2))));
-    float2 c2 = add2x(mul2s(dexp_2(mul2s(r.gamma, A4)), A3), splat2(A2));
+    float2 arg = subp2(splat2(k1), mul2s(r.cos_gamma, k2));
+    float2 chi = Safe ? fdiv_normal_2(r.one_plus_cg2, dpow15_2_safe(arg)) : fdiv2(r.one_plus_cg2, dpow15_2(arg));
+    float2 c2 = add2x(mul2s(dexp_2<Safe>(mul2s(r.gamma, A4)), A3), splat2(A2));
     c2 = add2x(mul2s(r.cos_gamma_sqr, A5), c2);
     c2 = add2x(mul2s(chi, A6), c2);
     c2 = add2x(mul2s(r.sqrt_cos_theta, A7), c2);
@@ -555,6 +564,7 @@ SSK_COLD Vec3 finish_rgb_sun_cold(const HotBlock &U, const float *sun_rad, RayTe
 SSK_COLD float sky_rgb_exact_cold(const HotBlock &U, int c, RayTerms r) {
     return (float) ((double) (U.sky_scale * render_sky(U, c, exact_terms(r))) * (1.0 / 106.7502593994140625));
 }
+SSK_COLD float2 render_sky_p_generic_cold(const HotBlock &U, int c, RayTermsP r) { return render_sky_p<false>(U, c, r); }
 /// SunskyEmitter::eval, RGB, two rays (see eval_rgb)
 template <int A>
 SSK_HD void eval_rgb_p(const HotBlock &U, const float *sun_rad, const Vec3p &wi, bool act0, bool act1, float2 out[3]) {
@@ -582,7 +592,15 @@ SSK_HD void eval_rgb_p(const HotBlock &U, const float *sun_rad, const Vec3p &wi,
     } else {
         float2 res[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) res[c] = mul2s(render_sky_p(U, c, g.r), U.sky_scale);
+        for (int c = 0; c < 3; ++c) res[c] = mul2s(render_sky_p<true>(U, c, g.r), U.sky_scale);
+        {   // rays outside the guard (none with the dataset's coefficients): generic sequence for the pair
+            const bool in0 = g.r.inv_denom_c1.x >= 0.f && g.r.inv_denom_c1.x <= U.exact_lim_s && fabsf(g.r.gamma.x) <= U.exact_lim_gamma,
+                       in1 = g.r.inv_denom_c1.y >= 0.f && g.r.inv_denom_c1.y <= U.exact_lim_s && fabsf(g.r.gamma.y) <= U.exact_lim_gamma;
+            if (!((in0 || !g.active0) && (in1 || !g.active1))) {
+#pragma unroll 1
+                for (int c = 0; c < 3; ++c) res[c] = mul2s(render_sky_p_generic_cold(U, c, g.r), U.sky_scale);
+            }
+        }
         if (g.hit0) {
             Vec3 v = finish_rgb_sun_cold(U, sun_rad, lane_terms(g.r, 0), Vec3{ res[0].x, res[1].x, res[2].x });
             res[0].x = v.x; res[1].x = v.y; res[2].x = v.z;
@@ -705,9 +723,9 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
     EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = out[3] = 0.f; return; }
     bool ok = true, valid[4];
-    // EXACT from the pair table: rays inside the guard take the select-free sequence, the others redo the four
-    // wavelengths with the generic one behind a call (same values; see HotBlock::exact_lim_s)
-    const bool safe = A == kExact && ExactPairs && g.r.inv_denom_c1 >= 0.f && g.r.inv_denom_c1 <= U.exact_lim_s &&
+    // EXACT: rays inside the guard take the select-free sequence, the others redo the four wavelengths with the
+    // generic one behind a call (same values; see HotBlock::exact_lim_s)
+    const bool safe = A == kExact && g.r.inv_denom_c1 >= 0.f && g.r.inv_denom_c1 <= U.exact_lim_s &&
                       fabsf(g.r.gamma) <= U.exact_lim_gamma;
 #pragma unroll
     for (int w = 0; w < 4; ++w) {
@@ -737,14 +755,14 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
                 float2 sk = render_sky_2<true>(pairs, b.lo, g.r);
                 out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
             } else {
-                float2 sk = render_sky_2(S, b.lo, g.r);
+                float2 sk = render_sky_2<true>(S, b.lo, g.r);
                 out[w] = U.sky_scale * lerp(sk.x, sk.y, b.f);
             }
         }
     }
     const float4 wav4 = make_float4(wav[0], wav[1], wav[2], wav[3]);
-    if (A == kExact && ExactPairs && !safe) {
-        float4 e = sky_spec_pairs_generic_cold(U, pairs, g.r, wav4);
+    if (A == kExact && !safe) {
+        float4 e = ExactPairs ? sky_spec_pairs_generic_cold(U, pairs, g.r, wav4) : sky_spec_exact_cold(U, S, g.r, wav4);
         out[0] = e.x; out[1] = e.y; out[2] = e.z; out[3] = e.w;
     }
     if (A == kFast && !ok) {
