@@ -48,10 +48,15 @@ constexpr int kThreads = 256;
 #ifndef SSK_SPECX_MINB
 #define SSK_SPECX_MINB 1
 #endif
-// EXACT spectral eval, one ray per thread: 3 CTAs per SM (79 registers, no spills); left to the compiler it takes 89
-// registers and drops to 2 CTAs, which measured 5 % slower
+// EXACT spectral eval, one ray per thread. Measured on B200 (2^24 rays): no prefetch, 3 CTAs / SM (80 registers) 28.8
+// Gevals/s with 19 % of the stall samples on the first use of the loaded inputs; software-pipelined loads at 3 CTAs
+// (80 registers, prefetch registers spilled) 28.4; pipelined loads at 2 CTAs (96 registers, nothing spilled) 30.3;
+// inputs through the TMA ring (SSK_EVAL_TMA=1) 27.6. Without the pipelined loads 2 CTAs are 5 % slower than 3.
+#ifndef SSK_EVAL_PREFETCH_EXACT
+#define SSK_EVAL_PREFETCH_EXACT 1
+#endif
 #ifndef SSK_SPECX1_MINB
-#define SSK_SPECX1_MINB 3
+#define SSK_SPECX1_MINB 2
 #endif
 #ifndef SSK_SPECT_MINB
 #define SSK_SPECT_MINB 3           /* TMA-staged FAST spectral eval: resident CTAs per SM (4 = 64 registers, 8 bytes of spill) */
@@ -193,7 +198,7 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
     stage_block(&S, pairs, blk, A == kExact);
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
-    if (R == 1 && A == kFast && SSK_EVAL_PREFETCH == 1) {
+    if (R == 1 && (A == kFast || SSK_EVAL_PREFETCH_EXACT == 1) && SSK_EVAL_PREFETCH == 1) {
         // one ray per thread, software-pipelined: the 7 input planes of the next grid-stride iteration are
         // requested before this ray's arithmetic starts (ncu: long_scoreboard was the top stall without it)
         size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
