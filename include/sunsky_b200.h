@@ -310,7 +310,8 @@ int  ssk_group_sweep(const ssk_group *g, const ssk_params *frames, int n_frames,
 int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t n, void *stream);
 /* Test hook for EXACT mode's guarded shortcuts, each beside the sequence it replaces (device pointers, n even):
  * op 0 / 1: normal-range division a / b by reciprocal refinement / IEEE division; op 2 / 3: exp(a) without / with the
- * range selects; op 4 / 5: pow(a, 1.5) without / with the special cases. b may be NULL for op >= 2. */
+ * range selects; op 4 / 5: pow(a, 1.5) without / with the special cases; op 6 / 7: square root without / with the
+ * range test; op 8: scalar form of op 0. b may be NULL for ops 2-7. */
 int ssk_debug_math_device(int op, const float *a, const float *b, float *out, size_t n, void *stream);
 
 /* Measurement aid: the time the bare transfers of a *_host call take with nothing else in the way -- h2d_bytes from

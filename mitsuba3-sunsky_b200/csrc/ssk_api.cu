@@ -1039,7 +1039,7 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
 }
 
 int ssk_debug_math_device(int op, const float *a, const float *b, float *out, size_t n, void *stream) {
-    if (!a || !out || op < 0 || op > 5 || (op < 2 && !b) || (n & 1)) return fail(SSK_ERR_INVALID, "bad argument");
+    if (!a || !out || op < 0 || op > 8 || ((op < 2 || op == 8) && !b) || (n & 1)) return fail(SSK_ERR_INVALID, "bad argument");
     if (n == 0) return SSK_OK;
     math_probe_kernel<<<1184, 256, 0, (cudaStream_t) stream>>>(op, a, b, out, n);
     g_launches++;

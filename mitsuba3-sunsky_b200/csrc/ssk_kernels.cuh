@@ -188,6 +188,30 @@ eval_rgb_pair_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
     }
 }
 
+/// Ray loop of eval_spec_kernel, one ray per thread, software-pipelined: the 7 input planes of the next grid-stride
+/// iteration are requested before this ray's arithmetic starts (ncu: long_scoreboard was the top stall without it).
+/// The prefetch index is clamped to the last ray instead of guarded by a branch (the tail re-reads ray n - 1).
+template <int A, typename I>
+__device__ __forceinline__ void eval_spec_pipelined(const HotBlock &U, const HotBlock &S, const float2 *pairs, const float *sun_rad,
+                                                    const Planes3 &in, const Planes4 &wav, const OutPlanes4 &out, I n, float dir_sign) {
+    const I stride = (I) gridDim.x * (I) blockDim.x, last = n - 1;
+    I i = (I) blockIdx.x * (I) blockDim.x + (I) threadIdx.x;
+    if (i >= n) return;
+    float nx = __ldcs(in.x + i), ny = __ldcs(in.y + i), nz = __ldcs(in.z + i);
+    float na = __ldcs(wav.a + i), nb = __ldcs(wav.b + i), nc = __ldcs(wav.c + i), nd = __ldcs(wav.d + i);
+    for (;;) {
+        Vec3 wi = { dir_sign * nx, dir_sign * ny, dir_sign * nz };
+        float wl[4] = { na, nb, nc, nd }, o[4];
+        const I j = i + stride, jc = j < last ? j : last;
+        nx = __ldcs(in.x + jc); ny = __ldcs(in.y + jc); nz = __ldcs(in.z + jc);
+        na = __ldcs(wav.a + jc); nb = __ldcs(wav.b + jc); nc = __ldcs(wav.c + jc); nd = __ldcs(wav.d + jc);
+        eval_spec<A, A == kExact>(U, S, pairs, sun_rad, wi, wl, true, o);
+        __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]); __stcs(out.d + i, o[3]);
+        if (j >= n) break;
+        i = j;
+    }
+}
+
 /// eval / eval_direction, spectral (4 wavelengths per ray)
 template <int A, int R>
 __global__ void __launch_bounds__(kThreads, (A == kFast && R == 1) ? SSK_SPECF_MINB : (R == 1 ? SSK_SPECX1_MINB : SSK_SPECX_MINB))
@@ -199,25 +223,10 @@ eval_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restr
     const float *sun_rad = blk->sun_rad;
     const size_t stride = (size_t) gridDim.x * blockDim.x * R;
     if (R == 1 && (A == kFast || SSK_EVAL_PREFETCH_EXACT == 1) && SSK_EVAL_PREFETCH == 1) {
-        // one ray per thread, software-pipelined: the 7 input planes of the next grid-stride iteration are
-        // requested before this ray's arithmetic starts (ncu: long_scoreboard was the top stall without it)
-        size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
-        float nx = 0.f, ny = 0.f, nz = 0.f, na = 0.f, nb = 0.f, nc = 0.f, nd = 0.f;
-        if (i < n) {
-            nx = __ldcs(in.x + i); ny = __ldcs(in.y + i); nz = __ldcs(in.z + i);
-            na = __ldcs(wav.a + i); nb = __ldcs(wav.b + i); nc = __ldcs(wav.c + i); nd = __ldcs(wav.d + i);
-        }
-        for (; i < n; i += stride) {
-            Vec3 wi = { dir_sign * nx, dir_sign * ny, dir_sign * nz };
-            float wl[4] = { na, nb, nc, nd }, o[4];
-            const size_t j = i + stride;
-            if (j < n) {
-                nx = __ldcs(in.x + j); ny = __ldcs(in.y + j); nz = __ldcs(in.z + j);
-                na = __ldcs(wav.a + j); nb = __ldcs(wav.b + j); nc = __ldcs(wav.c + j); nd = __ldcs(wav.d + j);
-            }
-            eval_spec<A, A == kExact>(U, S, pairs, sun_rad, wi, wl, true, o);
-            __stcs(out.a + i, o[0]); __stcs(out.b + i, o[1]); __stcs(out.c + i, o[2]); __stcs(out.d + i, o[3]);
-        }
+        // one ray per thread, software-pipelined (eval_spec_pipelined); 32-bit ray indices whenever they fit: one
+        // IMAD.WIDE per plane address instead of a 64-bit add pair
+        if (n <= 0x7fffffffu) eval_spec_pipelined<A, uint32_t>(U, S, pairs, sun_rad, in, wav, out, (uint32_t) n, dir_sign);
+        else eval_spec_pipelined<A, size_t>(U, S, pairs, sun_rad, in, wav, out, n, dir_sign);
         return;
     }
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * R; i < n; i += stride) {
@@ -1101,7 +1110,7 @@ __global__ void fdiv_by_kernel(const float *a, const float *b, float *out, size_
 
 /// Test hook for the guarded shortcuts of EXACT mode, each next to the sequence it replaces (bit-compared by the tests):
 ///   op 0 / 1: fdiv_normal_2(a, b) / IEEE a / b      op 2 / 3: dexp_2<true>(a) / dexp(a)
-///   op 4 / 5: dpow15_2_safe(a) / dpow15(a)
+///   op 4 / 5: dpow15_2_safe(a) / dpow15(a)          op 6 / 7: sqrt_normal(a) / sqrtf(a)      op 8: fdiv_normal(a, b)
 __global__ void math_probe_kernel(int op, const float *a, const float *b, float *out, size_t n) {
     for (size_t i = ((size_t) blockIdx.x * blockDim.x + threadIdx.x) * 2; i + 1 < n; i += (size_t) gridDim.x * blockDim.x * 2) {
         float2 x = f2(a[i], a[i + 1]), y = b ? f2(b[i], b[i + 1]) : splat2(1.f), r;
@@ -1111,7 +1120,10 @@ __global__ void math_probe_kernel(int op, const float *a, const float *b, float 
             case 2: r = dexp_2<true>(x); break;
             case 3: r = f2(dexp(x.x), dexp(x.y)); break;
             case 4: r = dpow15_2_safe(x); break;
-            default: r = f2(dpow15(x.x), dpow15(x.y)); break;
+            case 5: r = f2(dpow15(x.x), dpow15(x.y)); break;
+            case 6: r = f2(sqrt_normal(x.x), sqrt_normal(x.y)); break;
+            case 7: r = f2(sqrtf(x.x), sqrtf(x.y)); break;
+            default: r = f2(fdiv_normal(x.x, y.x), fdiv_normal(x.y, y.y)); break;
         }
         out[i] = r.x; out[i + 1] = r.y;
     }

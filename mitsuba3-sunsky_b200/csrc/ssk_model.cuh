@@ -130,7 +130,9 @@ template <int A> SSK_HD RayTerms ray_terms(float cos_theta, float gamma) {
     r.cos_gamma_sqr = r.cos_gamma * r.cos_gamma;
     // `coefs[1] / (cos_theta + 0.01f)` divides a Spectrum by a Float: Dr.Jit routes an array divided by
     // a shallower operand to a1 * rcp(a2) (drjit/array_router.h:218-232), rcp = 1/x on the LLVM backend
-    r.inv_denom_c1 = fdiv(1.f, cos_theta + 0.01f);
+    // (only evaluated for active rays, cos_theta >= 0: the divisor lies in [0.01, 1.01] and fdiv_normal is the IEEE
+    // quotient without the range test)
+    r.inv_denom_c1 = fdiv_normal(1.f, cos_theta + 0.01f);
     r.one_plus_cg2 = 1.f + r.cos_gamma_sqr;
     r.sqrt_cos_theta = A == kFast ? hw_sqrt(fmaxf(cos_theta, 0.f)) : safe_sqrt(cos_theta);
     return r;
@@ -404,7 +406,7 @@ template <int A> SSK_HD EvalGeom eval_geom(const HotBlock &U, const Vec3 &wi, bo
     Vec3 neg = { -wi.x, -wi.y, -wi.z };
     Vec3 wo = xform(U.to_local, neg);
     Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
-    float cos_theta = wo.z, gamma = unit_angle(n, wo);
+    float cos_theta = wo.z, gamma = unit_angle<A == kFast>(n, wo);
     EvalGeom g;
     g.active = active_in && cos_theta >= 0.f;
     g.hit_sun = g.active && dot3(n, wo) >= U.cos_cutoff;
@@ -499,7 +501,7 @@ template <int A> SSK_HD RayTermsP ray_terms_p(float2 cos_theta, float2 gamma) {
     r.cos_gamma = dcos_2(gamma);
     r.cos_gamma_sqr = mul2(r.cos_gamma, r.cos_gamma);
     float2 den = add2s(cos_theta, 0.01f);
-    r.inv_denom_c1 = f2(fdiv(1.f, den.x), fdiv(1.f, den.y));
+    r.inv_denom_c1 = fdiv_normal_2(splat2(1.f), den);        // IEEE quotient for active rays (den in [0.01, 1.01]); others are discarded
     r.one_plus_cg2 = add2x(r.cos_gamma_sqr, splat2(1.f));
     r.sqrt_cos_theta = A == kFast ? f2(hw_sqrt(fmaxf(cos_theta.x, 0.f)), hw_sqrt(fmaxf(cos_theta.y, 0.f))) : safe_sqrt2(cos_theta);
     return r;
@@ -548,7 +550,7 @@ template <int A> SSK_HD EvalGeomP eval_geom_p(const HotBlock &U, const Vec3p &wi
     Vec3p neg = { neg2(wi.x), neg2(wi.y), neg2(wi.z) };
     Vec3p wo = xform_p(U.to_local, neg);
     Vec3 n = { U.sun_n[0], U.sun_n[1], U.sun_n[2] };
-    float2 cos_theta = wo.z, gamma = unit_angle_p(n, wo), dn = dot3_p(n, wo);
+    float2 cos_theta = wo.z, gamma = unit_angle_p<A == kFast>(n, wo), dn = dot3_p(n, wo);
     EvalGeomP g;
     g.active0 = act0 && cos_theta.x >= 0.f; g.active1 = act1 && cos_theta.y >= 0.f;
     g.hit0 = g.active0 && dn.x >= U.cos_cutoff; g.hit1 = g.active1 && dn.y >= U.cos_cutoff;

@@ -418,6 +418,13 @@ def test_exact_mode_shortcuts_are_bit_identical(ssk):
         assert int((run(2, x) != run(3, x)).sum()) == 0, "dexp_2<true> differs from dexp"
         y = spread(-39, 39) if trial % 2 else 0.001 + 4 * torch.rand(n, device="cuda", generator=gen)
         assert int((run(4, y) != run(5, y)).sum()) == 0, "dpow15_2_safe differs from dpow15"
+        assert int((run(8, a, b) != run(1, a, b)).sum()) == 0, "fdiv_normal differs from IEEE division"
+        # squared lengths from 2^-100 up; reciprocals of cos(theta) + 0.01
+        z = spread(-100, 4) if trial % 2 else 4 * torch.rand(n, device="cuda", generator=gen) + 7.9e-31
+        assert int((run(6, z) != run(7, z)).sum()) == 0, "sqrt_normal differs from sqrtf"
+        assert int((run(7, z) != torch.sqrt(z).view(torch.int32)).sum()) == 0
+        one = torch.ones(n, device="cuda"); den = 0.01 + 1.0 * torch.rand(n, device="cuda", generator=gen)
+        assert int((run(8, one, den) != (one / den).view(torch.int32)).sum()) == 0
 
 
 FAST_GRID = [(t, a, eta) for t in (1.0, 2.3, 3.0, 5.5, 8.0, 10.0) for a in (0.0, 0.3, 1.0) for eta in (0.5, 3.0, 12.0, 30.0, 50.2, 75.0, 89.5)]
