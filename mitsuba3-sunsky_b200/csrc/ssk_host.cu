@@ -293,7 +293,7 @@ void build_emitter_pre(HostEmitter &E, const ssk_params &p, bool from_constructo
         B.p_mu_phi[k] = mu_p; B.p_mu_theta[k] = mu_t; B.p_sigma_phi[k] = sg_p; B.p_sigma_theta[k] = sg_t;
         B.p_rsigma_phi[k] = 1.f / sg_p; B.p_rsigma_theta[k] = 1.f / sg_t;
         B.p_weight[k] = E.pmf[i]; B.p_volume[k] = volume; B.p_rvolume[k] = 1.f / volume;
-        if (!ordinary) B.pdf_generic = 1;
+        if (!ordinary || !(E.pmf[i] <= 1e10f)) B.pdf_generic = 1;     // (weight bound: gauss_exp_2 in ssk_model.cuh)
         const double kk = sqrt(0.5 * 1.4426950408889634074);
         B.p_k_phi[k] = (float) (kk / (double) sg_p); B.p_k_theta[k] = (float) (kk / (double) sg_t);
         B.p_wv[k] = (float) ((double) E.pmf[i] * 0.15915494309189533577 / (double) volume);

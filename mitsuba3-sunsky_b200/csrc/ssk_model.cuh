@@ -795,6 +795,14 @@ SSK_COLD float tgmm_sum_generic(const HotBlock &U, float phi, float theta) {
     return pdf;
 }
 
+/// exp(x) of a Gaussian exponent x <= 0 for the EXACT density sums below: the select-free dexp_2<true> on the
+/// exponent clamped at -86. A clamped element comes out as e^-86 = 4.5e-38 instead of something smaller (or the 0 the
+/// reference's underflow select gives): its numerator weight * g / 2 pi is far below 2^-70 (weights <= 1e10, checked on
+/// the host), so the sums flag it `tiny` like any other negligible term -- a density >= 2^-30 absorbs it without a
+/// trace, anything smaller is recomputed with the generic sequence. NaN / infinite exponents clamp the same way and
+/// end in the generic sum, which propagates them as the reference does.
+SSK_HD float2 gauss_exp_2(float2 x) { return dexp_2<true>(f2(fmaxf(x.x, -86.f), fmaxf(x.y, -86.f))); }
+
 /// The same sum with the three divisions per component done by fdiv_by() on reciprocals rounded at
 /// setup (identical quotients, 3 instructions each). A numerator below 2^-70 could make the residual
 /// inexact; such a term only matters when the whole density is tiny, and then the generic sum is redone.
@@ -809,7 +817,7 @@ SSK_HD float tgmm_sum_exact(const HotBlock &U, float phi, float theta) {
                                   f2(U.p_sigma_phi[i], U.p_sigma_phi[i + 1]), f2(U.p_rsigma_phi[i], U.p_rsigma_phi[i + 1])),
                    sy = fdiv_by_2(sub2(splat2(theta), f2(U.p_mu_theta[i], U.p_mu_theta[i + 1])),
                                   f2(U.p_sigma_theta[i], U.p_sigma_theta[i + 1]), f2(U.p_rsigma_theta[i], U.p_rsigma_theta[i + 1]));
-            float2 g = mul2s(dexp_2(mul2s(fma2(sy, sy, mul2(sx, sx)), -.5f)), SSK_INV_TWO_PI);
+            float2 g = mul2s(gauss_exp_2(mul2s(fma2(sy, sy, mul2(sx, sx)), -.5f)), SSK_INV_TWO_PI);
             float2 num = mul2(f2(U.p_weight[i], U.p_weight[i + 1]), g);
             tiny = tiny || fdiv_by_tiny(num.x) || fdiv_by_tiny(num.y);
             float2 q = fdiv_by_2(num, f2(U.p_volume[i], U.p_volume[i + 1]), f2(U.p_rvolume[i], U.p_rvolume[i + 1]));
@@ -886,7 +894,7 @@ SSK_HD float2 tgmm_sum_exact_p(const HotBlock &U, float2 phi, float2 theta) {
         if (i < U.n_pdf) {
             float2 sx = fdiv_by_2(add2s(phi, -U.p_mu_phi[i]), splat2(U.p_sigma_phi[i]), splat2(U.p_rsigma_phi[i])),
                    sy = fdiv_by_2(add2s(theta, -U.p_mu_theta[i]), splat2(U.p_sigma_theta[i]), splat2(U.p_rsigma_theta[i]));
-            float2 g = mul2s(dexp_2(mul2s(fma2(sy, sy, mul2(sx, sx)), -.5f)), SSK_INV_TWO_PI);
+            float2 g = mul2s(gauss_exp_2(mul2s(fma2(sy, sy, mul2(sx, sx)), -.5f)), SSK_INV_TWO_PI);
             float2 num = mul2s(g, U.p_weight[i]);
             tiny0 = tiny0 || fdiv_by_tiny(num.x); tiny1 = tiny1 || fdiv_by_tiny(num.y);
             pdf = add2(pdf, fdiv_by_2(num, splat2(U.p_volume[i]), splat2(U.p_rvolume[i])));
