@@ -381,7 +381,8 @@ struct SampleArgs {
     const float *w0, *w1, *w2, *w3;     // it.wavelengths (spectral)
     float *dx, *dy, *dz, *pdf;
     float *q0, *q1, *q2, *q3;           // weight planes
-    float *ox, *oy, *oz, *dist;         // ds.p / ds.dist, nullable
+    float *ox, *oy, *oz, *dist;         // ds.p / ds.dist, nullable (sample_ray through sample_sorted_kernel<.., Ray>: ray origin)
+    const float *s2x, *s2y;             // sample_ray only: the origin-disc sample
 };
 
 /// sample_direction, fused: select technique -> sample -> pdf -> eval -> weight (sunsky.cpp:399-441)
@@ -683,7 +684,9 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
 }
 
 #else
-template <int A, bool Spectral, bool Weight = true>
+/// Ray = true (RGB sample_ray, sunsky.cpp:354-397): u0 / u1 are sample3, the pdf carries the origin disc's
+/// 1 / (pi r^2), the stored direction is the RAY's (-d), and the origin is computed from a.s2x / a.s2y into a.ox..oz
+template <int A, bool Spectral, bool Weight = true, bool Ray = false>
 __global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
 sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
@@ -730,8 +733,21 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
             const int la = perm[l0], lb = two ? perm[l1] : la;
             const size_t ia = base + la, ib = base + lb;
             DirSampleP s = sample_dir_p<A>(U, S, f2(tu0[la], two ? tu0[lb] : 0.5f), f2(tu1[la], two ? tu1[lb] : 0.5f));
-            gst2(a.dx, ia, ib, two, s.d_world.x); gst2(a.dy, ia, ib, two, s.d_world.y); gst2(a.dz, ia, ib, two, s.d_world.z);
-            gst2(a.pdf, ia, ib, two, s.pdf);
+            if (Ray) {
+                static_assert(!Ray || (Weight && !Spectral), "ray mode: RGB, fused weights");
+                s.pdf = mul2s(s.pdf, U.ray_pdf_scale);
+                s.active0 = s.active0 && s.pdf.x > 0.f; s.active1 = s.active1 && s.pdf.y > 0.f;
+                const float2 rx = neg2(s.d_world.x), ry = neg2(s.d_world.y), rz = neg2(s.d_world.z);
+                gst2(a.dx, ia, ib, two, rx); gst2(a.dy, ia, ib, two, ry); gst2(a.dz, ia, ib, two, rz);
+                const float2 s2x = gld2(a.s2x, ia, ib, two, 0.5f), s2y = gld2(a.s2y, ia, ib, two, 0.5f);
+                float dxa, dya, dxb, dyb;
+                disk_concentric(s2x.x, s2y.x, dxa, dya); disk_concentric(s2x.y, s2y.y, dxb, dyb);
+                const Vec3 oa = ray_origin(U, Vec3{ rx.x, ry.x, rz.x }, dxa, dya), ob = ray_origin(U, Vec3{ rx.y, ry.y, rz.y }, dxb, dyb);
+                gst2(a.ox, ia, ib, two, f2(oa.x, ob.x)); gst2(a.oy, ia, ib, two, f2(oa.y, ob.y)); gst2(a.oz, ia, ib, two, f2(oa.z, ob.z));
+            } else {
+                gst2(a.dx, ia, ib, two, s.d_world.x); gst2(a.dy, ia, ib, two, s.d_world.y); gst2(a.dz, ia, ib, two, s.d_world.z);
+                gst2(a.pdf, ia, ib, two, s.pdf);
+            }
             // first pass: weight plane 0 keeps, per SLOT of the sorted tile, the sample it holds and its `active`
             // flag, so that weight_spec_sorted_kernel walks the samples in the same technique order
             if (!Weight) {
@@ -761,7 +777,7 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
                 gst2(c == 0 ? a.q0 : c == 1 ? a.q1 : c == 2 ? a.q2 : a.q3, ia, ib, two, w);
             }
             }
-            if (a.ox || a.dist) {          // bounding-sphere bookkeeping (sunsky.cpp:415-421), as sample_pair_kernel
+            if (!Ray && (a.ox || a.dist)) { // bounding-sphere bookkeeping (sunsky.cpp:415-421), as sample_pair_kernel
                 float2 px = f2(0.f, 0.f), py = px, pz = px;
                 if (a.px) { px = gld2(a.px, ia, ib, two, 0.f); py = gld2(a.py, ia, ib, two, 0.f); pz = gld2(a.pz, ia, ib, two, 0.f); }
                 Vec3p rel = { add2s(px, -U.bs_center[0]), add2s(py, -U.bs_center[1]), add2s(pz, -U.bs_center[2]) };

@@ -1248,6 +1248,16 @@ SSK_HD void coordinate_system_dev(const Vec3 &n, Vec3 &s, Vec3 &t) {
     t = { b, fmaf(n.y, n.y * a, sign), -n.y };
 }
 
+/// Ray origin of sample_ray (sunsky.cpp:390-392) from the ray direction and the concentric-disc point (ox, oy):
+/// Frame3f(d_world).to_world((ox, oy, 0)) (frame.h:39-41), then center + (offset - d_world) * radius
+SSK_HD Vec3 ray_origin(const HotBlock &U, const Vec3 &d_world, float ox, float oy) {
+    Vec3 fs, ft;
+    coordinate_system_dev(d_world, fs, ft);
+    Vec3 perp = { fmaf(d_world.x, 0.f, fmaf(ft.x, oy, fs.x * ox)), fmaf(d_world.y, 0.f, fmaf(ft.y, oy, fs.y * ox)),
+                  fmaf(d_world.z, 0.f, fmaf(ft.z, oy, fs.z * ox)) };
+    return { U.bs_center[0] + (perp.x - d_world.x) * U.bs_radius, U.bs_center[1] + (perp.y - d_world.y) * U.bs_radius,
+             U.bs_center[2] + (perp.z - d_world.z) * U.bs_radius };
+}
 /// Geometry part of sample_ray (sunsky.cpp:360-383, 390-392): direction, pdf (incl. the origin disc), origin
 struct RaySample { Vec3 d_world, origin; float pdf; bool active; };
 template <int A> SSK_HD RaySample sample_ray_geom(const HotBlock &U, const HotBlock &S, float s2x, float s2y, float s3x, float s3y) {
@@ -1261,13 +1271,7 @@ template <int A> SSK_HD RaySample sample_ray_geom(const HotBlock &U, const HotBl
     r.active = d.z >= 0.f;
     r.pdf = combined_pdf<A>(U, d, pick_sky, r.active) * U.ray_pdf_scale;
     r.active = r.active && r.pdf > 0.f;
-    Vec3 fs, ft;
-    coordinate_system_dev(r.d_world, fs, ft);
-    // Frame3f(d_world).to_world((ox, oy, 0)) (frame.h:39-41), then center + (offset - d_world) * radius
-    Vec3 perp = { fmaf(r.d_world.x, 0.f, fmaf(ft.x, oy, fs.x * ox)), fmaf(r.d_world.y, 0.f, fmaf(ft.y, oy, fs.y * ox)),
-                  fmaf(r.d_world.z, 0.f, fmaf(ft.z, oy, fs.z * ox)) };
-    r.origin = { U.bs_center[0] + (perp.x - r.d_world.x) * U.bs_radius, U.bs_center[1] + (perp.y - r.d_world.y) * U.bs_radius,
-                 U.bs_center[2] + (perp.z - r.d_world.z) * U.bs_radius };
+    r.origin = ray_origin(U, r.d_world, ox, oy);
     return r;
 }
 
