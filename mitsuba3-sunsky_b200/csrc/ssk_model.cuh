@@ -270,8 +270,8 @@ SSK_HD void build_exact_pair_table(const HotBlock &B, float2 *xp) {
 }
 
 /// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
-/// lane-dependent channels); the radiance scale T[10] folds sky_scale and, in RGB mode, the CIE-Y
-/// normalisation. What is approximated and what is not follows the conditioning of the formula:
+/// lane-dependent channels); the radiance scale (mean radiance x sky_scale and, in RGB mode, the CIE-Y
+/// normalisation) is folded into the five c2 coefficients T2, T3, T5, T6, T7 on the host, T[10] keeps it for reference. What is approximated and what is not follows the conditioning of the formula:
 ///  * c1 = 1 + A0 exp(A1 / (cos(theta) + 0.01)) has A0 ~ -1.1: it cancels to ~0.1 over most of the sky, a
 ///    10-20x amplification of any error in the exponential. It is evaluated with the reference sequence.
 ///  * the argument of the -3/2 power keeps the reference's two roundings (it cancels to ~(1 - A8)^2 towards
@@ -299,7 +299,7 @@ SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool
     extern long long g_fast_calls, g_fast_fallbacks;
     g_fast_calls++; g_fast_fallbacks += !ok;
 #endif
-    return c1 * c2 * T[10];
+    return c1 * c2;
 }
 
 /// sky_channel_fast on a pair of channels (the two neighbouring bins of a wavelength, two RGB channels):
@@ -316,7 +316,7 @@ SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, 
     float2 c2 = fma2(splat2(r.sqrt_cos_theta), T[7], fma2(chi, T[6], fma2(splat2(r.cos_gamma_sqr), T[5], fma2(ex, T[3], T[2]))));
     float2 s2 = fma2(splat2(r.sqrt_cos_theta), abs2(T[7]), fma2(chi, abs2(T[6]), fma2(splat2(r.cos_gamma_sqr), abs2(T[5]), fma2(ex, abs2(T[3]), abs2(T[2])))));
     ok = ok_e && fabsf(c2.x) >= kCancel * s2.x && fabsf(c2.y) >= kCancel * s2.y;
-    return mul2(mul2(c1, c2), T[10]);
+    return mul2(c1, c2);
 }
 
 /// compute_cos_psi (sunsky.h:384-392); `1.0 - ...` is evaluated in fp64 by the reference, which
@@ -543,7 +543,7 @@ SSK_HD float2 sky_channel_fast_p(const float T[kFastCoefs], const RayTermsP &r, 
     float2 s2 = fma2(r.sqrt_cos_theta, splat2(fabsf(T[7])), fma2(chi, splat2(fabsf(T[6])), fma2(r.cos_gamma_sqr, splat2(fabsf(T[5])), fma2(ex, splat2(fabsf(T[3])), splat2(fabsf(T[2]))))));
     ok0 = ok_e && fabsf(c2.x) >= kCancel * s2.x;
     ok1 = ok_e && fabsf(c2.y) >= kCancel * s2.y;
-    return mul2s(mul2(c1, c2), T[10]);
+    return mul2(c1, c2);
 }
 struct EvalGeomP { RayTermsP r; bool active0, active1, hit0, hit1; };
 template <int A> SSK_HD EvalGeomP eval_geom_p(const HotBlock &U, const Vec3p &wi, bool act0, bool act1) {
