@@ -313,6 +313,11 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
  * range selects; op 4 / 5: pow(a, 1.5) without / with the special cases; op 6 / 7: square root without / with the
  * range test; op 8: scalar form of op 0. b may be NULL for ops 2-7. */
 int ssk_debug_math_device(int op, const float *a, const float *b, float *out, size_t n, void *stream);
+/* Test hook: overrides the per-emitter guard of EXACT mode's select-free sky term (rays with 1 / (cos(theta) + 0.01) >
+ * lim_s or gamma > lim_gamma take the generic sequence behind a call). With the shipped datasets no ray ever fails the
+ * guard the library derives, so the tests shrink it to drive rays through the fallback and compare the results, which
+ * must not change by a bit. The next ssk_update restores the derived limits. */
+int ssk_debug_set_exact_limits(ssk_ctx *ctx, float lim_s, float lim_gamma);
 
 /* Measurement aid: the time the bare transfers of a *_host call take with nothing else in the way -- h2d_bytes from
  * pinned host memory on one stream while d2h_bytes go back on another, in pieces of piece_bytes (0 = one copy per

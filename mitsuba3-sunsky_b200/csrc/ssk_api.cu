@@ -1056,6 +1056,13 @@ int ssk_debug_fdiv_by_device(const float *a, const float *b, float *out, size_t 
     return SSK_OK;
 }
 
+int ssk_debug_set_exact_limits(ssk_ctx *ctx, float lim_s, float lim_gamma) {
+    if (!ctx) return fail(SSK_ERR_INVALID, "null context");
+    ctx->E.block.exact_lim_s = lim_s; ctx->E.block.exact_lim_gamma = lim_gamma;
+    if (int rc = rotate_block(ctx)) return rc;
+    return upload_block(ctx);
+}
+
 int ssk_debug_math_device(int op, const float *a, const float *b, float *out, size_t n, void *stream) {
     if (!a || !out || op < 0 || op > 8 || ((op < 2 || op == 8) && !b) || (n & 1)) return fail(SSK_ERR_INVALID, "bad argument");
     if (n == 0) return SSK_OK;

@@ -81,6 +81,7 @@ SYMBOLS = {
                                       C.POINTER(C.c_double)]),
     "ssk_debug_fdiv_by_device": (C.c_int, [FP, FP, FP, C.c_size_t, C.c_void_p]),
     "ssk_debug_math_device": (C.c_int, [C.c_int, FP, FP, FP, C.c_size_t, C.c_void_p]),
+    "ssk_debug_set_exact_limits": (C.c_int, [CTX, C.c_float, C.c_float]),
     "ssk_sun_coordinates": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float,
                                       C.c_float, C.c_float, FP]),
     "ssk_normalize_direction": (C.c_int, [FP, FP]),

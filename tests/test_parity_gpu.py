@@ -427,6 +427,30 @@ def test_exact_mode_shortcuts_are_bit_identical(ssk):
         assert int((run(8, one, den) != (one / den).view(torch.int32)).sum()) == 0
 
 
+@pytest.mark.parametrize("spectral", [False, True])
+def test_exact_guard_fallback_keeps_every_bit(ssk, spectral):
+    """EXACT mode evaluates the sky term with select-free sequences for rays inside a per-emitter guard and with the
+    generic sequence otherwise. The derived guard admits every ray for the shipped datasets, so the fallback is driven
+    here by shrinking the guard (ssk_debug_set_exact_limits): about half the rays, scattered over the warps, then take
+    the generic path, and eval / sample_direction / env maps must not change by a bit."""
+    from sunsky_b200 import _capi
+    import sunsky_b200.sweep as sw
+    L = _capi.lib()
+    rng = np.random.default_rng(23)
+    n = 1 << 16
+    wo = common.hemisphere_dirs(n, rng); u = rng.random((2, n), dtype=np.float32)
+    wav = (360 + 359 * rng.random((4, n), dtype=np.float32)).astype(np.float32) if spectral else None
+    for t, a, eta in [(3.0, 0.3, 30.0), (8.5, 0.9, 4.0), (1.2, 0.0, 75.0)]:
+        e = ssk.SunskyEmitter(spectral=spectral, turbidity=t, albedo=a, sun_direction=sw.sun_direction(eta), arith="exact")
+        want_eval = e.eval(-wo, wav)
+        d0, p0, w0 = e.sample_direction(u, None, wav)
+        for lim_s, lim_g in [(2.0, 10.0), (1e30, 1.0), (-1.0, -1.0)]:      # cos(theta) < 0.49 / gamma > 1 rad / every ray
+            assert L.ssk_debug_set_exact_limits(e._ctx, lim_s, lim_g) == 0
+            assert common.bit_equal(e.eval(-wo, wav), want_eval), (t, a, eta, lim_s, lim_g)
+            d1, p1, w1 = e.sample_direction(u, None, wav)
+            assert common.bit_equal(d1, d0) and common.bit_equal(p1, p0) and common.bit_equal(w1, w0)
+
+
 FAST_GRID = [(t, a, eta) for t in (1.0, 2.3, 3.0, 5.5, 8.0, 10.0) for a in (0.0, 0.3, 1.0) for eta in (0.5, 3.0, 12.0, 30.0, 50.2, 75.0, 89.5)]
 
 
