@@ -808,13 +808,30 @@ weight_spec_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock
     stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const size_t n_tiles = (n + kTile - 1) / kTile;
+    // slot codes are read one tile ahead: the dependent chain code -> sample index -> planes loses one memory round
+    // trip per tile, and the barrier below no longer waits for the slowest warp's code load
+    const int s0 = (int) threadIdx.x, s1 = s0 + kThreads;
+    int nc0 = -1, nc1 = -1;
+    if ((size_t) blockIdx.x < n_tiles) {
+        const size_t base = (size_t) blockIdx.x * kTile;
+        const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
+        nc0 = s0 < valid ? __float_as_int(__ldcs(a.q0 + base + s0)) : -1;
+        nc1 = s1 < valid ? __float_as_int(__ldcs(a.q0 + base + s1)) : -1;
+    }
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const size_t base = tile * kTile;
-        const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
-        const int s0 = (int) threadIdx.x, s1 = s0 + kThreads;
-        const int c0 = s0 < valid ? __float_as_int(__ldcs(a.q0 + base + s0)) : -1,
-                  c1 = s1 < valid ? __float_as_int(__ldcs(a.q0 + base + s1)) : -1;
-        __syncthreads();               // every slot code of the tile is read before weight plane 0 is overwritten
+        const int c0 = nc0, c1 = nc1;
+        const size_t next = tile + gridDim.x;
+        if (next < n_tiles) {
+            const size_t nbase = next * kTile;
+            const int nvalid = (int) (n - nbase < (size_t) kTile ? n - nbase : (size_t) kTile);
+            nc0 = s0 < nvalid ? __float_as_int(__ldcs(a.q0 + nbase + s0)) : -1;
+            nc1 = s1 < nvalid ? __float_as_int(__ldcs(a.q0 + nbase + s1)) : -1;
+        }
+        // every slot code of THIS tile was read (an iteration ago, before the previous barrier, or in the prologue) by
+        // all threads before weight plane 0 of the tile is overwritten below; the next tile's codes are read before
+        // this barrier and its plane is written after the next one
+        __syncthreads();
         // (requesting the second slot's planes before the first slot's arithmetic measured slower: 18.4 vs 18.7
         // Gsamples/s -- the FAST variant sits at its 80-register cap)
 #pragma unroll 1
