@@ -565,7 +565,19 @@ weight_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
 // samples of the SAME technique, so all warps but the one on the boundary are homogeneous. Inputs of the tile are
 // staged in shared memory, outputs are scattered back to their own slots (32-bit stores inside the tile's lines,
 // merged in L2). Per-sample arithmetic is the pair code unchanged: results are bit-identical to any other pairing.
-constexpr int kTile = 2 * kThreads;
+// A tile is kTileRounds x 512 samples: every thread sorts 2 * kTileRounds samples into the tile and then works through
+// kTileRounds pairs, round r taking sorted slots 512 r + 2 t, + 1. With one round (round 1 of the project) the first
+// warps of a CTA got TGMM samples and the last ones sun-cone samples, which cost 1.7 x as much: 24 % of the stall
+// samples sat at the tile barrier. With two rounds a half-and-half tile gives every warp one round of each technique,
+// and all warps of the CTA still run the same technique's code at the same time (instruction cache).
+#ifndef SSK_TILE_ROUNDS
+#define SSK_TILE_ROUNDS 2
+#endif
+#ifndef SSK_SORT_PER_WARP
+#define SSK_SORT_PER_WARP 0
+#endif
+constexpr int kTileRounds = SSK_SORT_PER_WARP ? 1 : SSK_TILE_ROUNDS;
+constexpr int kTile = 2 * kThreads * kTileRounds;
 __device__ __forceinline__ float2 gld2(const float *p, size_t ia, size_t ib, bool two, float pad) {
     return make_float2(__ldcs(p + ia), two ? __ldcs(p + ib) : pad);
 }
@@ -579,9 +591,6 @@ __device__ __forceinline__ void gst2(float *p, size_t ia, size_t ib, bool two, f
 // the two techniques' code paths (65 KB of SASS) thrash the instruction cache: `no_inst` becomes the top stall (29 %)
 // and the kernel is 4 % SLOWER (20.9 vs 21.7 Gsamples/s, profiles/r2_summary.md). The barriers were acting as a
 // phase lock that keeps the instruction working set small.
-#ifndef SSK_SORT_PER_WARP
-#define SSK_SORT_PER_WARP 0
-#endif
 #if SSK_SORT_PER_WARP
 template <int A, bool Spectral, bool Weight = true>
 __global__ void __launch_bounds__(kThreads, Spectral ? SSK_SAMPLE_MINB_SPEC : SSK_SAMPLE_MINB)
@@ -693,7 +702,7 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
     __shared__ __align__(16) float2 pairs[(A == kFast && Spectral) ? kPairTable : 1];
     __shared__ __align__(8) float tu0[kTile], tu1[kTile];
     __shared__ unsigned short perm[kTile];
-    __shared__ int wcount[kThreads / 32][2];
+    __shared__ int wcount[kTileRounds][kThreads / 32][2];
     stage_block(&S, (A == kFast && Spectral) ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
@@ -702,31 +711,49 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
     for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const size_t base = tile * kTile;
         const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
-        // 1. stage the tile's samples (coalesced 64-bit loads) and classify
-        const int l0 = 2 * t, l1 = 2 * t + 1;
-        float2 v0 = f2(0.f, 0.f), v1 = f2(0.f, 0.f);
-        if (l1 < valid) { v0 = __ldcs(reinterpret_cast<const float2 *>(a.u0 + base + l0)); v1 = __ldcs(reinterpret_cast<const float2 *>(a.u1 + base + l0)); }
-        else if (l0 < valid) { v0.x = __ldcs(a.u0 + base + l0); v1.x = __ldcs(a.u1 + base + l0); }
-        tu0[l0] = v0.x; tu0[l1] = v0.y; tu1[l0] = v1.x; tu1[l1] = v1.y;
-        const bool ok0 = l0 < valid, ok1 = l1 < valid;
-        const bool sky0 = ok0 && v0.x < U.sky_w, sky1 = ok1 && v0.y < U.sky_w;
-        const unsigned bs0 = __ballot_sync(0xffffffffu, sky0), bs1 = __ballot_sync(0xffffffffu, sky1);
-        const unsigned bn0 = __ballot_sync(0xffffffffu, ok0 && !sky0), bn1 = __ballot_sync(0xffffffffu, ok1 && !sky1);
-        if (lane == 0) { wcount[warp][0] = __popc(bs0) + __popc(bs1); wcount[warp][1] = __popc(bn0) + __popc(bn1); }
-        __syncthreads();
-        // 2. slot of each sample: sky samples first (warp-major), then sun samples
-        int sky_before = 0, sun_before = 0, sky_total = 0;
+        // 1. stage the tile's samples (coalesced 64-bit loads) and classify; sample 512 h + 2 t (+ 1) in part h
+        unsigned bs0[kTileRounds], bs1[kTileRounds], bn0[kTileRounds], bn1[kTileRounds];
 #pragma unroll
-        for (int w = 0; w < kThreads / 32; ++w) {
-            const int cs = wcount[w][0], cn = wcount[w][1];
-            if (w < warp) { sky_before += cs; sun_before += cn; }
-            sky_total += cs;
+        for (int h = 0; h < kTileRounds; ++h) {
+            const int l0 = 2 * kThreads * h + 2 * t, l1 = l0 + 1;
+            float2 v0 = f2(0.f, 0.f), v1 = f2(0.f, 0.f);
+            if (l1 < valid) { v0 = __ldcs(reinterpret_cast<const float2 *>(a.u0 + base + l0)); v1 = __ldcs(reinterpret_cast<const float2 *>(a.u1 + base + l0)); }
+            else if (l0 < valid) { v0.x = __ldcs(a.u0 + base + l0); v1.x = __ldcs(a.u1 + base + l0); }
+            tu0[l0] = v0.x; tu0[l1] = v0.y; tu1[l0] = v1.x; tu1[l1] = v1.y;
+            const bool ok0 = l0 < valid, ok1 = l1 < valid;
+            const bool sky0 = ok0 && v0.x < U.sky_w, sky1 = ok1 && v0.y < U.sky_w;
+            bs0[h] = __ballot_sync(0xffffffffu, sky0); bs1[h] = __ballot_sync(0xffffffffu, sky1);
+            bn0[h] = __ballot_sync(0xffffffffu, ok0 && !sky0); bn1[h] = __ballot_sync(0xffffffffu, ok1 && !sky1);
+            if (lane == 0) { wcount[h][warp][0] = __popc(bs0[h]) + __popc(bs1[h]); wcount[h][warp][1] = __popc(bn0[h]) + __popc(bn1[h]); }
         }
-        if (sky0) perm[sky_before + __popc(bs0 & lt)] = (unsigned short) l0;
-        else if (ok0) perm[sky_total + sun_before + __popc(bn0 & lt)] = (unsigned short) l0;
-        if (sky1) perm[sky_before + __popc(bs0) + __popc(bs1 & lt)] = (unsigned short) l1;
-        else if (ok1) perm[sky_total + sun_before + __popc(bn0) + __popc(bn1 & lt)] = (unsigned short) l1;
         __syncthreads();
+        // 2. slot of each sample: sky samples first (part-major, then warp-major), then sun samples
+        int sky_total = 0;
+#pragma unroll
+        for (int h = 0; h < kTileRounds; ++h)
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; ++w) sky_total += wcount[h][w][0];
+        int sky_before = 0, sun_before = 0;
+#pragma unroll
+        for (int h = 0; h < kTileRounds; ++h) {
+            int sky_here = sky_before, sun_here = sun_before;
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; ++w) {
+                const int cs = wcount[h][w][0], cn = wcount[h][w][1];
+                if (w < warp) { sky_here += cs; sun_here += cn; }
+                sky_before += cs; sun_before += cn;
+            }
+            const int l0 = 2 * kThreads * h + 2 * t, l1 = l0 + 1;
+            const bool in0 = (bs0[h] >> lane) & 1u, in1 = (bs1[h] >> lane) & 1u, sn0 = (bn0[h] >> lane) & 1u, sn1 = (bn1[h] >> lane) & 1u;
+            if (in0) perm[sky_here + __popc(bs0[h] & lt)] = (unsigned short) l0;
+            else if (sn0) perm[sky_total + sun_here + __popc(bn0[h] & lt)] = (unsigned short) l0;
+            if (in1) perm[sky_here + __popc(bs0[h]) + __popc(bs1[h] & lt)] = (unsigned short) l1;
+            else if (sn1) perm[sky_total + sun_here + __popc(bn0[h]) + __popc(bn1[h] & lt)] = (unsigned short) l1;
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int round = 0; round < kTileRounds; ++round) {
+        const int l0 = 2 * kThreads * round + 2 * t, l1 = l0 + 1;
         // 3. two samples of one technique per thread
         if (l0 < valid) {
             const bool two = l1 < valid;
@@ -790,6 +817,7 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
                 }
             }
         }
+        }
         __syncthreads();               // tu0 / tu1 / perm are rewritten by the next tile
     }
 }
@@ -809,34 +837,41 @@ weight_spec_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock
     const float *sun_rad = blk->sun_rad;
     const size_t n_tiles = (n + kTile - 1) / kTile;
     // slot codes are read one tile ahead: the dependent chain code -> sample index -> planes loses one memory round
-    // trip per tile, and the barrier below no longer waits for the slowest warp's code load
-    const int s0 = (int) threadIdx.x, s1 = s0 + kThreads;
-    int nc0 = -1, nc1 = -1;
+    // trip per tile, and the barrier below no longer waits for the slowest warp's code load. Thread t takes the sorted
+    // slots t, t + 256, ...: one from every stretch of the tile, sky samples first and sun-cone samples last
+    constexpr int kSlots = kTile / kThreads;
+    __shared__ int codes[2][kTile];                 // [tile parity][slot]; every thread reads back only what it wrote
+    int buf = 0;
     if ((size_t) blockIdx.x < n_tiles) {
         const size_t base = (size_t) blockIdx.x * kTile;
         const int valid = (int) (n - base < (size_t) kTile ? n - base : (size_t) kTile);
-        nc0 = s0 < valid ? __float_as_int(__ldcs(a.q0 + base + s0)) : -1;
-        nc1 = s1 < valid ? __float_as_int(__ldcs(a.q0 + base + s1)) : -1;
+#pragma unroll
+        for (int k = 0; k < kSlots; ++k) {
+            const int sk = (int) threadIdx.x + kThreads * k;
+            codes[0][sk] = sk < valid ? __float_as_int(__ldcs(a.q0 + base + sk)) : -1;
+        }
     }
-    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
         const size_t base = tile * kTile;
-        const int c0 = nc0, c1 = nc1;
         const size_t next = tile + gridDim.x;
         if (next < n_tiles) {
             const size_t nbase = next * kTile;
             const int nvalid = (int) (n - nbase < (size_t) kTile ? n - nbase : (size_t) kTile);
-            nc0 = s0 < nvalid ? __float_as_int(__ldcs(a.q0 + nbase + s0)) : -1;
-            nc1 = s1 < nvalid ? __float_as_int(__ldcs(a.q0 + nbase + s1)) : -1;
+#pragma unroll
+            for (int k = 0; k < kSlots; ++k) {
+                const int sk = (int) threadIdx.x + kThreads * k;
+                codes[buf ^ 1][sk] = sk < nvalid ? __float_as_int(__ldcs(a.q0 + nbase + sk)) : -1;
+            }
         }
         // every slot code of THIS tile was read (an iteration ago, before the previous barrier, or in the prologue) by
         // all threads before weight plane 0 of the tile is overwritten below; the next tile's codes are read before
         // this barrier and its plane is written after the next one
         __syncthreads();
-        // (requesting the second slot's planes before the first slot's arithmetic measured slower: 18.4 vs 18.7
+        // (requesting the next slot's planes before this slot's arithmetic measured slower: 18.4 vs 18.7
         // Gsamples/s -- the FAST variant sits at its 80-register cap)
 #pragma unroll 1
-        for (int k = 0; k < 2; ++k) {
-            const int cd = k == 0 ? c0 : c1;
+        for (int k = 0; k < kSlots; ++k) {
+            const int cd = codes[buf][(int) threadIdx.x + kThreads * k];
             if (cd < 0) continue;
             const size_t i = base + (size_t) (cd & (kTile - 1));
             const Vec3 wi = { -__ldcs(a.dx + i), -__ldcs(a.dy + i), -__ldcs(a.dz + i) };
