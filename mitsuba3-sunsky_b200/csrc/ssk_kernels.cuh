@@ -568,10 +568,12 @@ weight_spec_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__res
 // A tile is kTileRounds x 512 samples: every thread sorts 2 * kTileRounds samples into the tile and then works through
 // kTileRounds pairs, round r taking sorted slots 512 r + 2 t, + 1. With one round (round 1 of the project) the first
 // warps of a CTA got TGMM samples and the last ones sun-cone samples, which cost 1.7 x as much: 24 % of the stall
-// samples sat at the tile barrier. With two rounds a half-and-half tile gives every warp one round of each technique,
-// and all warps of the CTA still run the same technique's code at the same time (instruction cache).
+// samples sat at the tile barrier. With several rounds every warp gets its share of each technique, and all warps of
+// the CTA still run the same technique's code at the same time (instruction cache). Measured on B200, FAST, 2^24
+// samples (sun + sky RGB / spectral / sample_ray RGB, Gsamples/s): 1 round 22.1 / 18.9 / 19.4, 2 rounds 23.4 / 20.0 /
+// 20.2, 4 rounds 24.2 / 20.8 / 21.0, 8 rounds 23.0 / 20.4 / 19.5 (40 KB of shared memory per CTA).
 #ifndef SSK_TILE_ROUNDS
-#define SSK_TILE_ROUNDS 2
+#define SSK_TILE_ROUNDS 4
 #endif
 #ifndef SSK_SORT_PER_WARP
 #define SSK_SORT_PER_WARP 0
