@@ -400,12 +400,13 @@ int launch_sample_a(const ssk_ctx *ctx, bool spectral, bool vec, const SampleArg
     // both techniques in play (0 < w < 1): technique-sorted tiles; one technique only: plain pairs
     static const bool no_sort = getenv("SSK_SAMPLE_NOSORT") != nullptr;
     const float w = ctx->E.block.sky_w;
-    // Measured on B200 (2^24 samples, t=6 a=0.5 eta=50.2): FAST RGB 18.1 -> 20.9 Gsamples/s sorted; FAST spectral
-    // 14.8 -> 13.6, EXACT RGB 13.8 -> 13.0, EXACT spectral 9.4 -> 6.6 (their 73-112 KB bodies already stall on
-    // instruction fetch, and warps of one CTA running different techniques widen the fetch working set) -- so only
-    // the FAST RGB kernel sorts.
-    if (A == kFast && !spectral && !getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a) && w > 0.f && w < 1.f && !no_sort)
-        return launch_sample_sorted_t<kFast, false>(ctx, a, n, s);
+    // Measured on B200 (2^24 samples, t=6 a=0.5 eta=50.2), fused kernels sorted vs unsorted: with one round per tile
+    // FAST RGB 18.1 -> 20.9 Gsamples/s, EXACT RGB 13.8 -> 13.0, FAST spectral 14.8 -> 13.6, EXACT spectral 9.4 -> 6.6
+    // (73-112 KB bodies that already stall on instruction fetch); with four rounds per tile (ssk_kernels.cuh,
+    // SSK_TILE_ROUNDS) FAST RGB 24.2 and EXACT RGB 14.3 -> 15.3. Both RGB modes sort; spectral runs as two passes (above).
+    static const bool no_sort_exact = getenv("SSK_SAMPLE_NOSORT_EXACT") != nullptr;
+    if ((A == kFast || !no_sort_exact) && !spectral && !getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a) && w > 0.f && w < 1.f && !no_sort)
+        return launch_sample_sorted_t<A, false>(ctx, a, n, s);
     if (!getenv("SSK_RAYS_PER_THREAD") && sample_planes_aligned8(a))
         return spectral ? launch_sample_pair_t<A, true>(ctx, a, n, s) : launch_sample_pair_t<A, false>(ctx, a, n, s);
     if (spectral) return launch_sample_t<A, kSampleRays, true>(ctx, a, n, s);
@@ -489,14 +490,13 @@ int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStre
         return SSK_OK;
     }
 #if !SSK_SORT_PER_WARP
-    // FAST RGB: the technique-sorted ray-pair kernel of sample_direction in ray mode (origin, scaled pdf, -d). Measured
-    // on 2^24 rays: FAST 19.4 vs 17.9 Grays/s for the scalar kernel below; EXACT 12.9 vs 13.2 (as for sample_direction,
-    // the EXACT bodies are too large to gain from sorting), so EXACT keeps the scalar kernel
+    // RGB: the technique-sorted ray-pair kernel of sample_direction in ray mode (origin, scaled pdf, -d). Measured on
+    // 2^24 rays with four rounds per tile: FAST 21.0 vs 17.9 Grays/s for the scalar kernel below, EXACT 14.0 vs 13.2
     static const bool scalar_rays = getenv("SSK_RAY_SCALAR") != nullptr;
     const void *planes[] = { a.s2x, a.s2y, a.s3x, a.s3y, a.ox, a.oy, a.oz, a.dx, a.dy, a.dz, a.q0, a.q1, a.q2 };
     uintptr_t acc = 0;
     for (const void *q : planes) acc |= reinterpret_cast<uintptr_t>(q);
-    if (A == kFast && !Spectral && !scalar_rays && (acc & 7u) == 0) {
+    if (!Spectral && !scalar_rays && (acc & 7u) == 0) {
         SampleArgs sa = {};
         sa.u0 = a.s3x; sa.u1 = a.s3y; sa.s2x = a.s2x; sa.s2y = a.s2y;
         sa.dx = a.dx; sa.dy = a.dy; sa.dz = a.dz; sa.ox = a.ox; sa.oy = a.oy; sa.oz = a.oz;
