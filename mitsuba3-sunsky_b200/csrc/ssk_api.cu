@@ -481,6 +481,28 @@ template <int A, bool Spectral>
 int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStream_t s) {
     int grid = 1;
     static const bool fused = getenv("SSK_SAMPLE_FUSED") != nullptr;
+#if !SSK_SORT_PER_WARP
+    if (Spectral && !fused && !getenv("SSK_RAY_SCALAR")) {
+        // two technique-sorted passes, as spectral sample_direction: geometry (direction, origin, pdf), then
+        // wavelengths + eval + weight in the sorted order
+        const void *planes[] = { a.s2x, a.s2y, a.s3x, a.s3y, a.ox, a.oy, a.oz, a.dx, a.dy, a.dz, a.q0, a.q1, a.q2, a.q3 };
+        uintptr_t acc = 0;
+        for (const void *q : planes) acc |= reinterpret_cast<uintptr_t>(q);
+        if ((acc & 7u) == 0) {
+            SampleArgs sa = {};
+            sa.u0 = a.s3x; sa.u1 = a.s3y; sa.s2x = a.s2x; sa.s2y = a.s2y;
+            sa.dx = a.dx; sa.dy = a.dy; sa.dz = a.dz; sa.ox = a.ox; sa.oy = a.oy; sa.oz = a.oz;
+            sa.q0 = a.q0; sa.q1 = a.q1; sa.q2 = a.q2; sa.q3 = a.q3;
+            sa.wl_sample = a.wl_sample; sa.ow0 = a.w0; sa.ow1 = a.w1; sa.ow2 = a.w2; sa.ow3 = a.w3;
+            if (int rc = occupancy_grid(ctx, sample_sorted_kernel<A, false, false, true>, n, &grid, 2)) return rc;
+            sample_sorted_kernel<A, false, false, true><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, sa, n);
+            if (int rc = occupancy_grid(ctx, weight_spec_sorted_kernel<A, true>, n, &grid, 2)) return rc;
+            weight_spec_sorted_kernel<A, true><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, sa, n);
+            g_launches++;
+            return SSK_OK;
+        }
+    }
+#endif
     if (Spectral && !fused) {                      // two kernels, see weight_spec_kernel
         if (int rc = occupancy_grid(ctx, sample_ray_kernel<A, false, false>, n, &grid, 1)) return rc;
         sample_ray_kernel<A, false, false><<<grid, kThreads, 0, s>>>(hot(ctx), ctx->d_block, a, n);

@@ -383,6 +383,8 @@ struct SampleArgs {
     float *q0, *q1, *q2, *q3;           // weight planes
     float *ox, *oy, *oz, *dist;         // ds.p / ds.dist, nullable (sample_ray through sample_sorted_kernel<.., Ray>: ray origin)
     const float *s2x, *s2y;             // sample_ray only: the origin-disc sample
+    const float *wl_sample;             // spectral sample_ray only: the wavelength sample and the sampled wavelengths
+    float *ow0, *ow1, *ow2, *ow3;
 };
 
 /// sample_direction, fused: select technique -> sample -> pdf -> eval -> weight (sunsky.cpp:399-441)
@@ -763,7 +765,7 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
             const size_t ia = base + la, ib = base + lb;
             DirSampleP s = sample_dir_p<A>(U, S, f2(tu0[la], two ? tu0[lb] : 0.5f), f2(tu1[la], two ? tu1[lb] : 0.5f));
             if (Ray) {
-                static_assert(!Ray || (Weight && !Spectral), "ray mode: RGB, fused weights");
+                static_assert(!Ray || !Spectral, "ray mode: RGB with fused weights, or the first pass of the spectral path");
                 s.pdf = mul2s(s.pdf, U.ray_pdf_scale);
                 s.active0 = s.active0 && s.pdf.x > 0.f; s.active1 = s.active1 && s.pdf.y > 0.f;
                 const float2 rx = neg2(s.d_world.x), ry = neg2(s.d_world.y), rz = neg2(s.d_world.z);
@@ -773,6 +775,7 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
                 disk_concentric(s2x.x, s2y.x, dxa, dya); disk_concentric(s2x.y, s2y.y, dxb, dyb);
                 const Vec3 oa = ray_origin(U, Vec3{ rx.x, ry.x, rz.x }, dxa, dya), ob = ray_origin(U, Vec3{ rx.y, ry.y, rz.y }, dxb, dyb);
                 gst2(a.ox, ia, ib, two, f2(oa.x, ob.x)); gst2(a.oy, ia, ib, two, f2(oa.y, ob.y)); gst2(a.oz, ia, ib, two, f2(oa.z, ob.z));
+                if (!Weight) gst2(a.q1, ia, ib, two, s.pdf);      // no pdf output in sample_ray: weight plane 1 carries it to the second pass
             } else {
                 gst2(a.dx, ia, ib, two, s.d_world.x); gst2(a.dy, ia, ib, two, s.d_world.y); gst2(a.dz, ia, ib, two, s.d_world.z);
                 gst2(a.pdf, ia, ib, two, s.pdf);
@@ -830,7 +833,9 @@ sample_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__r
 /// low slots, sun-cone samples -- all inside the sun disc -- in the high ones), thread t takes slots t and
 /// t + kThreads, so only the warp on the boundary runs the sun-disc evaluation for some lanes and not others
 /// (unsorted, every warp did: 0.63 vs 0.33 ms sky-only for 2^24 samples).
-template <int A>
+/// Ray = true: second pass of spectral sample_ray (sunsky.cpp:384-396): the stored direction is the ray's, the pdf
+/// comes from weight plane 1, the wavelengths are importance-sampled here from a.wl_sample and written to a.ow0..3
+template <int A, bool Ray = false>
 __global__ void __launch_bounds__(kThreads, A == kFast ? SSK_SPECF_MINB : SSK_SPECX_MINB)
 weight_spec_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock *__restrict__ blk, SampleArgs a, size_t n) {
     __shared__ __align__(16) HotBlock S;
@@ -876,11 +881,19 @@ weight_spec_sorted_kernel(const __grid_constant__ HotBlock U, const EmitterBlock
             const int cd = codes[buf][(int) threadIdx.x + kThreads * k];
             if (cd < 0) continue;
             const size_t i = base + (size_t) (cd & (kTile - 1));
-            const Vec3 wi = { -__ldcs(a.dx + i), -__ldcs(a.dy + i), -__ldcs(a.dz + i) };
-            const float wl[4] = { __ldcs(a.w0 + i), __ldcs(a.w1 + i), __ldcs(a.w2 + i), __ldcs(a.w3 + i) };
-            const float pdf = __ldcs(a.pdf + i);
-            float o[4];
-            eval_spec<A>(U, S, pairs, sun_rad, wi, wl, (cd & kTile) != 0, o);
+            float o[4], pdf;
+            if (Ray) {
+                const Vec3 dr = { __ldcs(a.dx + i), __ldcs(a.dy + i), __ldcs(a.dz + i) };
+                pdf = __ldcs(a.q1 + i);
+                float w[4];
+                sample_wavelengths_spec<A>(U, S, pairs, sun_rad, dr, __ldcs(a.wl_sample + i), (cd & kTile) != 0, w, o);
+                __stcs(a.ow0 + i, w[0]); __stcs(a.ow1 + i, w[1]); __stcs(a.ow2 + i, w[2]); __stcs(a.ow3 + i, w[3]);
+            } else {
+                const Vec3 wi = { -__ldcs(a.dx + i), -__ldcs(a.dy + i), -__ldcs(a.dz + i) };
+                const float wl[4] = { __ldcs(a.w0 + i), __ldcs(a.w1 + i), __ldcs(a.w2 + i), __ldcs(a.w3 + i) };
+                pdf = __ldcs(a.pdf + i);
+                eval_spec<A>(U, S, pairs, sun_rad, wi, wl, (cd & kTile) != 0, o);
+            }
             const float inv_pdf = A == kFast ? hw_rcp(pdf) : fdiv(1.f, pdf);
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
