@@ -98,8 +98,9 @@ def test_empty_and_tiny_batches(ssk):
         assert common.bit_equal(e.eval(-g["wo"][:, 600:600 + n]), g["eval"][:, 600:600 + n])
         d, pdf, w = e.sample_direction(g["u"][:, :n])
         assert common.bit_equal(d, g["s_d"][:, :n]) and common.bit_equal(w, g["s_weight"][:, :n])
-    # ragged tails of every kernel family, both arithmetic modes, RGB and spectral: n around the 2-, 4- and
-    # 512-sample (sorted tile) granularities, at an offset that also misaligns the sliced planes' start
+    # ragged tails of every kernel family, both arithmetic modes, RGB and spectral: n around the 2-, 4-, 512- (one
+    # round of a sorted tile) and 2048-sample (sorted tile) granularities, at an offset that also misaligns the sliced
+    # planes' start
     import torch
     for name in ("cfg3_rgb_sunsky", "cfg3_spec_sunsky"):
         g = emitters.golden(name)
@@ -110,7 +111,7 @@ def test_empty_and_tiny_batches(ssk):
             full_d, full_pdf, full_w = e.sample_direction(g["u"], None, wav)
             full_o, full_rd, full_rwav, full_rw = e.sample_ray(g["wl_sample"], g["s2"], g["u"])
             assert e.sample_ray(g["wl_sample"][:0], g["s2"][:, :0], g["u"][:, :0])[0].shape == (3, 0)
-            for n in (1, 2, 511, 513, 1025):
+            for n in (1, 2, 511, 513, 1025, 2047, 2049, 3079):
                 for off in (0, 1):
                     sl = slice(off, off + n)
                     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
