@@ -122,6 +122,70 @@ def test_empty_and_tiny_batches(ssk):
                     assert common.bit_equal(o.cpu().numpy(), full_o[:, sl]) and common.bit_equal(rw.cpu().numpy(), full_rw[:, sl])
 
 
+@pytest.mark.parametrize("arith", ["exact", "fast"])
+@pytest.mark.parametrize("spectral", [False, True])
+def test_kernels_write_only_their_own_lanes(ssk, spectral, arith):
+    """Every output plane of eval / pdf_direction / sample_direction / sample_ray is a window of n lanes inside a
+    larger buffer filled with a sentinel: the kernels (sorted 2048-sample tiles, ray pairs, 32-bit and clamped
+    prefetch indices) must leave the 64 lanes on either side untouched, for n around every tile granularity and for
+    windows that start 4-, 8- and 16-byte aligned."""
+    import ctypes as C
+    import torch
+    from sunsky_b200 import _capi
+    import sunsky_b200.sweep as sw
+    L = _capi.lib()
+    e = ssk.SunskyEmitter(spectral=spectral, turbidity=4.0, albedo=0.4, sun_direction=sw.sun_direction(35.0), arith=arith)
+    e.set_scene(*common.SCENE_BBOX)
+    Cn = 4 if spectral else 3
+    pad, sentinel = 64, -12345.5
+    gen = torch.Generator(device="cuda"); gen.manual_seed(3)
+
+    def window(k, n, off):
+        big = torch.full((k, n + 2 * pad + 4), sentinel, device="cuda")
+        return big, big[:, pad + off:pad + off + n]
+
+    def pp(view):
+        arr = (_capi.FP * view.shape[0])()
+        for i in range(view.shape[0]):
+            arr[i] = C.cast(view[i].data_ptr(), _capi.FP)
+        return arr
+
+    def untouched(big, n, off):
+        return bool((big[:, :pad + off] == sentinel).all()) and bool((big[:, pad + off + n:] == sentinel).all())
+
+    for n in (1, 7, 255, 257, 512, 2047, 2048, 2049, 4100):
+        for off in (0, 1, 2):
+            u = torch.rand((2, n), device="cuda", generator=gen); s2 = torch.rand((2, n), device="cuda", generator=gen)
+            ws = torch.rand((1, n), device="cuda", generator=gen)
+            wav = 360 + 359 * torch.rand((4, n), device="cuda", generator=gen)
+            ct = torch.rand(n, device="cuda", generator=gen); st = (1 - ct * ct).sqrt(); ph = 6.28318 * torch.rand(n, device="cuda", generator=gen)
+            dirs = torch.stack([st * ph.cos(), st * ph.sin(), ct]).contiguous()
+            w_pp = pp(wav) if spectral else None
+            # eval, pdf
+            big_o, out = window(Cn, n, off)
+            assert L.ssk_eval_device(e._ctx, pp(-dirs), w_pp, n, pp(out), None) == 0
+            big_p, pdf = window(1, n, off)
+            assert L.ssk_pdf_direction_device(e._ctx, pp(dirs), n, C.cast(pdf[0].data_ptr(), _capi.FP), None) == 0
+            # sample_direction with every optional output
+            big_d, d = window(3, n, off); big_q, q = window(Cn, n, off); big_sp, spdf = window(1, n, off)
+            big_pp, p_out = window(3, n, off); big_dist, dist = window(1, n, off)
+            assert L.ssk_sample_direction_device(e._ctx, pp(u), None, w_pp, n, pp(d), C.cast(spdf[0].data_ptr(), _capi.FP), pp(q),
+                                                 pp(p_out), C.cast(dist[0].data_ptr(), _capi.FP), None) == 0
+            # sample_ray
+            big_ro, ro = window(3, n, off); big_rd, rd = window(3, n, off); big_rq, rq = window(Cn, n, off)
+            big_rw, rw = window(4, n, off)
+            assert L.ssk_sample_ray_device(e._ctx, C.cast(ws[0].data_ptr(), _capi.FP) if spectral else None, pp(s2), pp(u), n,
+                                           pp(ro), pp(rd), pp(rw) if spectral else None, pp(rq), None) == 0
+            torch.cuda.synchronize()
+            for name, big in [("eval", big_o), ("pdf", big_p), ("d", big_d), ("weight", big_q), ("sample pdf", big_sp),
+                              ("p", big_pp), ("dist", big_dist), ("ray o", big_ro), ("ray d", big_rd), ("ray weight", big_rq)] + \
+                             ([("ray wavelengths", big_rw)] if spectral else []):
+                assert untouched(big, n, off), f"{name}: lanes outside the window were written (n={n}, offset={off})"
+            # and the windows themselves were written in full
+            for name, view in [("eval", out), ("d", d), ("weight", q), ("ray o", ro), ("ray d", rd), ("ray weight", rq)]:
+                assert not bool((view == sentinel).any()), f"{name}: lanes inside the window were left unwritten (n={n}, offset={off})"
+
+
 def test_update_and_set_scene_reach_the_device(ssk):
     g1 = emitters.golden("cfg1_rgb"); g3 = emitters.golden("cfg3_rgb_sunsky")
     e = emitters.make(ssk, "cfg1_rgb", g=g1)
