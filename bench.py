@@ -157,7 +157,9 @@ def cpu_flavours(wi, wav, threads, budget_s=24.0):
         cal, _ = cpu_rate(r, wi, wav, threads, min(n_max, 1 << 18))
         n_all = int(min(n_max, max(1 << 18, 2 ** int(np.log2(cal * 1e9 * budget_s / 6)))))
         n_one = int(min(n_max, max(1 << 16, n_all // max(threads, 1))))
-        v_all, t_all = cpu_rate(r, wi, wav, threads, n_all, repeat=2)
+        # at least ~3 s of repeated passes: the first passes of a freshly started thread pool run 20-30 % slow
+        _, t_first = cpu_rate(r, wi, wav, threads, n_all)
+        v_all, t_all = cpu_rate(r, wi, wav, threads, n_all, repeat=int(min(40, max(3, np.ceil(3.0 / max(t_first, 1e-3))))))
         v_one, t_one = cpu_rate(r, wi, wav, 1, n_one)
         out[name] = {"value": v_all, "single_thread_value": v_one, "lanes": n_all, "seconds": t_all,
                      "single_thread_lanes": n_one}
@@ -540,7 +542,7 @@ def main():
                 fl = cpu_flavours(wi_h, wav_h, threads)
                 best = max(("packet", "scalar"), key=lambda k: fl[k]["value"])
                 cpu = {"value": fl[best]["value"], "unit": "Gevals/s", "cores": threads, "kind": "reference",
-                       "sample": f"{fl[best]['lanes']} of the {N_EVAL} configs[1] directions, best of 2 ({fl[best]['seconds']:.2f} s), the "
+                       "sample": f"{fl[best]['lanes']} of the {N_EVAL} configs[1] directions, best of >= 3 s of repeated passes ({fl[best]['seconds']:.2f} s each), the "
                                  f"reference's eval() on {'dr::Packet<float, %d> (%s)' % (fl['packet_width'], fl['isa']) if best == 'packet' else 'float'} "
                                  f"over {threads} host threads (the faster of its two CPU flavours; host has {cores} logical cores)",
                        "scalar_value": fl["scalar"]["value"], "scalar_single_thread_value": fl["scalar"]["single_thread_value"],
