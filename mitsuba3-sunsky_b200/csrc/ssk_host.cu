@@ -309,6 +309,10 @@ void build_emitter_post(HostEmitter &E, const float sky_rad[11], const float sun
     B.sky_w = E.sky_w; B.r_sky_w = 1.f / E.sky_w;
     B.one_minus_sky_w = 1.f - E.sky_w; B.r_one_minus_sky_w = 1.f / B.one_minus_sky_w;
     for (int i = 0; i < 10; ++i) { B.wl_pdf[i] = E.spectral_pdf[i]; B.wl_cdf[i] = E.spectral_cdf[i]; }
+    for (int i = 0; i < 10; ++i) {
+        const float y0 = B.wl_pdf[i], y1 = i + 1 < 10 ? B.wl_pdf[i + 1] : 0.f;
+        B.wl_rdiff[i] = fdiv(1.f, y0 - y1); B.wl_ry0[i] = fdiv(1.f, y0);
+    }
     B.wl_integral = E.spectral_integral; B.wl_norm = E.spectral_norm;
     B.wl_interval = (float) ((720.0 - 360.0) / 9.0); B.wl_inv_interval = 1.f / B.wl_interval;
     B.wl_valid_lo = E.spectral_valid[0]; B.wl_valid_hi = E.spectral_valid[1];

@@ -101,6 +101,10 @@ struct HotBlock {
     int32_t wl_valid_lo, wl_valid_hi, wl_iters;      // m_valid and the binary search trip count
     float ray_pdf_scale;                             // InvPi * rcp(radius^2) of sample_ray (sunsky.cpp:381)
     int32_t pad2_[4];
+    // per interval i of the wavelength density: RN(1 / (pdf[i] - pdf[i+1])) and RN(1 / pdf[i]), the two IEEE quotients
+    // ContinuousDistribution::sample_pdf forms per sample (distr_1d.h:489-493), taken once on the host (same operands,
+    // same correctly rounded result, infinities included)
+    float wl_rdiff[10], wl_ry0[10];
 };
 
 /// HotBlock followed by the sun radiance table, which only lanes inside the sun disc read (from L2).
@@ -1203,8 +1207,8 @@ SSK_HD void wavelength_sample_pdf(const HotBlock &U, const HotBlock &S, float sa
     const uint32_t index = start;
     float y0 = S.wl_pdf[index], y1 = S.wl_pdf[index + 1], c0 = index > 0 ? S.wl_cdf[index - 1] : 0.f;
     sample = (sample - c0) * U.wl_inv_interval;
-    float t_linear = (y0 - safe_sqrt(fmaf(y0, y0, 2.f * sample * (y1 - y0)))) * fdiv(1.f, y0 - y1),
-          t_const = sample * fdiv(1.f, y0),
+    float t_linear = (y0 - safe_sqrt(fmaf(y0, y0, 2.f * sample * (y1 - y0)))) * S.wl_rdiff[index],
+          t_const = sample * S.wl_ry0[index],
           t = y0 == y1 ? t_const : t_linear;
     wav = fmaf((float) index + t, U.wl_interval, 360.f);
     pdf = fmaf(t, y1 - y0, y0) * U.wl_norm;
