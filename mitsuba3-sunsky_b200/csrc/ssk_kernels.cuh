@@ -1005,13 +1005,23 @@ sample_wavelengths_kernel(const __grid_constant__ HotBlock U, const EmitterBlock
     __shared__ __align__(16) float2 pairs[A == kFast ? kPairTable : 1];
     stage_block(&S, A == kFast ? pairs : nullptr, blk);
     const float *sun_rad = blk->sun_rad;
-    const size_t stride = (size_t) gridDim.x * blockDim.x;
-    for (size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        Vec3 wi = { __ldcs(in.x + i), __ldcs(in.y + i), __ldcs(in.z + i) };
+    // software-pipelined like eval_spec_pipelined: the next grid-stride iteration's four planes are requested before
+    // this ray's arithmetic (prefetch index clamped to the last ray)
+    const size_t stride = (size_t) gridDim.x * blockDim.x, last = n - 1;
+    size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float nx = __ldcs(in.x + i), ny = __ldcs(in.y + i), nz = __ldcs(in.z + i), ns = __ldcs(sample + i);
+    for (;;) {
+        Vec3 wi = { nx, ny, nz };
+        const float smp = ns;
+        const size_t j = i + stride, jc = j < last ? j : last;
+        nx = __ldcs(in.x + jc); ny = __ldcs(in.y + jc); nz = __ldcs(in.z + jc); ns = __ldcs(sample + jc);
         float w[4], q[4];
-        sample_wavelengths_spec<A>(U, S, pairs, sun_rad, wi, __ldcs(sample + i), true, w, q);
+        sample_wavelengths_spec<A>(U, S, pairs, sun_rad, wi, smp, true, w, q);
         __stcs(wav.a + i, w[0]); __stcs(wav.b + i, w[1]); __stcs(wav.c + i, w[2]); __stcs(wav.d + i, w[3]);
         __stcs(weight.a + i, q[0]); __stcs(weight.b + i, q[1]); __stcs(weight.c + i, q[2]); __stcs(weight.d + i, q[3]);
+        if (j >= n) break;
+        i = j;
     }
 }
 
