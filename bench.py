@@ -365,7 +365,7 @@ def main():
     # the bare transfers of the same bytes, all ranks at once: what the host <-> device links of this box allow
     ceil_s, ceil_mean_s = C.c_double(), C.c_double()
     barrier()
-    rc = L.ssk_host_copy_ceiling(local, 7 * 4 * n_e2e, 4 * 4 * n_e2e, 7 * 4 * (1 << 21), 8, C.byref(ceil_s), C.byref(ceil_mean_s))
+    rc = L.ssk_host_copy_ceiling(local, 7 * 4 * n_e2e, 4 * 4 * n_e2e, 7 * 4 * (1 << 19), 8, C.byref(ceil_s), C.byref(ceil_mean_s))
     assert rc == 0, L.ssk_last_error()
     barrier()
     ceil_best_ms = max_over_ranks(ceil_s.value * 1e3)
@@ -377,7 +377,7 @@ def main():
            "pcie_gbs": e2e_bytes / (e2e_ms * 1e-3) / 1e9,
            "pcie_peak_gbs": e2e_bytes / (ceil_ms * 1e-3) / 1e9, "copy_ceiling_ms": ceil_ms, "frac": ceil_ms / e2e_ms,
            "copy_ceiling_best_ms": ceil_best_ms,
-           "note": "ssk_eval_host: pinned host planes, 2 Mi-ray chunks over 3 streams, one strided H2D and one strided D2H copy per "
+           "note": "ssk_eval_host: pinned host planes, 512 Ki-ray chunks over 3 streams, one strided H2D and one strided D2H copy per "
                    "chunk, kernel in between, all inside the timed region. pcie_peak_gbs: the same bytes as bare pinned copies "
                    "(H2D on one stream, D2H on another, every rank at once; ssk_host_copy_ceiling), per GPU: mean of 8 passes, max "
                    "over ranks (copy_ceiling_best_ms: the best pass, which at N > 1 is a pass some other rank had already "

@@ -569,9 +569,12 @@ int launch_sample_ray(const ssk_ctx *ctx, const float *wl_sample, const float *c
 int ensure_staging(const ssk_ctx *ctx, int planes) {
     Staging &st = ctx->st;
     // elements per chunk and plane and streams in rotation (SSK_HOST_CHUNK_LOG2 / SSK_HOST_STREAMS). Measured on
-    // B200, spectral eval, 2^24 rays, pinned buffers: 2^18 1.29, 2^19 1.44, 2^20 1.54, 2^21 1.61, 2^22 1.57 Gevals/s;
-    // 2 to 6 streams within 1 % of each other -> 2 Mi elements (8 MiB per plane), 3 streams
-    static const int chunk_log2 = getenv("SSK_HOST_CHUNK_LOG2") ? std::min(24, std::max(12, atoi(getenv("SSK_HOST_CHUNK_LOG2")))) : 21;
+    // B200, spectral eval, 2^24 rays, pinned buffers, round-2 pipeline (one strided copy per chunk and direction, no
+    // host synchronisation between chunks): 2^18 1.80, 2^19 1.84, 2^20 1.82, 2^21 1.76 Gevals/s at one GPU (the copy
+    // ceiling of the same bytes is 1.85), 2^19 3.48 vs 2^21 3.39 at eight; 3 or 4 streams alike. Small chunks shorten
+    // the pipeline's fill and drain (first H2D, last D2H), which nothing overlaps. Round 1's pipeline (11 plane copies
+    // and a host synchronisation per chunk) had its optimum at 2^21.
+    static const int chunk_log2 = getenv("SSK_HOST_CHUNK_LOG2") ? std::min(24, std::max(12, atoi(getenv("SSK_HOST_CHUNK_LOG2")))) : 19;
     static const int n_streams = getenv("SSK_HOST_STREAMS") ? std::min(Staging::kStreams, std::max(1, atoi(getenv("SSK_HOST_STREAMS")))) : 3;
     const size_t chunk = (size_t) 1 << chunk_log2;
     if (st.planes >= planes && st.chunk == chunk) return SSK_OK;
