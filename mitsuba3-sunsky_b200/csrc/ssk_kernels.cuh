@@ -15,7 +15,10 @@
 
 namespace ssk {
 
-constexpr int kThreads = 256;
+#ifndef SSK_THREADS
+#define SSK_THREADS 256
+#endif
+constexpr int kThreads = SSK_THREADS;
 
 // Resident CTAs per SM each kernel family is compiled for (the register cap of __launch_bounds__); overridable
 // for tuning builds (-DSSK_..._MINB=n).
