@@ -486,8 +486,10 @@ template <int A, bool Spectral>
 int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStream_t s) {
     int grid = 1;
     static const bool fused = getenv("SSK_SAMPLE_FUSED") != nullptr;
+    static const bool scalar_rays = getenv("SSK_RAY_SCALAR") != nullptr;
+    (void) scalar_rays;
 #if !SSK_SORT_PER_WARP
-    if (Spectral && !fused && !getenv("SSK_RAY_SCALAR")) {
+    if (Spectral && !fused && !scalar_rays) {
         // two technique-sorted passes, as spectral sample_direction: geometry (direction, origin, pdf), then
         // wavelengths + eval + weight in the sorted order
         const void *planes[] = { a.s2x, a.s2y, a.s3x, a.s3y, a.ox, a.oy, a.oz, a.dx, a.dy, a.dz, a.q0, a.q1, a.q2, a.q3 };
@@ -519,7 +521,6 @@ int launch_sample_ray_t(const ssk_ctx *ctx, const RayArgs &a, size_t n, cudaStre
 #if !SSK_SORT_PER_WARP
     // RGB: the technique-sorted ray-pair kernel of sample_direction in ray mode (origin, scaled pdf, -d). Measured on
     // 2^24 rays with four rounds per tile: FAST 21.0 vs 17.9 Grays/s for the scalar kernel below, EXACT 14.0 vs 13.2
-    static const bool scalar_rays = getenv("SSK_RAY_SCALAR") != nullptr;
     const void *planes[] = { a.s2x, a.s2y, a.s3x, a.s3y, a.ox, a.oy, a.oz, a.dx, a.dy, a.dz, a.q0, a.q1, a.q2 };
     uintptr_t acc = 0;
     for (const void *q : planes) acc |= reinterpret_cast<uintptr_t>(q);
