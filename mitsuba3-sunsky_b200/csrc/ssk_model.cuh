@@ -323,6 +323,33 @@ SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, 
     return mul2(c1, c2);
 }
 
+/// sky_channel_fast_2 for the spectral eval loop: instead of a flag per bin pair it keeps two running margins for the
+/// whole ray -- g1 = min |c1| (c1 = 1 + p cancels exactly when |c1| is small: the ray is fine if g1 >= kC1Guard) and
+/// g2 = min (|c2| - kCancel s2) (fine if g2 >= 0) -- so that the per-pair compares and their scale multiplies become one
+/// min each and the two compares happen once per ray. A NaN margin is dropped by the min: such a ray does not fall back,
+/// and its fast result is the NaN the reference sequence would propagate as well.
+SSK_HD float2 sky_channel_fast_2g(const float2 T[kFastCoefs], const RayTerms &r, float &g1, float &g2) {
+#if SSK_C1_MODE == 1
+    float2 a1 = mul2(T[1], splat2(r.inv_denom_c1));
+    float2 c1 = add2(mul2(T[0], f2(hw_ex2(a1.x), hw_ex2(a1.y))), splat2(1.f));
+    g1 = fminf(g1, fminf(fabsf(c1.x), fabsf(c1.y)));
+#else
+    bool ok_e;
+    float2 c1 = c1_fast_2(T[0], T[1], T[11], splat2(r.inv_denom_c1), ok_e);
+    if (!ok_e) g1 = 0.f;
+#endif
+    float2 t = subp2(T[8], mul2s(T[9], r.cos_gamma));
+    float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
+    float2 chi = mul2s(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
+    float2 a = mul2s(T[4], r.gamma);
+    float2 ex = f2(hw_ex2(a.x), hw_ex2(a.y));
+    float2 c2 = fma2(splat2(r.sqrt_cos_theta), T[7], fma2(chi, T[6], fma2(splat2(r.cos_gamma_sqr), T[5], fma2(ex, T[3], T[2]))));
+    float2 s2 = fma2(splat2(r.sqrt_cos_theta), abs2(T[7]), fma2(chi, abs2(T[6]), fma2(splat2(r.cos_gamma_sqr), abs2(T[5]), fma2(ex, abs2(T[3]), abs2(T[2])))));
+    float2 d = fma2(s2, splat2(-kCancel), abs2(c2));
+    g2 = fminf(g2, fminf(d.x, d.y));
+    return mul2(c1, c2);
+}
+
 /// compute_cos_psi (sunsky.h:384-392); `1.0 - ...` is evaluated in fp64 by the reference, which
 /// rounds to the same fp32 value as the fp32 subtraction
 SSK_HD float cos_psi(const HotBlock &P, float gamma) {
@@ -729,6 +756,7 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
     EvalGeom g = eval_geom<A>(U, wi, active_in);
     if (!g.active) { out[0] = out[1] = out[2] = out[3] = 0.f; return; }
     bool ok = true, valid[4];
+    float g1 = 1e30f, g2 = 1e30f;                   // FAST: cancellation margins of the ray (sky_channel_fast_2g)
     // EXACT: rays inside the guard take the select-free sequence, the others redo the four wavelengths with the
     // generic one behind a call (same values; see HotBlock::exact_lim_s)
     const bool safe = A == kExact && g.r.inv_denom_c1 >= 0.f && g.r.inv_denom_c1 <= U.exact_lim_s &&
@@ -750,9 +778,7 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
 #pragma unroll
             for (int k = 0; k < kFastCoefs; ++k) T[k] = pairs[k * kChanPad + b.lo];
 #endif
-            bool ok_w;
-            float2 sk = sky_channel_fast_2(T, g.r, ok_w);
-            ok = ok && ok_w;
+            float2 sk = sky_channel_fast_2g(T, g.r, g1, g2);
             out[w] = lerp(sk.x, sk.y, b.f);
         } else {
             // EXACT: with ExactPairs the kernel staged build_exact_pair_table's table in `pairs`
@@ -767,6 +793,7 @@ SSK_HD void eval_spec(const HotBlock &U, const HotBlock &S, const float2 *pairs,
         }
     }
     const float4 wav4 = make_float4(wav[0], wav[1], wav[2], wav[3]);
+    if (A == kFast) ok = g1 >= kC1Guard && g2 >= 0.f;
     if (A == kExact && !safe) {
         float4 e = ExactPairs ? sky_spec_pairs_generic_cold(U, pairs, g.r, wav4) : sky_spec_exact_cold(U, S, g.r, wav4);
         out[0] = e.x; out[1] = e.y; out[2] = e.z; out[3] = e.w;
