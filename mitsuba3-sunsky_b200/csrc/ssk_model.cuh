@@ -32,7 +32,8 @@ constexpr int kFastCoefs = 12;
 
 // How FAST mode evaluates c1 = 1 + A0 exp(A1 / (cos(theta) + 0.01)), which cancels to ~0.1 towards the zenith:
 //   0  the reference's exp polynomial with a cheaper range reduction (fexp): 24 instructions per bin pair
-//   1  MUFU ex2 on a pre-scaled exponent, guarded: |c1| < 1/16 |A0 e| (error amplification > 16) -> reference path
+//   1  c1 = fma(A0, MUFU ex2 of a pre-scaled exponent, 1), guarded: |c1| < 1/16 (error amplification > 16, A0 e ~ -1)
+//      -> reference path
 //   2  u = A1 s + ln|A0|; c1 = -expm1(u) by a degree-6 polynomial where A0 < 0 and |u| < 1/4 (no cancellation at
 //      all: the small quantity is computed directly), 1 + sgn(A0) 2^(u log2 e) on the MUFU elsewhere (c1 >= 0.22
 //      there, amplification < 5). Select, not branch. No fallback needed.
@@ -197,9 +198,8 @@ SSK_HD float2 c1_fast_2(float2 T0, float2 T1, float2 T11, float2 s, bool &ok) {
 #elif SSK_C1_MODE == 1
     (void) T11;
     float2 a = mul2(T1, s);
-    float2 p = mul2(T0, f2(hw_ex2(a.x), hw_ex2(a.y)));
-    float2 c1 = add2(p, splat2(1.f));
-    ok = fabsf(c1.x) >= kC1Guard * fabsf(p.x) && fabsf(c1.y) >= kC1Guard * fabsf(p.y);
+    float2 c1 = fma2(T0, f2(hw_ex2(a.x), hw_ex2(a.y)), splat2(1.f));
+    ok = fabsf(c1.x) >= kC1Guard && fabsf(c1.y) >= kC1Guard;
     return c1;
 #else
     ok = true;
@@ -221,8 +221,8 @@ SSK_HD float c1_fast(float T0, float T1, float T11, float s, bool &ok) {
     return T0 * fexp(T1 * s, ok) + 1.f;
 #elif SSK_C1_MODE == 1
     (void) T11;
-    float p = T0 * hw_ex2(T1 * s), c1 = p + 1.f;
-    ok = fabsf(c1) >= kC1Guard * fabsf(p);
+    float c1 = fmaf(T0, hw_ex2(T1 * s), 1.f);
+    ok = fabsf(c1) >= kC1Guard;
     return c1;
 #else
     ok = true;
@@ -286,7 +286,7 @@ SSK_HD void build_exact_pair_table(const HotBlock &B, float2 *xp) {
 ///    |c2| falls below kCancel of it; the caller then evaluates this channel with the reference sequence.
 constexpr float kCancel = 0.125f;
 /// All three variants (scalar, bin pair, ray pair) run ONE explicit op sequence, so they agree bit for bit:
-///   c1 = 1 + T0 fexp(T1 / (cos(theta) + .01))      product and sum rounded separately (it cancels to ~0.1)
+///   c1 = fma(T0, 2^(T1 / (cos(theta) + .01)), 1)   one rounding (SSK_C1_MODE 1; it cancels to ~0.1, guarded by |c1| >= 1/16)
 ///   t  = T8 - T9 cos(gamma)                        two roundings, as the reference (it cancels towards the sun)
 ///   c2 = fma chain T2 + T3 2^(T4 gamma) + T5 cos^2(gamma) + T6 chi + T7 sqrt(cos(theta)), s2 its |.| twin
 SSK_HD float sky_channel_fast(const float T[kFastCoefs], const RayTerms &r, bool &ok) {
@@ -331,7 +331,7 @@ SSK_HD float2 sky_channel_fast_2(const float2 T[kFastCoefs], const RayTerms &r, 
 SSK_HD float2 sky_channel_fast_2g(const float2 T[kFastCoefs], const RayTerms &r, float &g1, float &g2) {
 #if SSK_C1_MODE == 1
     float2 a1 = mul2(T[1], splat2(r.inv_denom_c1));
-    float2 c1 = add2(mul2(T[0], f2(hw_ex2(a1.x), hw_ex2(a1.y))), splat2(1.f));
+    float2 c1 = fma2(T[0], f2(hw_ex2(a1.x), hw_ex2(a1.y)), splat2(1.f));
     g1 = fminf(g1, fminf(fabsf(c1.x), fabsf(c1.y)));
 #else
     bool ok_e;
@@ -576,6 +576,29 @@ SSK_HD float2 sky_channel_fast_p(const float T[kFastCoefs], const RayTermsP &r, 
     ok1 = ok_e && fabsf(c2.y) >= kCancel * s2.y;
     return mul2(c1, c2);
 }
+/// sky_channel_fast_p with running cancellation margins per ray (see sky_channel_fast_2g): g1 = min |c1|, g2 = min
+/// (|c2| - kCancel s2) over the channels, element x / y for ray 0 / 1
+SSK_HD float2 min2(float2 a, float2 b) { return f2(fminf(a.x, b.x), fminf(a.y, b.y)); }
+SSK_HD float2 sky_channel_fast_pg(const float T[kFastCoefs], const RayTermsP &r, float2 &g1, float2 &g2) {
+#if SSK_C1_MODE == 1
+    float2 a1 = mul2s(r.inv_denom_c1, T[1]);
+    float2 c1 = fma2(splat2(T[0]), f2(hw_ex2(a1.x), hw_ex2(a1.y)), splat2(1.f));
+    g1 = min2(g1, abs2(c1));
+#else
+    bool ok_e;
+    float2 c1 = c1_fast_2(splat2(T[0]), splat2(T[1]), splat2(T[11]), r.inv_denom_c1, ok_e);
+    if (!ok_e) g1 = f2(0.f, 0.f);
+#endif
+    float2 t = subp2(splat2(T[8]), mul2s(r.cos_gamma, T[9]));
+    float2 rs = f2(hw_rsqrt(t.x), hw_rsqrt(t.y));
+    float2 chi = mul2(mul2(mul2(rs, rs), rs), r.one_plus_cg2);
+    float2 a = mul2s(r.gamma, T[4]);
+    float2 ex = f2(hw_ex2(a.x), hw_ex2(a.y));
+    float2 c2 = fma2(r.sqrt_cos_theta, splat2(T[7]), fma2(chi, splat2(T[6]), fma2(r.cos_gamma_sqr, splat2(T[5]), fma2(ex, splat2(T[3]), splat2(T[2])))));
+    float2 s2 = fma2(r.sqrt_cos_theta, splat2(fabsf(T[7])), fma2(chi, splat2(fabsf(T[6])), fma2(r.cos_gamma_sqr, splat2(fabsf(T[5])), fma2(ex, splat2(fabsf(T[3])), splat2(fabsf(T[2]))))));
+    g2 = min2(g2, fma2(s2, splat2(-kCancel), abs2(c2)));
+    return mul2(c1, c2);
+}
 struct EvalGeomP { RayTermsP r; bool active0, active1, hit0, hit1; };
 template <int A> SSK_HD EvalGeomP eval_geom_p(const HotBlock &U, const Vec3p &wi, bool act0, bool act1) {
     Vec3p neg = { neg2(wi.x), neg2(wi.y), neg2(wi.z) };
@@ -604,15 +627,22 @@ SSK_HD void eval_rgb_p(const HotBlock &U, const float *sun_rad, const Vec3p &wi,
     EvalGeomP g = eval_geom_p<A>(U, wi, act0, act1);
     if (!g.active0 && !g.active1) { out[0] = out[1] = out[2] = f2(0.f, 0.f); return; }
     if (A == kFast) {
+        float2 g1 = f2(1e30f, 1e30f), g2 = g1;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             float T[kFastCoefs];
 #pragma unroll
             for (int k = 0; k < kFastCoefs; ++k) T[k] = U.sky_fast[k][c];
-            bool ok0, ok1;
-            out[c] = sky_channel_fast_p(T, g.r, ok0, ok1);
-            if (!ok0 && g.active0) out[c].x = sky_rgb_exact_cold(U, c, lane_terms(g.r, 0));
-            if (!ok1 && g.active1) out[c].y = sky_rgb_exact_cold(U, c, lane_terms(g.r, 1));
+            out[c] = sky_channel_fast_pg(T, g.r, g1, g2);
+        }
+        // a ray on which some channel cancels redoes its three channels with the reference sequence
+        if (g.active0 && !(g1.x >= kC1Guard && g2.x >= 0.f)) {
+#pragma unroll 1
+            for (int c = 0; c < 3; ++c) out[c].x = sky_rgb_exact_cold(U, c, lane_terms(g.r, 0));
+        }
+        if (g.active1 && !(g1.y >= kC1Guard && g2.y >= 0.f)) {
+#pragma unroll 1
+            for (int c = 0; c < 3; ++c) out[c].y = sky_rgb_exact_cold(U, c, lane_terms(g.r, 1));
         }
         if (g.hit0) {
             Vec3 v = add_sun_rgb_fast_cold(U, sun_rad, lane_terms(g.r, 0), Vec3{ out[0].x, out[1].x, out[2].x });
