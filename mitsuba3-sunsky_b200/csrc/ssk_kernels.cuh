@@ -944,12 +944,20 @@ setup_sum_kernel(const float *__restrict__ buf, float *__restrict__ partial, int
     const float *p = buf + (size_t) emitter * emitter_stride + (size_t) chain * kQuadChunk;
     constexpr int kTiles = 8;
     float acc = 0.f;
+    // the next group of tiles is requested before the current group is added: the chain of adds never waits for memory
+    float nv[kTiles];
+#pragma unroll
+    for (int u = 0; u < kTiles; ++u) {
+        const int j = u * 32 + lane;
+        nv[u] = j < len ? __ldcg(p + j) : 0.f;
+    }
     for (int j0 = 0; j0 < len; j0 += 32 * kTiles) {
         float v[kTiles];
 #pragma unroll
         for (int u = 0; u < kTiles; ++u) {
-            const int j = j0 + u * 32 + lane;
-            v[u] = j < len ? __ldcg(p + j) : 0.f;
+            v[u] = nv[u];
+            const int j = j0 + 32 * kTiles + u * 32 + lane;
+            nv[u] = j < len ? __ldcg(p + j) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < kTiles; ++u) {
