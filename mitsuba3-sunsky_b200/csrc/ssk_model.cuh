@@ -275,9 +275,11 @@ SSK_HD void build_exact_pair_table(const HotBlock &B, float2 *xp) {
 
 /// render_sky for one channel, FAST. `T` is one column of HotBlock::sky_fast (already gathered for
 /// lane-dependent channels); the radiance scale (mean radiance x sky_scale and, in RGB mode, the CIE-Y
-/// normalisation) is folded into the five c2 coefficients T2, T3, T5, T6, T7 on the host, T[10] keeps it for reference. What is approximated and what is not follows the conditioning of the formula:
+/// normalisation) is folded into the five c2 coefficients T2, T3, T5, T6, T7 on the host, T[10] keeps it for
+/// reference. What is approximated and what is not follows the conditioning of the formula:
 ///  * c1 = 1 + A0 exp(A1 / (cos(theta) + 0.01)) has A0 ~ -1.1: it cancels to ~0.1 over most of the sky, a
-///    10-20x amplification of any error in the exponential. It is evaluated with the reference sequence.
+///    10-20x amplification of any error in the exponential. SSK_C1_MODE selects how it is evaluated (default: MUFU
+///    ex2 and one FMA, with a fallback to the reference sequence where |c1| < 1/16).
 ///  * the argument of the -3/2 power keeps the reference's two roundings (it cancels to ~(1 - A8)^2 towards
 ///    the sun); the power itself is rsqrt^3.
 ///  * c2 is a sum of terms of either sign that is well conditioned except for a low sun near the horizon,
